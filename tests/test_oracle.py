@@ -1,0 +1,177 @@
+"""Pins oracle/exchange_oracle.py (CPU restatement) before anything trusts it.
+
+1. The reference's own known-answer vectors for this path, restated from
+   python/ray/data/tests/test_util.py:235-377 and test_sort.py:165-183.
+2. Fixtures under tests/golden/ produced by running the reference itself
+   (tests/golden/make_golden.py).
+3. When /root/reference is present (build container only): live side-by-side.
+"""
+import random
+
+import numpy as np
+import pyarrow as pa
+import pytest
+
+import _golden as G
+from oracle import exchange_oracle as O
+from oracle import ref_shim
+
+
+# ---- 1. reference KATs (test_util.py:235-377) --------------------------------
+
+def test_kat_single_column_ascending():
+    t = pa.table({"value": [1, 2, 2, 3, 5]})
+    got = [O.find_partition_index(t, (v,), ["value"], [False]) for v in (0, 2, 4, 6)]
+    assert got == [0, 1, 4, 5]
+
+
+def test_kat_single_column_descending():
+    t = pa.table({"value": [5, 3, 2, 2, 1]})
+    got = [O.find_partition_index(t, (v,), ["value"], [True]) for v in (6, 3, 2, 0)]
+    assert got == [0, 2, 4, 5]
+
+
+def test_kat_multi_column():
+    t = pa.table({"col1": [1, 1, 1, 2, 2], "col2": [3, 2, 1, 2, 1]})
+    f = lambda d: O.find_partition_index(t, d, ["col1", "col2"], [False, True])
+    assert [f((1, 3)), f((1, 2)), f((2, 2)), f((0, 4)), f((2, 0))] == [0, 1, 3, 0, 5]
+
+
+def test_kat_nulls():
+    t = pa.table({"value": [1, 2, 3, None, None]})
+    f = lambda d: O.find_partition_index(t, d, ["value"], [False])
+    assert [f((2,)), f((4,)), f((None,))] == [1, 3, 5]
+
+
+def test_kat_duplicates():
+    t = pa.table({"value": [2, 2, 2, 2, 2]})
+    assert [O.find_partition_index(t, (v,), ["value"], [False]) for v in (2, 1, 3)] == [0, 0, 5]
+    assert [O.find_partition_index(t, (v,), ["value"], [True]) for v in (2, 1, 3)] == [5, 5, 0]
+
+
+def test_kat_find_partitions():
+    t = pa.table({"value": [1, 2, 2, 3, 5]})
+    p = O.find_partitions(t, [(0,), (2,), (4,), (6,)], ["value"], [False])
+    assert [x.to_pydict()["value"] for x in p] == [[], [1], [2, 2, 3], [5], []]
+    t = pa.table({"value": [5, 3, 2, 2, 1]})
+    p = O.find_partitions(t, [(6,), (3,), (2,), (0,)], ["value"], [True])
+    assert [x.to_pydict()["value"] for x in p] == [[], [5, 3], [2, 2], [1], []]
+    t = pa.table({"col1": [1, 1, 1, 1, 1, 2, 2], "col2": [4, 3, 2.5, 2, 1, 2, 1]})
+    p = O.find_partitions(t, [(1, 3), (1, 2), (2, 2), (2, 0)], ["col1", "col2"], [False, True])
+    assert [x.to_pydict()["col2"] for x in p] == [[4], [3, 2.5], [2, 1], [2, 1], []]
+    t = pa.table({"col1": [2, 2, 1, 1, 1, 1, 1], "col2": [1, 2, 1, 2, 3, 4, 5]})
+    p = O.find_partitions(t, [(2, 0), (2, 2), (1, 2), (1, 6)], ["col1", "col2"], [True, False])
+    assert [x.to_pydict()["col2"] for x in p] == [[], [1, 2], [1, 2], [3, 4, 5], []]
+    t = pa.table({"value": [1, 2, 3, None, None]})
+    p = O.find_partitions(t, [(2,), (4,)], ["value"], [False])
+    assert [x.to_pydict()["value"] for x in p] == [[1], [2, 3], [None, None]]
+    t = pa.table({"value": [2, 2, 2, 2, 2]})
+    p = O.find_partitions(t, [(1,), (2,), (3,)], ["value"], [False])
+    assert [x.to_pydict()["value"] for x in p] == [[], [], [2, 2, 2, 2, 2], []]
+
+
+def test_kat_seeded_two_key_sort():
+    # test_sort.py:165-183: Random(0xDEED), a in [0,10), b in [0,10); sort == sorted()
+    rnd = random.Random(0xDEED)
+    rows = [{"a": rnd.randint(0, 9), "b": rnd.randint(0, 9)} for _ in range(1000)]
+    t = pa.Table.from_pylist(rows)
+    for desc in (False, True):
+        s = O.sort_table(t, ["a", "b"], [desc, desc])
+        exp = sorted(((r["a"], r["b"]) for r in rows), reverse=desc)
+        assert list(zip(s["a"].to_pylist(), s["b"].to_pylist())) == exp
+
+
+def test_empty_block_contract():
+    # test_sort.py:186-234
+    e = pa.table({"a": pa.array([], pa.int64())})
+    parts = O.sort_and_partition(e, [(1,), (2,)], ["a"], [False])
+    assert len(parts) == 3 and all(p.num_rows == 0 and p.num_columns == 0 for p in parts)
+    assert O.merge_sorted_blocks([e, e], ["a"], [False]).num_rows == 0
+    assert O.boundaries_from_samples([], [False], 4) == [None, None, None]
+
+
+def test_sort_is_stable_and_nulls_last_both_directions():
+    t = pa.table({"k": pa.array([3, None, 1, float("nan"), 2, None, float("nan")]),
+                  "i": list(range(7))})
+    assert O.sort_table(t, ["k"], [False])["i"].to_pylist() == [2, 4, 0, 3, 6, 1, 5]
+    assert O.sort_table(t, ["k"], [True])["i"].to_pylist() == [0, 4, 2, 3, 6, 1, 5]
+
+
+# ---- 2. reference-generated fixtures ----------------------------------------
+
+@pytest.mark.parametrize("case", G.cases("sort"), ids=lambda c: c["name"])
+def test_golden_sort(case):
+    blocks = [G.load(n) for n in case["inputs"]]
+    b = G.boundaries(case)
+    for i, blk in enumerate(blocks):
+        parts = O.sort_and_partition(blk, b, case["columns"], case["descending"])
+        assert len(parts) == len(case["map_outputs"][i])
+        for p, name in zip(parts, case["map_outputs"][i]):
+            assert G.tables_equal(p, G.load(name)), name
+    outs = O.sort_exchange(blocks, b, case["columns"], case["descending"])
+    for o, name in zip(outs, case["outputs"]):
+        assert G.tables_equal(o, G.load(name)), name
+
+
+@pytest.mark.parametrize("case", G.cases("shuffle"), ids=lambda c: c["name"])
+def test_golden_shuffle(case):
+    blocks = [G.load(n) for n in case["inputs"]]
+    outs = O.shuffle_exchange(blocks, case["num_outputs"], case["seed"])
+    for o, name in zip(outs, case["outputs"]):
+        assert G.tables_equal(o, G.load(name)), name
+
+
+@pytest.mark.parametrize("case", G.cases("aggregate"), ids=lambda c: c["name"])
+def test_golden_aggregate(case):
+    blocks = [G.load(n) for n in case["inputs"]]
+    got = O.groupby_aggregate(blocks, case["key"], [tuple(a) for a in case["aggs"]])
+    exp = pa.concat_tables([t for t in (G.load(n) for n in case["outputs"]) if t.num_rows])
+    assert got.schema.names == exp.schema.names
+    for n in exp.schema.names:
+        assert got[n].type == exp[n].type, n
+        a, b = exp[n].to_numpy(), got[n].to_numpy()
+        np.testing.assert_allclose(b, a, rtol=1e-12, atol=1e-12, equal_nan=True, err_msg=n)
+
+
+# ---- 3. live reference (build container only) ---------------------------------
+
+needs_ref = pytest.mark.skipif(not ref_shim.available(), reason="/root/reference absent")
+
+
+@needs_ref
+def test_live_reference_sort_random():
+    R = ref_shim.load()
+    rng = np.random.default_rng(5)
+    for trial in range(4):
+        blocks = [pa.table({"k": rng.integers(-50, 50, n), "f": rng.standard_normal(n),
+                            "s": pa.array([str(x) for x in rng.integers(0, 30, n)])})
+                  for n in (300, 0, 211)]
+        blocks[1] = blocks[0].slice(0, 0)
+        desc = [bool(trial & 1), bool(trial & 2)]
+        cols = ["k", "s"]
+        b = sorted([(int(rng.integers(-50, 50)), str(int(rng.integers(0, 30)))) for _ in range(3)],
+                   reverse=desc[0])
+        sk = R.SortKey(key=cols, descending=desc)
+        maps = [R.SortTaskSpec.map(i, x, 4, b, sk) for i, x in enumerate(blocks)]
+        ref = [R.SortTaskSpec.reduce(sk, "default", *[m[j] for m in maps])[0] for j in range(4)]
+        mine = O.sort_exchange(blocks, b, cols, desc)
+        for r, m in zip(ref, mine):
+            assert G.tables_equal(r, m)
+
+
+@needs_ref
+def test_live_reference_boundaries_from_samples():
+    R = ref_shim.load()
+    rng = np.random.default_rng(6)
+    samples = [(int(a), float(b)) for a, b in zip(rng.integers(0, 5, 40), rng.standard_normal(40))]
+    samples[3] = (samples[3][0], float("nan"))
+    # restate sort_task_spec.py:200-226 by running its own statements
+    for desc in ([False, False], [True, False], [False, True]):
+        exp = list(samples)
+        for i, d in list(enumerate(desc))[::-1]:
+            exp.sort(key=lambda s, i=i: R.NULL_SENTINEL if (s[i] is None or s[i] != s[i]) else s[i],
+                     reverse=d)
+        q = [int(x * (len(exp) - 1)) for x in np.linspace(0, 1, 6)]
+        exp = [exp[i] for i in q[1:-1]]
+        got = O.boundaries_from_samples(samples, desc, 5)
+        assert [tuple(map(repr, g)) for g in got] == [tuple(map(repr, e)) for e in exp]
