@@ -1,0 +1,184 @@
+"""``B200ArrowBlockAccessor``: the reference's Arrow block operations, on the GPU.
+
+Mirrors the exchange-relevant part of ``ArrowBlockAccessor``
+(python/ray/data/_internal/arrow_block.py:219-663) method for method -- same
+names, arguments, return shapes and empty-block contract -- with every
+arithmetic step (``sort_indices``, ``take``, ``searchsorted``, ``permutation``,
+the per-group aggregate loops) replaced by sm_100a kernels behind the C-ABI.
+Host Arrow tables go in, host Arrow tables come out (staging + kernels + copy
+back per call); the device-resident, multi-block path is
+``cluster_anywhere_b200.exchange.DeviceExchange``.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+import pyarrow as pa
+import torch
+
+from . import device as dev
+from . import keys as keymod
+from .block import BlockExecStats, BlockMetadata, empty_table
+from .sort_key import SortKey
+
+
+def _device_sort(rt: dev.Runtime, dt: dev.DeviceTable, sort_key: SortKey, want_norm: bool):
+    return dev.sort_permutation(rt, dt, sort_key.get_columns(), sort_key.get_descending(), want_norm)
+
+
+def _cuts_for(rt: dev.Runtime, dt: dev.DeviceTable, norms, boundaries, sort_key: SortKey) -> List[int]:
+    cols, desc = sort_key.get_columns(), sort_key.get_descending()
+    ktypes = [dev.key_type_of(dt.column(c).type) for c in cols]
+    lower, upper, flags = keymod.normalize_boundaries(boundaries, ktypes, desc)
+    thr = [keymod.last_class_threshold(k, dt.column(c).null_count) for k, c in zip(ktypes, cols)]
+    return dev.partition_cuts(rt, norms, dt.num_rows, lower, upper, flags, desc,
+                              [t[0] for t in thr], [t[1] for t in thr])
+
+
+class B200ArrowBlockAccessor:
+    def __init__(self, table: pa.Table, runtime: Optional[dev.Runtime] = None):
+        if not isinstance(table, pa.Table):
+            raise TypeError(f"B200ArrowBlockAccessor needs a pyarrow.Table, got {type(table)}")
+        self._table = table
+        self._rt = runtime
+
+    # -- plumbing ------------------------------------------------------------
+    @staticmethod
+    def for_block(block, runtime: Optional[dev.Runtime] = None) -> "B200ArrowBlockAccessor":
+        """python/ray/data/block.py:446-473 (Arrow branch only; pandas blocks are
+        converted by the caller)."""
+        if isinstance(block, B200ArrowBlockAccessor):
+            return block
+        try:
+            import pandas as pd
+
+            if isinstance(block, pd.DataFrame):
+                block = pa.Table.from_pandas(block, preserve_index=False)
+        except ImportError:
+            pass
+        return B200ArrowBlockAccessor(block, runtime)
+
+    @property
+    def rt(self) -> dev.Runtime:
+        if self._rt is None:
+            self._rt = dev.default_runtime()
+        return self._rt
+
+    def to_arrow(self) -> pa.Table:
+        return self._table
+
+    def to_block(self) -> pa.Table:
+        return self._table
+
+    def num_rows(self) -> int:
+        # arrow_block.py:286-289: a 0-column table counts as empty
+        return self._table.num_rows if self._table.num_columns > 0 else 0
+
+    def size_bytes(self) -> int:
+        return self._table.nbytes
+
+    def schema(self) -> pa.Schema:
+        return self._table.schema
+
+    def get_metadata(self, input_files=None, exec_stats: Optional[BlockExecStats] = None) -> BlockMetadata:
+        return BlockMetadata(self.num_rows(), self.size_bytes(), self.schema(), input_files, exec_stats)
+
+    @staticmethod
+    def _empty_table() -> pa.Table:
+        return empty_table()
+
+    def slice(self, start: int, end: int, copy: bool = False) -> pa.Table:
+        """arrow_block.py:219-223 (zero-copy view; ``copy`` compacts)."""
+        view = self._table.slice(start, max(0, end - start))
+        return view.combine_chunks() if copy else view
+
+    def select(self, columns: List[str]) -> pa.Table:
+        if not all(isinstance(c, str) for c in columns):
+            raise ValueError(
+                "Columns must be a list of column name strings when aggregating on "
+                f"Arrow blocks, but got: {columns}."
+            )
+        return self._table.select(columns)
+
+    # -- take / sample / shuffle ---------------------------------------------
+    def take(self, indices) -> pa.Table:
+        """Row gather on the GPU (arrow_block.py:319-328 -> transform_pyarrow.py:45-71)."""
+        idx = np.ascontiguousarray(np.asarray(indices), dtype=np.int64)
+        n = self.num_rows()
+        if idx.size and (idx.min() < 0 or idx.max() >= n):
+            raise IndexError("take index out of bounds")
+        rt = self.rt
+        dt = dev.stage_table(rt, self._table)
+        idx_d = rt.empty(idx.size, torch.int32)
+        dev._h2d(idx_d.view(torch.uint8), idx.astype(np.uint32).view(np.uint8))
+        out = dev.take_table(rt, dt, idx_d, idx.size)
+        return dev.export_table(rt, out)
+
+    def sample(self, n_samples: int, sort_key: SortKey) -> pa.Table:
+        """Key columns of ``n_samples`` random rows (table_block.py:253-264,
+        arrow_block.py:341-344).  The reference samples with an unseeded
+        ``random.sample``; so does this (the draw is host-side, the gather is K5)."""
+        import random
+
+        if sort_key is None or callable(sort_key):
+            raise NotImplementedError(f"Table sort key must be a column name, was: {sort_key}")
+        if self.num_rows() == 0:
+            return self._empty_table()
+        k = min(n_samples, self.num_rows())
+        indices = random.sample(range(self.num_rows()), k)
+        keys_only = B200ArrowBlockAccessor(self._table.select(sort_key.get_columns()), self._rt)
+        return keys_only.take(indices)
+
+    # -- sort ------------------------------------------------------------------
+    def sort(self, sort_key: SortKey) -> pa.Table:
+        """arrow_block.py:425-438."""
+        assert sort_key.get_columns(), (
+            f"Sorting columns couldn't be empty (got {sort_key.get_columns()})"
+        )
+        if self._table.num_rows == 0:
+            return self._empty_table()
+        sort_key.validate_schema(self._table.schema)
+        rt = self.rt
+        dt = dev.stage_table(rt, self._table)
+        perm, _ = _device_sort(rt, dt, sort_key, False)
+        return dev.export_table(rt, dev.take_table(rt, dt, perm, dt.num_rows))
+
+    def sort_and_partition(self, boundaries: List[tuple], sort_key: SortKey) -> List[pa.Table]:
+        """arrow_block.py:440-450: sort, then ``len(boundaries)+1`` range partitions
+        (util.py:806-828).  One staging, one sort, one gather, one copy back; the
+        partitions are zero-copy slices of the sorted table, as in the reference."""
+        assert sort_key.get_columns()
+        if self._table.num_rows == 0:
+            return [self._empty_table() for _ in range(len(boundaries) + 1)]
+        sort_key.validate_schema(self._table.schema)
+        rt = self.rt
+        dt = dev.stage_table(rt, self._table)
+        want = len(boundaries) > 0
+        perm, norms = _device_sort(rt, dt, sort_key, want)
+        sorted_dt = dev.take_table(rt, dt, perm, dt.num_rows)
+        if not want:
+            return [dev.export_table(rt, sorted_dt)]
+        cuts = _cuts_for(rt, dt, norms, boundaries, sort_key)
+        table = dev.export_table(rt, sorted_dt)
+        out, last = [], 0
+        for c in cuts:
+            out.append(table[last:c])  # util.py:823-827 slices exactly like this
+            last = c
+        out.append(table[last:])
+        return out
+
+    @staticmethod
+    def merge_sorted_blocks(blocks: List[pa.Table], sort_key: SortKey,
+                            runtime: Optional[dev.Runtime] = None) -> Tuple[pa.Table, BlockMetadata]:
+        """arrow_block.py:529-541 -> transform_pyarrow.py:540-547: drop empty runs,
+        concatenate in mapper order (schemas unified with type promotion), stable
+        re-sort.  Ties therefore resolve by (mapper index, position in run)."""
+        stats = BlockExecStats.builder()
+        blocks = [b for b in blocks if b.num_rows > 0]
+        if len(blocks) == 0:
+            ret = empty_table()
+        else:
+            t = pa.concat_tables(blocks, promote_options="permissive")
+            ret = B200ArrowBlockAccessor(t, runtime).sort(sort_key)
+        return ret, B200ArrowBlockAccessor(ret, runtime).get_metadata(exec_stats=stats.build())

@@ -1,0 +1,138 @@
+// K4: boundary search on sorted, normalised key columns -> partition cut indices.
+//
+// Replaces find_partition_index / find_partitions
+// (python/ray/data/_internal/util.py:728-828).  The reference runs, per boundary
+// and per key column, two numpy.searchsorted calls (left/right; descending columns
+// through a reversing sorter) after an O(N) `col == None` scan; here all key
+// columns are already order-preserving unsigned radix keys sorted ascending, so
+// every column -- whatever its direction -- is one lower_bound and one upper_bound
+// inside the run left by the previous column.  One thread per boundary: the work
+// is O(nb * ncols * log n) dependent loads, nowhere near any roofline.
+#include "common.cuh"
+
+namespace {
+
+constexpr int MAX_KEY_COLS = 8;
+struct ColPtrs {
+  const uint64_t* c[MAX_KEY_COLS];
+  uint64_t last_thr[MAX_KEY_COLS];  // keys >= this are NaN / null ("last" class)
+  uint8_t desc[MAX_KEY_COLS];       // column direction
+  uint8_t has_last[MAX_KEY_COLS];   // column may hold NaN / null rows
+};
+
+__device__ __forceinline__ uint64_t lower_bound_u64(const uint64_t* __restrict__ a, uint64_t lo,
+                                                    uint64_t hi, uint64_t v) {
+  while (lo < hi) {
+    const uint64_t mid = lo + ((hi - lo) >> 1);
+    if (a[mid] < v) lo = mid + 1;
+    else hi = mid;
+  }
+  return lo;
+}
+__device__ __forceinline__ uint64_t upper_bound_u64(const uint64_t* __restrict__ a, uint64_t lo,
+                                                    uint64_t hi, uint64_t v) {
+  while (lo < hi) {
+    const uint64_t mid = lo + ((hi - lo) >> 1);
+    if (a[mid] <= v) lo = mid + 1;
+    else hi = mid;
+  }
+  return lo;
+}
+
+__global__ void k_partition_bounds(ColPtrs cols, int ncols, uint64_t n,
+                                   const uint64_t* __restrict__ lower,
+                                   const uint64_t* __restrict__ upper,
+                                   const uint8_t* __restrict__ flags, int nb, int first_desc,
+                                   uint64_t* __restrict__ cuts) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nb) return;
+  uint64_t lo = 0, hi = n;
+  bool early = false;
+  for (int c = 0; c < ncols; ++c) {
+    if (lo == hi) {  // util.py:757-758: `if left == right: return right`
+      early = true;
+      break;
+    }
+    const int e = b * ncols + c;
+    const uint8_t f = flags ? flags[e] : 0;
+    if (f & 2) break;  // boundary tuple shorter than the key list
+    if (f & 4) {       // boundary sorts after every row of the current run (None boundary)
+      lo = hi;
+      continue;
+    }
+    const uint64_t L = lower[e], U = upper[e];
+    if (!cols.desc[c]) {
+      // ascending: numpy's order (numbers, then NaN) agrees with the stored order
+      const uint64_t l2 = lower_bound_u64(cols.c[c], lo, hi, L);
+      const uint64_t h2 = (f & 1) ? l2 : upper_bound_u64(cols.c[c], lo, hi, U);
+      lo = l2;
+      hi = h2;
+    } else {
+      // descending: the reference searches a REVERSED view with numpy.searchsorted
+      // (util.py:775-799).  NaN / null rows sit at the end of the stored order, i.e.
+      // at the FRONT of that view, where numpy's NaN-last comparator does not
+      // expect them; the outcome then depends on the probe sequence.  Reproduce
+      // numpy's binary search probe by probe so the cut points stay bit-exact.
+      const uint64_t* a = cols.c[c];
+      const uint64_t m = hi > lo ? hi - lo : 0;
+      const uint64_t thr = cols.last_thr[c];
+      const bool has_last = cols.has_last[c] != 0;
+      const bool key_last = (f & 8) != 0;  // NaN boundary
+      uint64_t mn = 0, mx = m;
+      while (mn < mx) {  // side='left': advance while arr < key
+        const uint64_t mid = mn + ((mx - mn) >> 1);
+        const uint64_t k = a[hi - 1 - mid];
+        const bool el = has_last && k >= thr;
+        const bool before_eq = (f & 1) ? (k < L) : (k <= U);  // arr >= key (value space)
+        const bool lt = key_last ? !el : (!el && !before_eq);
+        if (lt) mn = mid + 1;
+        else mx = mid;
+      }
+      const uint64_t left_idx = mn;
+      mn = 0;
+      mx = m;
+      while (mn < mx) {  // side='right': advance while arr <= key
+        const uint64_t mid = mn + ((mx - mn) >> 1);
+        const uint64_t k = a[hi - 1 - mid];
+        const bool el = has_last && k >= thr;
+        const bool before = k < L;  // arr > key (value space)
+        const bool key_lt_arr = !key_last && (el || before);
+        if (!key_lt_arr) mn = mid + 1;
+        else mx = mid;
+      }
+      const uint64_t right_idx = mn;
+      const uint64_t base = lo;
+      lo = base + (m - right_idx);
+      hi = base + (m - left_idx);
+    }
+  }
+  cuts[b] = early ? hi : (first_desc ? hi : lo);
+}
+
+}  // namespace
+
+extern "C" int xchg_partition_bounds(const uint64_t* const* norm_cols_host,
+                                     const uint8_t* col_desc_host,
+                                     const uint64_t* last_threshold_host,
+                                     const uint8_t* has_last_host, int ncols, uint64_t n,
+                                     const uint64_t* lower, const uint64_t* upper,
+                                     const uint8_t* flags, int nb, int first_descending,
+                                     uint64_t* cuts_out, void* stream) {
+  if (nb == 0) return XCHG_OK;
+  XCHG_REQUIRE(norm_cols_host && col_desc_host && last_threshold_host && has_last_host && lower &&
+                   upper && cuts_out,
+               "NULL argument");
+  XCHG_REQUIRE(ncols >= 1 && ncols <= MAX_KEY_COLS, "ncols must be in [1, %d]", MAX_KEY_COLS);
+  ColPtrs cp;
+  for (int c = 0; c < MAX_KEY_COLS; ++c) {
+    cp.c[c] = c < ncols ? norm_cols_host[c] : nullptr;
+    cp.last_thr[c] = c < ncols ? last_threshold_host[c] : ~0ull;
+    cp.desc[c] = c < ncols ? col_desc_host[c] : 0;
+    cp.has_last[c] = c < ncols ? has_last_host[c] : 0;
+  }
+  for (int c = 0; c < ncols; ++c) XCHG_REQUIRE(n == 0 || cp.c[c], "NULL key column %d", c);
+  k_partition_bounds<<<(nb + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+      cp, ncols, n, lower, upper, flags, nb, first_descending, cuts_out);
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}

@@ -1,0 +1,494 @@
+// K2 (key normalisation + digit histograms) and K3 (stable onesweep LSD radix sort
+// of 64-bit radix keys with 32-bit row ids) for sm_100a.
+//
+// Replaces pyarrow.compute.sort_indices as the reference calls it from
+// python/ray/data/_internal/arrow_ops/transform_pyarrow.py:41 and :546.
+//
+// Data layout in HBM: SoA -- one u64 normalised key array and one u32 row-id
+// array, ping-ponged between two buffer sets; 8-bit digits, only the digit places
+// whose histogram has more than one non-empty bin are run (range(10M) in int64
+// costs 3 passes, random 63-bit keys 8).  Every pass is ONE kernel: each CTA takes
+// an 8192-row tile (dynamic tile id), ranks it with warp match_any, publishes its
+// per-digit counts and resolves its global offsets by decoupled look-back, stages
+// the tile in shared memory in digit order and writes it out in coalesced runs.
+// Algorithmic bytes per pass: 24 B/row (12 read + 12 written).
+#include <algorithm>
+#include <type_traits>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int BINS = 256;
+constexpr int KEY_PLACES = 8;
+constexpr int NUM_PLACES = 9;  // 8 key digit places + the validity place
+constexpr int RS_THREADS = 512;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_ITEMS = 16;
+constexpr int RS_TILE = RS_THREADS * RS_ITEMS;  // 8192 rows
+constexpr size_t RS_SMEM = (size_t)RS_TILE * 12 + (BINS + BINS + 32) * 4;
+
+constexpr uint32_t FLAG_MASK = 3u << 30;
+constexpr uint32_t FLAG_LOCAL = 1u << 30;
+constexpr uint32_t FLAG_INCL = 2u << 30;
+constexpr uint32_t VAL_MASK = (1u << 30) - 1;
+
+// ------------------------------------------------------------------ K2 -----
+
+template <typename T>
+__device__ __forceinline__ uint64_t norm_value(T x, bool desc) {
+  if constexpr (std::is_same<T, float>::value) {
+    if (x != x) return 0xFFFFFFFEull;  // NaN after every number, both directions
+    uint32_t b = __float_as_uint(x);
+    if (x == 0.0f) b = 0;  // -0.0 ties with +0.0 (Arrow compares numerically)
+    uint32_t t = (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+    if (desc) t = ~t;
+    return (uint64_t)t;
+  } else if constexpr (std::is_same<T, double>::value) {
+    if (x != x) return 0xFFFFFFFFFFFFFFFEull;
+    uint64_t b = (uint64_t)__double_as_longlong(x);
+    if (x == 0.0) b = 0;
+    uint64_t t = (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+    if (desc) t = ~t;
+    return t;
+  } else {
+    using U = typename std::make_unsigned<T>::type;
+    U u = (U)x;
+    if constexpr (std::is_signed<T>::value) u ^= (U)((U)1 << (sizeof(T) * 8 - 1));
+    if (desc) u = (U)~u;
+    return (uint64_t)u;
+  }
+}
+
+// Key of a null row: one past the largest key a value can take (nulls last in both
+// directions).  64-bit integers have no spare value: they use UINT64_MAX and the
+// sort appends a 9th, validity-driven pass.
+template <typename T>
+__device__ __forceinline__ uint64_t null_key() {
+  if constexpr (std::is_same<T, float>::value) return 0xFFFFFFFFull;
+  else if constexpr (sizeof(T) == 8) return 0xFFFFFFFFFFFFFFFFull;
+  else return 1ull << (sizeof(T) * 8);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_normalize_hist(const T* __restrict__ keys, const uint32_t* __restrict__ perm,
+                 const uint8_t* __restrict__ validity, int64_t vbit, uint32_t n, int desc,
+                 uint64_t* __restrict__ out, uint32_t* __restrict__ ghist) {
+  __shared__ uint32_t sh[NUM_PLACES * BINS];
+  if (ghist) {
+    for (int j = threadIdx.x; j < NUM_PLACES * BINS; j += blockDim.x) sh[j] = 0;
+    __syncthreads();
+  }
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t stride = gridDim.x * blockDim.x;
+  const uint32_t n_up = (n + 31u) & ~31u;  // whole warps stay in the loop for the votes
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_up; i += stride) {
+    const bool active = i < n;
+    uint64_t key = 0;
+    bool valid = true;
+    if (active) {
+      const uint32_t row = perm ? perm[i] : i;
+      valid = validity ? bit_is_set(validity, (int64_t)row + vbit) : true;
+      key = valid ? norm_value<T>(keys[row], desc != 0) : null_key<T>();
+      out[i] = key;
+    }
+    if (ghist) {
+      const unsigned act = __ballot_sync(0xffffffffu, active);
+      const int first = __ffs(act) - 1;
+#pragma unroll
+      for (int p = 0; p < NUM_PLACES; ++p) {
+        const uint32_t d = (p < KEY_PLACES) ? (uint32_t)(key >> (8 * p)) & 255u : (valid ? 0u : 1u);
+        const uint32_t d0 = __shfl_sync(0xffffffffu, d, first);
+        const bool uni = __all_sync(0xffffffffu, !active || d == d0);
+        if (uni) {
+          if ((int)lane == first) atomicAdd(&sh[p * BINS + d0], (uint32_t)__popc(act));
+        } else if (active) {
+          atomicAdd(&sh[p * BINS + d], 1u);
+        }
+      }
+    }
+  }
+  if (ghist) {
+    __syncthreads();
+    for (int j = threadIdx.x; j < NUM_PLACES * BINS; j += blockDim.x)
+      if (sh[j]) atomicAdd(&ghist[j], sh[j]);
+  }
+}
+
+// One CTA: exclusive scan of each place's 256-bin histogram and the "place is
+// non-trivial" flags (more than one non-empty bin).
+__global__ void __launch_bounds__(BINS)
+k_scan_hist(const uint32_t* __restrict__ ghist, uint32_t* __restrict__ gexcl,
+            uint32_t* __restrict__ active, uint32_t n) {
+  __shared__ uint32_t wsum[BINS / 32];
+  __shared__ uint32_t s_full;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int p = 0; p < NUM_PLACES; ++p) {
+    if (tid == 0) s_full = 0;
+    __syncthreads();
+    const uint32_t c = ghist[p * BINS + tid];
+    if (c == n) s_full = 1;
+    uint32_t x = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) wsum[warp] = x;
+    __syncthreads();
+    uint32_t base = 0;
+    for (int w = 0; w < warp; ++w) base += wsum[w];
+    gexcl[p * BINS + tid] = base + x - c;
+    if (tid == 0) active[p] = s_full ? 0u : 1u;
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------ K3 -----
+
+template <int MODE>
+__device__ __forceinline__ uint32_t digit_of(uint64_t key, uint32_t val, int shift,
+                                             const uint8_t* validity, int64_t vbit) {
+  if constexpr (MODE == 0) {
+    return (uint32_t)(key >> shift) & 255u;
+  } else {
+    // validity place: valid rows -> bin 0, null rows -> bin 1; padding (val ==
+    // UINT32_MAX) -> bin 255 so that it ranks after every real row.
+    if (val == 0xFFFFFFFFu) return 255u;
+    return bit_is_set(validity, (int64_t)val + vbit) ? 0u : 1u;
+  }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(RS_THREADS, 2)
+k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+           uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, uint32_t n,
+           int shift, const uint32_t* __restrict__ gexcl, uint32_t* status,
+           uint32_t* tile_counter, const uint8_t* __restrict__ validity, int64_t vbit) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  uint64_t* skeys = reinterpret_cast<uint64_t*>(smem);
+  uint32_t* svals = reinterpret_cast<uint32_t*>(smem + (size_t)RS_TILE * 8);
+  uint32_t* whist = reinterpret_cast<uint32_t*>(smem);  // aliases skeys until ranks are final
+  uint32_t* sbase = reinterpret_cast<uint32_t*>(smem + (size_t)RS_TILE * 12);
+  uint32_t* sstart = sbase + BINS;
+  uint32_t* smisc = sstart + BINS;  // [0..7] warp sums of the digit scan, [16] tile id
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+  if (tid == 0) smisc[16] = atomicAdd(tile_counter, 1u);
+  for (int j = tid; j < RS_WARPS * BINS; j += RS_THREADS) whist[j] = 0;
+  __syncthreads();
+  const uint32_t tile = smisc[16];
+  const uint32_t tile_base = tile * (uint32_t)RS_TILE;
+  const uint32_t tile_items = min((uint32_t)RS_TILE, n - tile_base);
+  const uint32_t warp_base = tile_base + warp * (32 * RS_ITEMS) + lane;
+
+  // ---- load (warp-striped: item i of lane l sits at warp_base + 32*i) ----
+  uint64_t key[RS_ITEMS];
+  uint32_t val[RS_ITEMS];  // only live in MODE 1 (the compiler drops it otherwise)
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; ++i) {
+    const uint32_t idx = warp_base + 32 * i;
+    key[i] = idx < n ? keys_in[idx] : 0xFFFFFFFFFFFFFFFFull;
+    if constexpr (MODE == 1) val[i] = idx < n ? (vals_in ? vals_in[idx] : idx) : 0xFFFFFFFFu;
+    else val[i] = 0u;
+  }
+
+  // ---- rank inside the warp, in (i, lane) = memory order: stable ----
+  uint32_t* myhist = whist + warp * BINS;
+  uint32_t rank[RS_ITEMS];
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; ++i) {
+    const uint32_t d = digit_of<MODE>(key[i], val[i], shift, validity, vbit);
+    const unsigned m = __match_any_sync(0xffffffffu, d);
+    const int leader = __ffs(m) - 1;
+    uint32_t prev = 0;
+    if (lane == leader) {
+      prev = myhist[d];
+      myhist[d] = prev + (uint32_t)__popc(m);
+    }
+    prev = __shfl_sync(0xffffffffu, prev, leader);
+    rank[i] = prev + (uint32_t)__popc(m & lanemask_lt());
+    __syncwarp();
+  }
+  __syncthreads();
+
+  // ---- per digit: exclusive offsets across warps, tile totals, digit scan ----
+  uint32_t total = 0, incl = 0;
+  if (tid < BINS) {
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; ++w) {
+      const uint32_t c = whist[w * BINS + tid];
+      whist[w * BINS + tid] = total;
+      total += c;
+    }
+    incl = total;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += y;
+    }
+    if (lane == 31) smisc[warp] = incl;
+  }
+  __syncthreads();
+  if (tid < BINS) {
+    uint32_t start = incl - total;
+    for (int w = 0; w < warp; ++w) start += smisc[w];
+    sstart[tid] = start;
+
+    // decoupled look-back on this digit's column of the tile-status matrix
+    uint32_t cnt = total;
+    if (tid == BINS - 1) cnt -= (uint32_t)RS_TILE - tile_items;  // padding sits in bin 255
+    volatile uint32_t* st = status + (size_t)tile * BINS + tid;
+    uint32_t excl = 0;
+    if (tile == 0) {
+      *st = FLAG_INCL | cnt;
+    } else {
+      *st = FLAG_LOCAL | cnt;
+      int64_t t = (int64_t)tile - 1;
+      while (true) {
+        volatile uint32_t* ps = status + (size_t)t * BINS + tid;
+        uint32_t s;
+        do {
+          s = *ps;
+        } while ((s & FLAG_MASK) == 0);
+        excl += s & VAL_MASK;
+        if (s & FLAG_INCL) break;
+        --t;
+      }
+      *st = FLAG_INCL | (excl + cnt);
+    }
+    sbase[tid] = gexcl[tid] + excl - start;
+  }
+  __syncthreads();
+
+  // ---- final in-tile ranks ----
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; ++i) {
+    const uint32_t d = digit_of<MODE>(key[i], val[i], shift, validity, vbit);
+    rank[i] += myhist[d] + sstart[d];
+  }
+  __syncthreads();  // whist is dead from here: skeys may overwrite it
+
+  // ---- stage the tile in digit order ----
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; ++i) skeys[rank[i]] = key[i];
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; ++i) {
+    uint32_t v;
+    if constexpr (MODE == 1) {
+      v = val[i];
+    } else {
+      const uint32_t idx = warp_base + 32 * i;
+      v = idx < n ? (vals_in ? vals_in[idx] : idx) : 0xFFFFFFFFu;
+    }
+    svals[rank[i]] = v;
+  }
+  __syncthreads();
+
+  // ---- coalesced write-out: consecutive threads, consecutive ranks ----
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; ++i) {
+    const uint32_t pos = i * RS_THREADS + tid;
+    if (pos < tile_items) {
+      const uint64_t k = skeys[pos];
+      const uint32_t v = svals[pos];
+      const uint32_t d = digit_of<MODE>(k, v, shift, validity, vbit);
+      const uint32_t g = sbase[d] + pos;
+      keys_out[g] = k;
+      vals_out[g] = v;
+    }
+  }
+}
+
+__global__ void k_iota_or_copy(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, uint32_t n) {
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = in ? in[i] : i;
+}
+
+struct SortWorkspace {
+  uint64_t* norm;    // N: normalised keys in input order
+  uint64_t* keys_b;  // ping-pong side B
+  uint32_t* vals_b;
+  uint64_t* keys_a;  // side A keys when the caller does not want them
+  uint32_t* ghist;   // NUM_PLACES * BINS
+  uint32_t* gexcl;   // NUM_PLACES * BINS
+  uint32_t* active;  // NUM_PLACES (+ padding)
+  uint32_t* tile_counter;  // 16
+  uint32_t* status;  // ntiles * BINS
+  uint64_t total;
+};
+
+SortWorkspace carve(void* base, uint64_t n) {
+  SortWorkspace w;
+  uint64_t off = 0;
+  auto take = [&](uint64_t bytes) {
+    uint64_t o = off;
+    off = xchg_align_up(off + bytes, 256);
+    return (uint8_t*)base + o;
+  };
+  const uint64_t ntiles = (n + RS_TILE - 1) / RS_TILE;
+  w.norm = (uint64_t*)take(n * 8);
+  w.keys_b = (uint64_t*)take(n * 8);
+  w.keys_a = (uint64_t*)take(n * 8);
+  w.vals_b = (uint32_t*)take(n * 4);
+  w.ghist = (uint32_t*)take(NUM_PLACES * BINS * 4);
+  w.gexcl = (uint32_t*)take(NUM_PLACES * BINS * 4);
+  w.active = (uint32_t*)take(64);
+  w.tile_counter = (uint32_t*)take(64);
+  w.status = (uint32_t*)take(ntiles * BINS * 4);
+  w.total = off;
+  return w;
+}
+
+template <typename T>
+void launch_normalize(const void* keys, const uint32_t* perm, const uint8_t* validity, int64_t vbit,
+                      uint32_t n, int desc, uint64_t* out, uint32_t* ghist, cudaStream_t s) {
+  int blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)xchg_sm_count() * 8);
+  k_normalize_hist<T><<<blocks, 256, 0, s>>>((const T*)keys, perm, validity, vbit, n, desc, out, ghist);
+}
+
+int dispatch_normalize(const void* keys, int key_type, const uint32_t* perm, const uint8_t* validity,
+                       int64_t vbit, uint32_t n, int desc, uint64_t* out, uint32_t* ghist,
+                       cudaStream_t s) {
+  switch (key_type) {
+    case XCHG_I8: launch_normalize<int8_t>(keys, perm, validity, vbit, n, desc, out, ghist, s); break;
+    case XCHG_I16: launch_normalize<int16_t>(keys, perm, validity, vbit, n, desc, out, ghist, s); break;
+    case XCHG_I32: launch_normalize<int32_t>(keys, perm, validity, vbit, n, desc, out, ghist, s); break;
+    case XCHG_I64: launch_normalize<int64_t>(keys, perm, validity, vbit, n, desc, out, ghist, s); break;
+    case XCHG_U8: launch_normalize<uint8_t>(keys, perm, validity, vbit, n, desc, out, ghist, s); break;
+    case XCHG_U16: launch_normalize<uint16_t>(keys, perm, validity, vbit, n, desc, out, ghist, s); break;
+    case XCHG_U32: launch_normalize<uint32_t>(keys, perm, validity, vbit, n, desc, out, ghist, s); break;
+    case XCHG_U64: launch_normalize<uint64_t>(keys, perm, validity, vbit, n, desc, out, ghist, s); break;
+    case XCHG_F32: launch_normalize<float>(keys, perm, validity, vbit, n, desc, out, ghist, s); break;
+    case XCHG_F64: launch_normalize<double>(keys, perm, validity, vbit, n, desc, out, ghist, s); break;
+    default:
+      xchg_set_error("unknown key_type %d", key_type);
+      return XCHG_ERR_INVALID;
+  }
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+}  // namespace
+
+// Shared with the no-workspace variants: sorts already-normalised keys.
+int xchg_internal_onesweep_pass(int mode, const uint64_t* kin, const uint32_t* vin, uint64_t* kout,
+                                uint32_t* vout, uint32_t n, int shift, const uint32_t* gexcl,
+                                uint32_t* status, uint32_t* tile_counter, const uint8_t* validity,
+                                int64_t vbit, cudaStream_t s) {
+  static bool attr_done[2] = {false, false};
+  const uint32_t ntiles = (n + RS_TILE - 1) / RS_TILE;
+  if (mode == 0) {
+    if (!attr_done[0]) {
+      XCHG_CUDA_TRY(cudaFuncSetAttribute(k_onesweep<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)RS_SMEM));
+      attr_done[0] = true;
+    }
+    k_onesweep<0><<<ntiles, RS_THREADS, RS_SMEM, s>>>(kin, vin, kout, vout, n, shift, gexcl, status,
+                                                      tile_counter, validity, vbit);
+  } else {
+    if (!attr_done[1]) {
+      XCHG_CUDA_TRY(cudaFuncSetAttribute(k_onesweep<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)RS_SMEM));
+      attr_done[1] = true;
+    }
+    k_onesweep<1><<<ntiles, RS_THREADS, RS_SMEM, s>>>(kin, vin, kout, vout, n, shift, gexcl, status,
+                                                      tile_counter, validity, vbit);
+  }
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+extern "C" int xchg_sort_workspace_bytes(uint64_t n, uint64_t* bytes_out) {
+  XCHG_REQUIRE(bytes_out != nullptr, "bytes_out is NULL");
+  if (n > XCHG_MAX_ROWS) {
+    xchg_set_error("n=%llu exceeds XCHG_MAX_ROWS", (unsigned long long)n);
+    return XCHG_ERR_LIMIT;
+  }
+  *bytes_out = carve(nullptr, n).total + 256;
+  return XCHG_OK;
+}
+
+extern "C" int xchg_normalize_keys(const void* keys, int key_type, int descending,
+                                   const uint8_t* validity, int64_t validity_bit_offset,
+                                   const uint32_t* perm, uint64_t n, uint64_t* norm_out,
+                                   void* stream) {
+  if (n == 0) return XCHG_OK;
+  XCHG_REQUIRE(keys && norm_out, "NULL keys / norm_out");
+  if (n > XCHG_MAX_ROWS) {
+    xchg_set_error("n=%llu exceeds XCHG_MAX_ROWS", (unsigned long long)n);
+    return XCHG_ERR_LIMIT;
+  }
+  return dispatch_normalize(keys, key_type, perm, validity, validity_bit_offset, (uint32_t)n,
+                            descending, norm_out, nullptr, (cudaStream_t)stream);
+}
+
+extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
+                                const uint8_t* validity, int64_t validity_bit_offset,
+                                const uint32_t* perm_in, uint64_t n, uint32_t* perm_out,
+                                uint64_t* norm_keys_out, void* workspace, uint64_t workspace_bytes,
+                                void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  if (n == 0) return XCHG_OK;
+  XCHG_REQUIRE(keys && perm_out && workspace, "NULL keys / perm_out / workspace");
+  if (n > XCHG_MAX_ROWS) {
+    xchg_set_error("n=%llu exceeds XCHG_MAX_ROWS", (unsigned long long)n);
+    return XCHG_ERR_LIMIT;
+  }
+  uint8_t* base = (uint8_t*)xchg_align_up((uint64_t)(uintptr_t)workspace, 256);
+  SortWorkspace w = carve(base, n);
+  if ((uint64_t)(base - (uint8_t*)workspace) + w.total > workspace_bytes) {
+    xchg_set_error("sort workspace too small: have %llu, need %llu",
+                   (unsigned long long)workspace_bytes, (unsigned long long)(w.total + 256));
+    return XCHG_ERR_WORKSPACE;
+  }
+  const uint32_t n32 = (uint32_t)n;
+  const uint32_t ntiles = (n32 + RS_TILE - 1) / RS_TILE;
+
+  XCHG_CUDA_TRY(cudaMemsetAsync(w.ghist, 0, NUM_PLACES * BINS * 4, s));
+  int rc = dispatch_normalize(keys, key_type, perm_in, validity, validity_bit_offset, n32, descending,
+                              w.norm, w.ghist, s);
+  if (rc) return rc;
+  k_scan_hist<<<1, BINS, 0, s>>>(w.ghist, w.gexcl, w.active, n32);
+  XCHG_LAUNCH_CHECK();
+  uint32_t active[NUM_PLACES];
+  XCHG_CUDA_TRY(cudaMemcpyAsync(active, w.active, sizeof(active), cudaMemcpyDeviceToHost, s));
+  XCHG_CUDA_TRY(cudaStreamSynchronize(s));
+
+  int places[NUM_PLACES];
+  int np = 0;
+  for (int p = 0; p < KEY_PLACES; ++p)
+    if (active[p]) places[np++] = p;
+  const bool wide_int = key_type == XCHG_I64 || key_type == XCHG_U64;
+  if (wide_int && validity && active[KEY_PLACES]) places[np++] = KEY_PLACES;
+
+  uint64_t* keys_a = norm_keys_out ? norm_keys_out : w.keys_a;
+  if (np == 0) {
+    // every key equal: the stable order is the input order
+    int blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)xchg_sm_count() * 8);
+    k_iota_or_copy<<<blocks, 256, 0, s>>>(perm_in, perm_out, n32);
+    XCHG_LAUNCH_CHECK();
+    if (norm_keys_out)
+      XCHG_CUDA_TRY(cudaMemcpyAsync(norm_keys_out, w.norm, n * 8, cudaMemcpyDeviceToDevice, s));
+    return XCHG_OK;
+  }
+  const uint64_t* kin = w.norm;
+  const uint32_t* vin = perm_in;
+  for (int j = 0; j < np; ++j) {
+    const bool to_a = ((np - 1 - j) % 2) == 0;  // the last pass lands on side A
+    uint64_t* kout = to_a ? keys_a : w.keys_b;
+    uint32_t* vout = to_a ? perm_out : w.vals_b;
+    const int p = places[j];
+    XCHG_CUDA_TRY(cudaMemsetAsync(w.tile_counter, 0, 64, s));
+    XCHG_CUDA_TRY(cudaMemsetAsync(w.status, 0, (size_t)ntiles * BINS * 4, s));
+    rc = xchg_internal_onesweep_pass(p == KEY_PLACES ? 1 : 0, kin, vin, kout, vout, n32, 8 * p,
+                                     w.gexcl + p * BINS, w.status, w.tile_counter, validity,
+                                     validity_bit_offset, s);
+    if (rc) return rc;
+    kin = kout;
+    vin = vout;
+  }
+  return XCHG_OK;
+}

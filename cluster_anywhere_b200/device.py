@@ -1,0 +1,561 @@
+"""Arrow <-> HBM staging and thin wrappers over the C-ABI kernels.
+
+PyTorch is used for exactly three things here: device / pinned-host allocation,
+the current CUDA stream, and (in ``exchange/``) ``torch.distributed``.  All
+compute goes through ``libxchg_b200.so``.
+
+Device layout of a column (SoA, one allocation per buffer):
+
+* ``fixed``  -- ``n * width`` value bytes (Arrow primitive / fixed_size_binary /
+  fixed_size_list of primitives), optional validity bitmap.
+* ``bits``   -- Arrow boolean: bit-packed values, optional validity bitmap.
+* ``var``    -- ``int64[n+1]`` absolute BYTE offsets + contiguous value bytes
+  (binary / string / large_* / list<primitive> / tensor extension storage).  The
+  reference's int32 offsets are widened on the way in and narrowed on the way
+  out, so a device column may exceed 2 GiB while each exported Arrow chunk obeys
+  its offset width.  ``uniform`` records a row width shared by every row
+  (GraySort payloads, tensor rows): such columns are gathered without reading
+  offsets.
+"""
+from __future__ import annotations
+
+import ctypes
+import warnings
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+import pyarrow as pa
+import torch
+
+from . import _cabi
+from ._cabi import XchgError
+
+_PAD = 64  # every device buffer is padded so 16-byte windows / 4-byte words stay in bounds
+
+
+def _vp(t: Optional[torch.Tensor]):
+    if t is None:
+        return None
+    return ctypes.c_void_p(t.data_ptr())
+
+
+class Runtime:
+    """Per-process handle: device, stream and scratch allocation."""
+
+    def __init__(self, device: Optional[torch.device] = None):
+        if device is None:
+            if _cabi._test_double is not None:
+                device = torch.device("cpu")
+            else:
+                if not torch.cuda.is_available() or _cabi.load().xchg_device_count() < 1:
+                    raise XchgError(
+                        "no CUDA device visible: the B200 exchange engine has no CPU fallback"
+                    )
+                device = torch.device("cuda", torch.cuda.current_device())
+        self.device = torch.device(device)
+        self.is_cuda = self.device.type == "cuda"
+        if not self.is_cuda and _cabi._test_double is None:
+            raise XchgError("CPU device requested but the engine has no CPU path")
+        self.launches = 0  # kernels launched through this runtime (bench bookkeeping)
+
+    # -- allocation ---------------------------------------------------------
+    def empty(self, n: int, dtype=torch.uint8) -> torch.Tensor:
+        itemsize = torch.empty(0, dtype=dtype).element_size()
+        pad = (_PAD + itemsize - 1) // itemsize
+        return torch.empty(int(n) + pad, dtype=dtype, device=self.device)[: int(n)]
+
+    def zeros(self, n: int, dtype=torch.uint8) -> torch.Tensor:
+        itemsize = torch.empty(0, dtype=dtype).element_size()
+        pad = (_PAD + itemsize - 1) // itemsize
+        return torch.zeros(int(n) + pad, dtype=dtype, device=self.device)[: int(n)]
+
+    def host_empty(self, n: int, dtype=torch.uint8) -> torch.Tensor:
+        return torch.empty(int(n), dtype=dtype, pin_memory=self.is_cuda)
+
+    @property
+    def stream(self):
+        if not self.is_cuda:
+            return None
+        return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def synchronize(self):
+        if self.is_cuda:
+            torch.cuda.current_stream(self.device).synchronize()
+
+    def call(self, name: str, *args, launches: int = 1):
+        self.launches += launches
+        _cabi.call(name, *args)
+
+
+_default_runtime: Optional[Runtime] = None
+
+
+def default_runtime() -> Runtime:
+    global _default_runtime
+    if _default_runtime is None:
+        _default_runtime = Runtime()
+    return _default_runtime
+
+
+def reset_default_runtime():
+    global _default_runtime
+    _default_runtime = None
+
+
+# ---------------------------------------------------------------------------
+# Column model
+# ---------------------------------------------------------------------------
+
+_KEY_TYPES = {
+    pa.int8(): _cabi.I8, pa.int16(): _cabi.I16, pa.int32(): _cabi.I32, pa.int64(): _cabi.I64,
+    pa.uint8(): _cabi.U8, pa.uint16(): _cabi.U16, pa.uint32(): _cabi.U32, pa.uint64(): _cabi.U64,
+    pa.float32(): _cabi.F32, pa.float64(): _cabi.F64,
+    pa.date32(): _cabi.I32, pa.date64(): _cabi.I64,
+}
+
+
+def key_type_of(t: pa.DataType) -> int:
+    """xchg_key_type of an Arrow type usable as a sort / group key."""
+    if isinstance(t, pa.ExtensionType):
+        t = t.storage_type
+    if t in _KEY_TYPES:
+        return _KEY_TYPES[t]
+    if pa.types.is_timestamp(t) or pa.types.is_time64(t) or pa.types.is_duration(t):
+        return _cabi.I64
+    if pa.types.is_time32(t):
+        return _cabi.I32
+    raise NotImplementedError(
+        f"sort/group key of Arrow type {t} is not supported by the B200 engine yet "
+        "(supported: integers, floats, date/time/timestamp/duration)"
+    )
+
+
+@dataclass
+class DeviceColumn:
+    type: pa.DataType
+    n: int
+    kind: str  # 'fixed' | 'bits' | 'var'
+    width: int  # bytes per row (fixed); bytes per element (var)
+    data: Optional[torch.Tensor]
+    offsets: Optional[torch.Tensor] = None  # int64[n+1], byte offsets (var)
+    validity: Optional[torch.Tensor] = None  # bitmap, bit offset 0
+    null_count: int = 0
+    uniform: Optional[int] = None  # row bytes if every row has the same size (var)
+
+    def nbytes(self) -> int:
+        b = 0 if self.data is None else self.data.numel()
+        if self.offsets is not None:
+            b += self.offsets.numel() * (4 if _var_offset_bits(self.type) == 32 else 8)
+        if self.validity is not None:
+            b += (self.n + 7) // 8
+        return b
+
+
+@dataclass
+class DeviceTable:
+    names: List[str]
+    columns: List[DeviceColumn]
+    num_rows: int
+    schema: pa.Schema
+
+    def column(self, name: str) -> DeviceColumn:
+        return self.columns[self.names.index(name)]
+
+    def nbytes(self) -> int:
+        return sum(c.nbytes() for c in self.columns)
+
+
+def _storage_type(t: pa.DataType) -> pa.DataType:
+    return t.storage_type if isinstance(t, pa.ExtensionType) else t
+
+
+def _var_offset_bits(t: pa.DataType) -> int:
+    t = _storage_type(t)
+    if pa.types.is_large_binary(t) or pa.types.is_large_string(t) or pa.types.is_large_list(t):
+        return 64
+    return 32
+
+
+def _classify(t: pa.DataType):
+    """-> (kind, width) for the storage layout of Arrow type ``t``."""
+    t = _storage_type(t)
+    if pa.types.is_boolean(t):
+        return "bits", 0
+    if pa.types.is_fixed_size_binary(t):
+        return "fixed", t.byte_width
+    if pa.types.is_fixed_size_list(t):
+        child = t.value_type
+        if pa.types.is_primitive(child) and not pa.types.is_boolean(child):
+            return "fixed", t.list_size * (child.bit_width // 8)
+        raise NotImplementedError(f"fixed_size_list of {child} is not supported")
+    if pa.types.is_primitive(t) or pa.types.is_decimal(t):
+        return "fixed", t.bit_width // 8
+    if (pa.types.is_binary(t) or pa.types.is_string(t) or pa.types.is_large_binary(t)
+            or pa.types.is_large_string(t)):
+        return "var", 1
+    if pa.types.is_list(t) or pa.types.is_large_list(t):
+        child = t.value_type
+        if pa.types.is_primitive(child) and not pa.types.is_boolean(child):
+            return "var", child.bit_width // 8
+        raise NotImplementedError(f"list of {child} is not supported")
+    raise NotImplementedError(f"Arrow type {t} is not supported by the B200 engine")
+
+
+def _np_view(buf: pa.Buffer) -> np.ndarray:
+    return np.frombuffer(buf, dtype=np.uint8)
+
+
+def _h2d(dst: torch.Tensor, src: np.ndarray):
+    """Async host->device copy of a uint8 numpy view into a uint8 device tensor."""
+    if src.size == 0:
+        return
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        t = torch.from_numpy(src)
+    dst.copy_(t, non_blocking=True)
+
+
+def _chunk_storage(chunk: pa.Array) -> pa.Array:
+    return chunk.storage if isinstance(chunk, pa.ExtensionArray) else chunk
+
+
+def stage_column(rt: Runtime, col, typ: Optional[pa.DataType] = None) -> DeviceColumn:
+    """Copy one (chunked) Arrow column into HBM."""
+    chunks = col.chunks if isinstance(col, pa.ChunkedArray) else [col]
+    typ = typ or col.type
+    kind, width = _classify(typ)
+    n = sum(len(c) for c in chunks)
+    null_count = sum(c.null_count for c in chunks)
+    chunks = [_chunk_storage(c) for c in chunks if len(c) > 0]
+    lib = rt
+
+    validity = None
+    if null_count:
+        # bit-level concatenation of the chunks' validity bitmaps (host side; the
+        # null path is not the hot path)
+        import pyarrow.compute as pac
+
+        bits = np.concatenate([pac.is_valid(c).to_numpy(zero_copy_only=False) for c in chunks])
+        packed = np.packbits(bits, bitorder="little")
+        validity = rt.zeros((len(packed) + 3) // 4 * 4)
+        _h2d(validity[: len(packed)], packed)
+
+    if kind == "fixed":
+        data = rt.empty(n * width)
+        pos = 0
+        for c in chunks:
+            if pa.types.is_fixed_size_list(c.type):
+                flat = c.flatten()  # respects offset/length
+                if flat.null_count:
+                    raise NotImplementedError("nulls inside fixed_size_list values")
+                buf, start, nb = flat.buffers()[1], flat.offset * (width // c.type.list_size), len(c) * width
+            else:
+                buf, start, nb = c.buffers()[1], c.offset * width, len(c) * width
+            _h2d(data[pos : pos + nb], _np_view(buf)[start : start + nb])
+            pos += nb
+        return DeviceColumn(typ, n, kind, width, data, None, validity, null_count)
+
+    if kind == "bits":
+        import pyarrow.compute as pac
+
+        vals = np.concatenate(
+            [pac.fill_null(c, False).to_numpy(zero_copy_only=False) for c in chunks]
+        ) if chunks else np.zeros(0, dtype=bool)
+        packed = np.packbits(vals, bitorder="little")
+        data = rt.zeros((len(packed) + 3) // 4 * 4)
+        _h2d(data[: len(packed)], packed)
+        return DeviceColumn(typ, n, kind, 0, data, None, validity, null_count)
+
+    # var
+    obits = _var_offset_bits(typ)
+    odt = np.int32 if obits == 32 else np.int64
+    spans = []
+    total = 0
+    for c in chunks:
+        bufs = c.buffers()
+        offs = np.frombuffer(bufs[1], dtype=odt)[c.offset : c.offset + len(c) + 1]
+        if pa.types.is_list(c.type) or pa.types.is_large_list(c.type):
+            child = c.values
+            if child.null_count:
+                raise NotImplementedError("nulls inside list values")
+            vbuf = child.buffers()[1]
+            vbase = child.offset * width
+        else:
+            vbuf = bufs[2]
+            vbase = 0
+        first, last = int(offs[0]), int(offs[-1])
+        nb = (last - first) * width
+        spans.append((offs, vbuf, vbase + first * width, nb, first))
+        total += nb
+    data = rt.empty(total)
+    offsets = rt.empty(n + 1, torch.int64)
+    pos_rows, pos_bytes = 0, 0
+    for offs, vbuf, vstart, nb, first in spans:
+        m = len(offs) - 1
+        if vbuf is not None and nb:
+            _h2d(data[pos_bytes : pos_bytes + nb], _np_view(vbuf)[vstart : vstart + nb])
+        raw = rt.empty((m + 1) * offs.itemsize)
+        _h2d(raw, offs.view(np.uint8))
+        dst = offsets[pos_rows : pos_rows + m + 1]
+        if obits == 32 and width == 1:
+            rt.call("xchg_offsets_widen", _vp(raw), m + 1, pos_bytes, _vp(dst), rt.stream)
+        else:
+            o = raw.view(torch.int32 if obits == 32 else torch.int64).to(torch.int64)
+            dst.copy_((o - first) * width + pos_bytes)
+        pos_rows += m
+        pos_bytes += nb
+    if not spans:
+        offsets.zero_()
+    dc = DeviceColumn(typ, n, kind, width, data, offsets, validity, null_count)
+    if n > 0 and total % n == 0:
+        flag = rt.zeros(1, torch.int32)
+        rt.call("xchg_offsets_check_uniform", _vp(offsets), n, total // n, _vp(flag), rt.stream)
+        if int(flag.item()) == 0:
+            dc.uniform = total // n
+    return dc
+
+
+def stage_table(rt: Runtime, table: pa.Table) -> DeviceTable:
+    cols = [stage_column(rt, table.column(i), table.schema.field(i).type)
+            for i in range(table.num_columns)]
+    return DeviceTable(list(table.schema.names), cols, table.num_rows, table.schema)
+
+
+# ---------------------------------------------------------------------------
+# Gather (K5) and export
+# ---------------------------------------------------------------------------
+
+def take_column(rt: Runtime, col: DeviceColumn, idx: torch.Tensor, n_out: int) -> DeviceColumn:
+    """Device ``take``: rows ``idx[0:n_out]`` of ``col`` (idx = uint32 row ids)."""
+    validity, null_count = None, 0
+    if col.validity is not None and n_out:
+        validity = rt.zeros(((n_out + 31) // 32) * 4)
+        cnt = rt.zeros(1, torch.int64)
+        rt.call("xchg_gather_bitmap", _vp(col.validity), 0, _vp(idx), n_out, _vp(validity), _vp(cnt),
+                rt.stream)
+        null_count = cnt  # resolved lazily at export (one sync for the whole table)
+    if col.kind == "fixed":
+        out = rt.empty(n_out * col.width)
+        if n_out:
+            rt.call("xchg_gather_fixed", _vp(col.data), col.width, _vp(idx), n_out, _vp(out), rt.stream)
+        return DeviceColumn(col.type, n_out, "fixed", col.width, out, None, validity, null_count)
+    if col.kind == "bits":
+        out = rt.zeros(((n_out + 31) // 32) * 4)
+        if n_out:
+            rt.call("xchg_gather_bitmap", _vp(col.data), 0, _vp(idx), n_out, _vp(out), None, rt.stream)
+        return DeviceColumn(col.type, n_out, "bits", 0, out, None, validity, null_count)
+    # var
+    if col.uniform is not None:
+        w = col.uniform
+        out = rt.empty(n_out * w)
+        if n_out and w:
+            rt.call("xchg_gather_rows", _vp(col.data), w, _vp(idx), n_out, _vp(out), rt.stream)
+        # offsets are arithmetic; materialised only on export
+        return DeviceColumn(col.type, n_out, "var", col.width, out, None, validity, null_count, uniform=w)
+    out_off = rt.empty(n_out + 1, torch.int64)
+    ws_bytes = ctypes.c_uint64()
+    _cabi.check(_cabi.load().xchg_gather_offsets_workspace_bytes(n_out, ctypes.byref(ws_bytes)))
+    ws = rt.empty(ws_bytes.value)
+    rt.call("xchg_gather_offsets", _vp(col.offsets), _vp(idx), n_out, _vp(out_off), _vp(ws),
+            ws_bytes.value, rt.stream, launches=3)
+    total = int(out_off[n_out].item()) if n_out else 0  # sync: output byte count
+    out = rt.empty(total)
+    if total:
+        rt.call("xchg_gather_bytes", _vp(col.data), _vp(col.offsets), _vp(idx), n_out, _vp(out_off),
+                _vp(out), rt.stream)
+    return DeviceColumn(col.type, n_out, "var", col.width, out, out_off, validity, null_count)
+
+
+def take_table(rt: Runtime, table: DeviceTable, idx: torch.Tensor, n_out: Optional[int] = None) -> DeviceTable:
+    n_out = int(idx.numel()) if n_out is None else n_out
+    cols = [take_column(rt, c, idx, n_out) for c in table.columns]
+    return DeviceTable(list(table.names), cols, n_out, table.schema)
+
+
+def _export_buffers(rt: Runtime, col: DeviceColumn, lo: int, hi: int, pending: list):
+    """Queue D2H copies for rows [lo, hi) of a column; returns a closure that builds
+    the Arrow array once the stream has been synchronised."""
+    n = hi - lo
+    typ = col.type
+    st = _storage_type(typ)
+
+    def d2h(t: torch.Tensor) -> torch.Tensor:
+        h = rt.host_empty(t.numel(), t.dtype)
+        h.copy_(t, non_blocking=True)
+        return h
+
+    val_h = None
+    val_bit0 = 0
+    if col.validity is not None and n:
+        b0, b1 = lo // 8, (hi + 7) // 8
+        val_h = d2h(col.validity[b0:b1])
+        val_bit0 = lo - b0 * 8
+    nulls = col.null_count
+
+    if col.kind == "fixed":
+        data_h = d2h(col.data[lo * col.width : hi * col.width])
+        offs_h = None
+    elif col.kind == "bits":
+        b0, b1 = lo // 8, (hi + 7) // 8
+        data_h = d2h(col.data[b0:b1])
+        offs_h = None
+    else:
+        obits = _var_offset_bits(typ)
+        odt = torch.int32 if obits == 32 else torch.int64
+        if col.uniform is not None:
+            w = col.uniform
+            data_h = d2h(col.data[lo * w : hi * w])
+            offs_d = rt.empty(n + 1, odt)
+            elem_w = w // col.width
+            if obits == 32:
+                rt.call("xchg_offsets_uniform32", n + 1, elem_w, _vp(offs_d), rt.stream)
+            else:
+                rt.call("xchg_offsets_uniform64", n + 1, elem_w, 0, _vp(offs_d), rt.stream)
+            offs_h = d2h(offs_d)
+        else:
+            off = col.offsets[lo : hi + 1]
+            ends = col.offsets[[lo, hi]].tolist() if n else [0, 0]  # sync (2 scalars)
+            data_h = d2h(col.data[ends[0] : ends[1]])
+            if col.width == 1 and obits == 32:
+                if ends[1] - ends[0] > 0x7FFFFFFF:
+                    raise XchgError(
+                        f"column of type {typ}: {ends[1]-ends[0]} bytes do not fit int32 offsets; "
+                        "export it in smaller row ranges"
+                    )
+                offs_d = rt.empty(n + 1, torch.int32)
+                rt.call("xchg_offsets_narrow", _vp(off), n + 1, _vp(offs_d), rt.stream)
+            else:
+                offs_d = ((off - off[0]) // col.width).to(odt)
+            offs_h = d2h(offs_d)
+
+    def build() -> pa.Array:
+        nc = int(nulls.item()) if isinstance(nulls, torch.Tensor) else int(nulls)
+        if lo != 0 or hi != col.n:
+            nc = -1 if val_h is not None else 0
+        vbuf = pa.py_buffer(val_h.numpy()) if val_h is not None else None
+        if val_h is not None and val_bit0:
+            # realign the bitmap slice to bit 0
+            bits = np.unpackbits(val_h.numpy(), bitorder="little")[val_bit0 : val_bit0 + n]
+            vbuf = pa.py_buffer(np.packbits(bits, bitorder="little"))
+        if col.kind == "fixed":
+            if pa.types.is_fixed_size_list(st):
+                child = pa.Array.from_buffers(st.value_type, n * st.list_size,
+                                              [None, pa.py_buffer(data_h.numpy())])
+                arr = pa.Array.from_buffers(st, n, [vbuf], null_count=nc, children=[child])
+            else:
+                arr = pa.Array.from_buffers(st, n, [vbuf, pa.py_buffer(data_h.numpy())], null_count=nc)
+        elif col.kind == "bits":
+            bit0 = lo - (lo // 8) * 8
+            if bit0:
+                bits = np.unpackbits(data_h.numpy(), bitorder="little")[bit0 : bit0 + n]
+                dbuf = pa.py_buffer(np.packbits(bits, bitorder="little"))
+            else:
+                dbuf = pa.py_buffer(data_h.numpy())
+            arr = pa.Array.from_buffers(st, n, [vbuf, dbuf], null_count=nc)
+        else:
+            obuf = pa.py_buffer(offs_h.numpy())
+            dbuf = pa.py_buffer(data_h.numpy())
+            if pa.types.is_list(st) or pa.types.is_large_list(st):
+                nchild = data_h.numel() // col.width
+                child = pa.Array.from_buffers(st.value_type, nchild, [None, dbuf])
+                arr = pa.Array.from_buffers(st, n, [vbuf, obuf], null_count=nc, children=[child])
+            else:
+                arr = pa.Array.from_buffers(st, n, [vbuf, obuf, dbuf], null_count=nc)
+        if isinstance(typ, pa.ExtensionType):
+            arr = pa.ExtensionArray.from_storage(typ, arr)
+        return arr
+
+    return build
+
+
+def export_table(rt: Runtime, table: DeviceTable, lo: int = 0, hi: Optional[int] = None) -> pa.Table:
+    """Copy rows [lo, hi) back to (pinned) host memory as an Arrow table."""
+    hi = table.num_rows if hi is None else hi
+    builders = [_export_buffers(rt, c, lo, hi, []) for c in table.columns]
+    rt.synchronize()
+    arrays = [b() for b in builders]
+    return pa.Table.from_arrays(arrays, schema=table.schema)
+
+
+# ---------------------------------------------------------------------------
+# Sort (K2 + K3) and boundary search (K4)
+# ---------------------------------------------------------------------------
+
+_ws_cache: Dict[int, int] = {}
+
+
+def sort_workspace_bytes(n: int) -> int:
+    if n not in _ws_cache:
+        out = ctypes.c_uint64()
+        _cabi.check(_cabi.load().xchg_sort_workspace_bytes(n, ctypes.byref(out)))
+        _ws_cache[n] = out.value
+        if len(_ws_cache) > 64:
+            _ws_cache.pop(next(iter(_ws_cache)))
+    return _ws_cache[n]
+
+
+# launches per xchg_sort_column call: normalise+hist, scan, <=9 passes (bench counts the
+# exact number from the active-place flags; here we book the upper bound lazily)
+def sort_permutation(rt: Runtime, table: DeviceTable, columns: Sequence[str],
+                     descending: Sequence[bool], want_norm: bool = False):
+    """Stable multi-key sort -> (perm uint32[n] as int32 tensor, [norm key arrays]).
+
+    LSD over key columns (last key first); each column is one stable radix sort.
+    ``norm`` (only when ``want_norm``) holds, per key column, the normalised keys
+    in FINAL sorted order -- the input of :func:`partition_cuts`.
+    """
+    n = table.num_rows
+    if n > (1 << 30) - 1:
+        raise XchgError(f"{n} rows exceed XCHG_MAX_ROWS per sort call")
+    ws_bytes = sort_workspace_bytes(n)
+    ws = rt.empty(ws_bytes)
+    perm = None
+    norm_primary = None
+    order = list(zip(columns, descending))
+    for ci in range(len(order) - 1, -1, -1):
+        name, desc = order[ci]
+        col = table.column(name)
+        if col.kind != "fixed":
+            raise NotImplementedError(f"sort key column {name!r} of type {col.type} is not supported")
+        kt = key_type_of(col.type)
+        out = rt.empty(n, torch.int32)
+        norm = rt.empty(n, torch.int64) if (want_norm and ci == 0) else None
+        rt.call("xchg_sort_column", _vp(col.data), kt, int(bool(desc)), _vp(col.validity), 0,
+                _vp(perm), n, _vp(out), _vp(norm), _vp(ws), ws_bytes, rt.stream, launches=10)
+        perm = out
+        if ci == 0:
+            norm_primary = norm
+    norms = None
+    if want_norm:
+        norms = [norm_primary]
+        for name, desc in order[1:]:
+            col = table.column(name)
+            nk = rt.empty(n, torch.int64)
+            rt.call("xchg_normalize_keys", _vp(col.data), key_type_of(col.type), int(bool(desc)),
+                    _vp(col.validity), 0, _vp(perm), n, _vp(nk), rt.stream)
+            norms.append(nk)
+    return perm, norms
+
+
+def partition_cuts(rt: Runtime, norms: List[torch.Tensor], n: int, lower: np.ndarray,
+                   upper: np.ndarray, flags: np.ndarray, descending: Sequence[bool],
+                   thresholds: Sequence[int], has_last: Sequence[bool]) -> List[int]:
+    """K4: cut indices for ``nb`` boundaries (arrays are [nb, ncols], row-major)."""
+    nb, ncols = lower.shape
+    if nb == 0:
+        return []
+    lo_d = rt.empty(nb * ncols, torch.int64)
+    up_d = rt.empty(nb * ncols, torch.int64)
+    fl_d = rt.empty(nb * ncols, torch.uint8)
+    _h2d(lo_d.view(torch.uint8), np.ascontiguousarray(lower, dtype=np.uint64).view(np.uint8).reshape(-1))
+    _h2d(up_d.view(torch.uint8), np.ascontiguousarray(upper, dtype=np.uint64).view(np.uint8).reshape(-1))
+    _h2d(fl_d, np.ascontiguousarray(flags, dtype=np.uint8).reshape(-1))
+    cuts = rt.empty(nb, torch.int64)
+    ptrs = (ctypes.c_void_p * ncols)(*[t.data_ptr() for t in norms[:ncols]])
+    cdesc = (ctypes.c_uint8 * ncols)(*[int(bool(d)) for d in descending[:ncols]])
+    thr = (ctypes.c_uint64 * ncols)(*[int(t) for t in thresholds[:ncols]])
+    hl = (ctypes.c_uint8 * ncols)(*[int(bool(h)) for h in has_last[:ncols]])
+    rt.call("xchg_partition_bounds", ptrs, cdesc, thr, hl, ncols, n, _vp(lo_d), _vp(up_d), _vp(fl_d),
+            nb, int(bool(descending[0])), _vp(cuts), rt.stream)
+    return [int(x) for x in cuts.tolist()]

@@ -1,0 +1,3 @@
+from .interfaces import ExchangeTaskScheduler, ExchangeTaskSpec  # noqa: F401
+from .pull_based import PullBasedShuffleTaskScheduler  # noqa: F401
+from .sort_task_spec import SortTaskSpec  # noqa: F401

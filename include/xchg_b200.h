@@ -1,0 +1,181 @@
+/*
+ * xchg_b200.h -- C-ABI of the B200-native exchange engine (libxchg_b200.so).
+ *
+ * Drop-in boundary for ONE hot path of the reference: Ray Data's all-to-all
+ * exchange (Dataset.sort / random_shuffle / groupby().aggregate on Arrow
+ * blocks).  The reference has no FFI for this path -- its boundary is the Python
+ * class surface BlockAccessor / ExchangeTaskSpec (python/ray/data/block.py:
+ * 256-512, python/ray/data/_internal/planner/exchange/interfaces.py:14-102) and
+ * its arithmetic lives in pyarrow / numpy calls.  Each entry point below names
+ * the reference call site it replaces.  The Python host layer
+ * (cluster_anywhere_b200/) binds these with ctypes and mirrors the reference's
+ * class surface on top; INTEGRATION.md shows the binding a reference
+ * maintainer would add.
+ *
+ * Conventions
+ *  - All pointers are DEVICE pointers unless the name ends in _host.
+ *  - Nothing here allocates: the caller passes workspaces (sizes from the
+ *    *_workspace_bytes queries) and a CUDA stream (cudaStream_t as void*, NULL =
+ *    legacy default stream).  Calls are asynchronous on that stream unless
+ *    stated otherwise.
+ *  - Every function returns 0 on success, a negative xchg_status otherwise;
+ *    xchg_last_error() returns a thread-local message.  There is no CPU
+ *    fallback: without a CUDA device every compute entry point fails.
+ *  - Row counts per call are limited to XCHG_MAX_ROWS (2^30 - 1).
+ *  - Validity bitmaps are Arrow LSB-first bitmaps; NULL means "no nulls".
+ */
+#ifndef XCHG_B200_H_
+#define XCHG_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define XCHG_ABI_VERSION 1
+#define XCHG_MAX_ROWS ((uint64_t)((1u << 30) - 1))
+
+typedef enum {
+  XCHG_OK = 0,
+  XCHG_ERR_INVALID = -1,   /* bad argument */
+  XCHG_ERR_CUDA = -2,      /* CUDA runtime error (message has the detail) */
+  XCHG_ERR_WORKSPACE = -3, /* workspace too small */
+  XCHG_ERR_LIMIT = -4      /* size beyond a documented maximum */
+} xchg_status;
+
+/* Physical key types (Arrow primitive layouts). */
+typedef enum {
+  XCHG_I8 = 0, XCHG_I16 = 1, XCHG_I32 = 2, XCHG_I64 = 3,
+  XCHG_U8 = 4, XCHG_U16 = 5, XCHG_U32 = 6, XCHG_U64 = 7,
+  XCHG_F32 = 8, XCHG_F64 = 9
+} xchg_key_type;
+
+int xchg_abi_version(void);
+const char* xchg_last_error(void);
+/* Number of visible CUDA devices (0 if none; never fails). */
+int xchg_device_count(void);
+
+/* ---------------------------------------------------------------- sort ---- */
+
+/* Workspace bytes xchg_sort_column needs for n rows. */
+int xchg_sort_workspace_bytes(uint64_t n, uint64_t* bytes_out);
+
+/*
+ * Stable sort of one key column -> row permutation.
+ * Replaces pyarrow.compute.sort_indices as called from
+ * python/ray/data/_internal/arrow_ops/transform_pyarrow.py:41 (sort) and :546
+ * (concat_and_sort), one key column per call; multi-key sorts chain calls from
+ * the LAST key to the first, feeding perm_out back as perm_in (LSD over
+ * columns; every call is stable).
+ *
+ * Order (Arrow's, both directions): finite numbers in the requested direction,
+ * then NaN, then null; ties keep input order; -0.0 == +0.0.
+ *
+ *  keys        n values of key_type (indexed by ORIGINAL row id)
+ *  validity    Arrow validity bitmap of the column or NULL; bit i+validity_bit_offset
+ *  perm_in     NULL = identity; else the current row order (n row ids)
+ *  perm_out    n row ids: perm_out[j] = original row id at sorted position j
+ *  norm_keys_out  optional (may be NULL): n order-preserving 64-bit radix keys in
+ *              sorted order (ascending as unsigned whatever the direction);
+ *              input to xchg_partition_bounds
+ *  Synchronises the stream once internally (reads 9 pass-activity flags).
+ */
+int xchg_sort_column(const void* keys, int key_type, int descending,
+                     const uint8_t* validity, int64_t validity_bit_offset,
+                     const uint32_t* perm_in, uint64_t n,
+                     uint32_t* perm_out, uint64_t* norm_keys_out,
+                     void* workspace, uint64_t workspace_bytes, void* stream);
+
+/*
+ * Key normalisation only (no sort): norm_out[i] = radix key of
+ * keys[perm ? perm[i] : i].  Used to build the secondary-key arrays
+ * xchg_partition_bounds searches.  For 64-bit integer columns nulls cannot be
+ * folded into 64 bits; they map to UINT64_MAX (callers treat that value as
+ * "null" only when the column has nulls).
+ */
+int xchg_normalize_keys(const void* keys, int key_type, int descending,
+                        const uint8_t* validity, int64_t validity_bit_offset,
+                        const uint32_t* perm, uint64_t n, uint64_t* norm_out,
+                        void* stream);
+
+/*
+ * Boundary search on sorted normalised keys -> partition cut indices.
+ * Replaces find_partition_index / find_partitions
+ * (python/ray/data/_internal/util.py:728-828): for boundary b, walk the key
+ * columns c = 0..ncols-1 narrowing [lo,hi) to the run whose normalised key lies
+ * in [lower[b*ncols+c], upper[b*ncols+c]]; stop early when lo == hi; result is
+ * hi if first_descending else lo.  flags per (boundary, column): bit0 = the equal
+ * range is empty (hi = lo = lower_bound), bit1 = boundary tuple ends before this
+ * column, bit2 = boundary sorts after every row (a None boundary: lo = hi),
+ * bit3 = boundary is NaN.
+ * Descending columns reproduce numpy.searchsorted over the reference's reversed
+ * view probe by probe (util.py:775-799), so that cut points stay identical even
+ * where NaN / null keys make that view unsorted for numpy; keys >=
+ * last_threshold_host[c] are the NaN / null class when has_last_host[c] != 0.
+ *
+ *  norm_cols_host   HOST array of ncols device pointers, each n keys in final
+ *                   sorted order; col_desc_host / last_threshold_host /
+ *                   has_last_host: HOST arrays of ncols entries
+ *  lower/upper/flags  nb*ncols entries, device
+ *  cuts_out    nb uint64 row indices, device
+ */
+int xchg_partition_bounds(const uint64_t* const* norm_cols_host, const uint8_t* col_desc_host,
+                          const uint64_t* last_threshold_host, const uint8_t* has_last_host,
+                          int ncols, uint64_t n,
+                          const uint64_t* lower, const uint64_t* upper,
+                          const uint8_t* flags, int nb, int first_descending,
+                          uint64_t* cuts_out, void* stream);
+
+/* -------------------------------------------------------------- gather ---- */
+
+/*
+ * out[i] = in[idx[i]] for fixed-width elements of `width` bytes (1,2,4,8,16 are
+ * vectorised; any other width takes the byte-row path).  Replaces
+ * pyarrow.Table.take for primitive columns
+ * (python/ray/data/_internal/arrow_ops/transform_pyarrow.py:45-71).
+ */
+int xchg_gather_fixed(const void* in, uint32_t width, const uint32_t* idx, uint64_t n_out,
+                      void* out, void* stream);
+
+/* out bit i = in bit (idx[i] + in_bit_offset); also counts nulls (zero bits)
+ * into *null_count_out (device uint64, may be NULL; must be zeroed by caller). */
+int xchg_gather_bitmap(const uint8_t* in, int64_t in_bit_offset, const uint32_t* idx,
+                       uint64_t n_out, uint8_t* out, uint64_t* null_count_out, void* stream);
+
+/*
+ * Variable-width take (Arrow binary/string/large_* /list child bytes).
+ * Replaces Table.take on var-width columns (same call site).
+ *  step 1  xchg_gather_offsets: out_off[0]=0, out_off[i+1]=out_off[i]+len(idx[i])
+ *          (int64, n_out+1 entries); in_off is int64 (n_in+1 entries, absolute).
+ *  step 2  xchg_gather_bytes: copies the row bytes.
+ */
+int xchg_gather_offsets_workspace_bytes(uint64_t n_out, uint64_t* bytes_out);
+int xchg_gather_offsets(const int64_t* in_off, const uint32_t* idx, uint64_t n_out,
+                        int64_t* out_off, void* workspace, uint64_t workspace_bytes,
+                        void* stream);
+int xchg_gather_bytes(const uint8_t* in_data, const int64_t* in_off, const uint32_t* idx,
+                      uint64_t n_out, const int64_t* out_off, uint8_t* out_data,
+                      void* stream);
+/* Uniform-width rows (every row `width` bytes; GraySort payload, tensor rows):
+ * out row i = in row idx[i]; no offsets are read. */
+int xchg_gather_rows(const uint8_t* in_data, uint32_t width, const uint32_t* idx,
+                     uint64_t n_out, uint8_t* out_data, void* stream);
+
+/* Offsets utilities for Arrow staging: widen int32 offsets to absolute int64
+ * (out[i] = in[i] - in[0] + base) and narrow back (out[i] = in[i] - in[0]). */
+int xchg_offsets_widen(const int32_t* in, uint64_t count, int64_t base, int64_t* out, void* stream);
+int xchg_offsets_narrow(const int64_t* in, uint64_t count, int32_t* out, void* stream);
+/* out[i] = base + i*width, count entries (offsets of uniform rows). */
+int xchg_offsets_uniform32(uint64_t count, uint32_t width, int32_t* out, void* stream);
+int xchg_offsets_uniform64(uint64_t count, uint64_t width, int64_t base, int64_t* out, void* stream);
+/* *flag_out (device uint32, caller zeroes) becomes nonzero unless every row has
+ * `width` bytes. */
+int xchg_offsets_check_uniform(const int64_t* off, uint64_t n_rows, uint64_t width,
+                               uint32_t* flag_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* XCHG_B200_H_ */

@@ -1,0 +1,267 @@
+"""TEST DOUBLE for libxchg_b200.so -- host-memory numpy stand-in for the C-ABI.
+
+Lets the ``-m "not gpu"`` suite exercise the Python host layer (Arrow staging,
+boundary normalisation, partition slicing, export, the exchange schedule) in a
+container without a GPU: pointers are host pointers (CPU torch tensors) and each
+entry point is an independent numpy restatement of the kernel's contract in
+include/xchg_b200.h.  It is installed only by tests (``_cabi._install_test_double``);
+the product path never sees it.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+
+
+def _addr(p):
+    if p is None:
+        return 0
+    if isinstance(p, ctypes.c_void_p):
+        return p.value or 0
+    if isinstance(p, int):
+        return p
+    return ctypes.addressof(p)
+
+
+def _arr(p, dtype, count):
+    a = _addr(p)
+    dt = np.dtype(dtype)
+    if count == 0:
+        return np.zeros(0, dtype=dt)
+    assert a != 0, "NULL pointer"
+    buf = (ctypes.c_uint8 * (count * dt.itemsize)).from_address(a)
+    return np.frombuffer(buf, dtype=dt, count=count)
+
+
+_KT = {0: np.int8, 1: np.int16, 2: np.int32, 3: np.int64, 4: np.uint8, 5: np.uint16,
+       6: np.uint32, 7: np.uint64, 8: np.float32, 9: np.float64}
+
+
+def _bits(p, bit_off, idx):
+    a = _addr(p)
+    pos = idx.astype(np.int64) + bit_off
+    nbytes = int(pos.max()) // 8 + 1 if len(pos) else 0
+    bm = _arr(p, np.uint8, nbytes)
+    return ((bm[pos >> 3] >> (pos & 7).astype(np.uint8)) & 1).astype(bool)
+
+
+def _normalize(vals, kt, desc):
+    dt = np.dtype(_KT[kt])
+    bits = dt.itemsize * 8
+    mask = np.uint64((1 << bits) - 1) if bits < 64 else np.uint64(0xFFFFFFFFFFFFFFFF)
+    if dt.kind == "f":
+        u = np.uint32 if bits == 32 else np.uint64
+        v = vals.copy()
+        v[v == 0] = 0.0
+        b = v.view(u).astype(np.uint64)
+        sign = np.uint64(1 << (bits - 1))
+        t = np.where(b & sign != 0, ~b & mask, b | sign)
+        if desc:
+            t = ~t & mask
+        t = np.where(np.isnan(vals), np.uint64(int(mask) - 1), t)
+        return t.astype(np.uint64)
+    if dt.kind == "i":
+        u = (vals.astype(np.int64).view(np.uint64) + np.uint64(1 << (bits - 1))) & mask
+    else:
+        u = vals.astype(np.uint64)
+    if desc:
+        u = ~u & mask
+    return u.astype(np.uint64)
+
+
+def _null_key(kt):
+    bits = np.dtype(_KT[kt]).itemsize * 8
+    return np.uint64(0xFFFFFFFFFFFFFFFF) if bits == 64 else np.uint64(1 << bits)
+
+
+class FakeLib:
+    def __init__(self):
+        self.err = b""
+        self.calls = []
+
+    def xchg_abi_version(self):
+        return 1
+
+    def xchg_last_error(self):
+        return self.err
+
+    def xchg_device_count(self):
+        return 0
+
+    def xchg_sort_workspace_bytes(self, n, out):
+        out._obj.value = 64
+        return 0
+
+    def _norm_col(self, keys, kt, desc, validity, vbit, perm, n):
+        dt = _KT[kt]
+        rows = _arr(perm, np.uint32, n).astype(np.int64) if _addr(perm) else np.arange(n)
+        nrows_src = int(rows.max()) + 1 if n else 0
+        src = _arr(keys, dt, nrows_src)
+        nk = _normalize(src[rows], kt, bool(desc))
+        valid = np.ones(n, dtype=bool)
+        if _addr(validity):
+            valid = _bits(validity, vbit, rows)
+            nk = np.where(valid, nk, _null_key(kt))
+        return rows, nk, valid
+
+    def xchg_sort_column(self, keys, kt, desc, validity, vbit, perm_in, n, perm_out, norm_out, ws, wsb, stream):
+        self.calls.append("sort_column")
+        if n == 0:
+            return 0
+        rows, nk, valid = self._norm_col(keys, kt, desc, validity, vbit, perm_in, n)
+        order = np.lexsort((nk, ~valid))  # stable: valid first, then by key
+        order = np.argsort(nk, kind="stable")
+        order = order[np.argsort(~valid[order], kind="stable")]
+        _arr(perm_out, np.uint32, n)[:] = rows[order].astype(np.uint32)
+        if _addr(norm_out):
+            _arr(norm_out, np.uint64, n)[:] = nk[order]
+        return 0
+
+    def xchg_normalize_keys(self, keys, kt, desc, validity, vbit, perm, n, out, stream):
+        if n == 0:
+            return 0
+        _, nk, _ = self._norm_col(keys, kt, desc, validity, vbit, perm, n)
+        _arr(out, np.uint64, n)[:] = nk
+        return 0
+
+    def xchg_partition_bounds(self, cols, col_desc, last_thr, has_last, ncols, n, lower, upper, flags,
+                              nb, first_desc, cuts, stream):
+        lo_a = _arr(lower, np.uint64, nb * ncols)
+        up_a = _arr(upper, np.uint64, nb * ncols)
+        fl_a = _arr(flags, np.uint8, nb * ncols) if _addr(flags) else np.zeros(nb * ncols, np.uint8)
+        out = _arr(cuts, np.uint64, nb)
+        arrays = [_arr(cols[c], np.uint64, n) for c in range(ncols)]
+        cdesc = [col_desc[c] for c in range(ncols)]
+        thr = [last_thr[c] for c in range(ncols)]
+        hl = [has_last[c] for c in range(ncols)]
+        for b in range(nb):
+            lo, hi = 0, n
+            early = False
+            for c in range(ncols):
+                if lo == hi:
+                    early = True
+                    break
+                f = int(fl_a[b * ncols + c])
+                if f & 2:
+                    break
+                if f & 4:
+                    lo = hi
+                    continue
+                L, U = int(lo_a[b * ncols + c]), int(up_a[b * ncols + c])
+                if not cdesc[c]:
+                    seg = arrays[c][lo:hi] if hi > lo else arrays[c][0:0]
+                    l2 = lo + int(np.searchsorted(seg, np.uint64(L), side="left"))
+                    h2 = l2 if (f & 1) else lo + int(np.searchsorted(seg, np.uint64(U), side="right"))
+                    lo, hi = l2, h2
+                    continue
+                # descending: numpy.searchsorted over the reversed view, probe by probe
+                a = arrays[c]
+                m = hi - lo if hi > lo else 0
+                key_last = bool(f & 8)
+
+                def is_last(k):
+                    return bool(hl[c]) and k >= thr[c]
+
+                mn, mx = 0, m
+                while mn < mx:
+                    mid = mn + ((mx - mn) >> 1)
+                    k = int(a[hi - 1 - mid])
+                    el = is_last(k)
+                    before_eq = (k < L) if (f & 1) else (k <= U)
+                    lt = (not el) if key_last else ((not el) and (not before_eq))
+                    if lt:
+                        mn = mid + 1
+                    else:
+                        mx = mid
+                left_idx = mn
+                mn, mx = 0, m
+                while mn < mx:
+                    mid = mn + ((mx - mn) >> 1)
+                    k = int(a[hi - 1 - mid])
+                    el = is_last(k)
+                    key_lt_arr = (not key_last) and (el or k < L)
+                    if not key_lt_arr:
+                        mn = mid + 1
+                    else:
+                        mx = mid
+                right_idx = mn
+                base = lo
+                lo, hi = base + (m - right_idx), base + (m - left_idx)
+            out[b] = hi if (early or first_desc) else lo
+        return 0
+
+    def xchg_gather_fixed(self, inp, width, idx, n, out, stream):
+        if n == 0:
+            return 0
+        ix = _arr(idx, np.uint32, n).astype(np.int64)
+        src = _arr(inp, np.uint8, (int(ix.max()) + 1) * width).reshape(-1, width)
+        _arr(out, np.uint8, n * width).reshape(-1, width)[:] = src[ix]
+        return 0
+
+    def xchg_gather_rows(self, inp, width, idx, n, out, stream):
+        return self.xchg_gather_fixed(inp, width, idx, n, out, stream)
+
+    def xchg_gather_bitmap(self, inp, bit_off, idx, n, out, null_count, stream):
+        if n == 0:
+            return 0
+        ix = _arr(idx, np.uint32, n)
+        bits = _bits(inp, bit_off, ix)
+        packed = np.packbits(bits, bitorder="little")
+        nbytes = ((n + 31) // 32) * 4
+        o = _arr(out, np.uint8, nbytes)
+        o[:] = 0
+        o[: len(packed)] = packed
+        if _addr(null_count):
+            _arr(null_count, np.uint64, 1)[0] += int((~bits).sum())
+        return 0
+
+    def xchg_gather_offsets_workspace_bytes(self, n, out):
+        out._obj.value = 64
+        return 0
+
+    def xchg_gather_offsets(self, in_off, idx, n, out_off, ws, wsb, stream):
+        o = _arr(out_off, np.int64, n + 1)
+        o[0] = 0
+        if n == 0:
+            return 0
+        ix = _arr(idx, np.uint32, n).astype(np.int64)
+        io = _arr(in_off, np.int64, int(ix.max()) + 2)
+        o[1:] = np.cumsum(io[ix + 1] - io[ix])
+        return 0
+
+    def xchg_gather_bytes(self, in_data, in_off, idx, n, out_off, out_data, stream):
+        if n == 0:
+            return 0
+        ix = _arr(idx, np.uint32, n).astype(np.int64)
+        io = _arr(in_off, np.int64, int(ix.max()) + 2)
+        oo = _arr(out_off, np.int64, n + 1)
+        src = _arr(in_data, np.uint8, int(io[ix + 1].max()))
+        dst = _arr(out_data, np.uint8, int(oo[n]))
+        for j in range(n):
+            dst[oo[j]:oo[j + 1]] = src[io[ix[j]]:io[ix[j] + 1]]
+        return 0
+
+    def xchg_offsets_widen(self, inp, count, base, out, stream):
+        i = _arr(inp, np.int32, count).astype(np.int64)
+        _arr(out, np.int64, count)[:] = i - i[0] + base
+        return 0
+
+    def xchg_offsets_narrow(self, inp, count, out, stream):
+        i = _arr(inp, np.int64, count)
+        _arr(out, np.int32, count)[:] = (i - i[0]).astype(np.int32)
+        return 0
+
+    def xchg_offsets_uniform32(self, count, width, out, stream):
+        _arr(out, np.int32, count)[:] = np.arange(count, dtype=np.int64) * width
+        return 0
+
+    def xchg_offsets_uniform64(self, count, width, base, out, stream):
+        _arr(out, np.int64, count)[:] = base + np.arange(count, dtype=np.int64) * width
+        return 0
+
+    def xchg_offsets_check_uniform(self, off, n_rows, width, flag, stream):
+        o = _arr(off, np.int64, n_rows + 1)
+        if (np.diff(o) != width).any():
+            _arr(flag, np.uint32, 1)[0] |= 1
+        return 0

@@ -25,3 +25,23 @@ def pytest_collection_modifyitems(config, items):
     for item in items:
         if "gpu" in item.keywords:
             item.add_marker(skip)
+
+
+@pytest.fixture(params=[pytest.param("host-double"), pytest.param("b200", marks=pytest.mark.gpu)])
+def engine(request):
+    """Runs a test body against (a) the host-memory test double of the C-ABI -- host
+    logic only, no GPU needed -- and (b) the real CUDA library on a B200."""
+    from cluster_anywhere_b200 import _cabi, device
+
+    if request.param == "host-double":
+        from _fake_cabi import FakeLib
+
+        _cabi._install_test_double(FakeLib())
+        device.reset_default_runtime()
+        yield request.param
+        _cabi._install_test_double(None)
+        device.reset_default_runtime()
+    else:
+        _cabi._install_test_double(None)
+        device.reset_default_runtime()
+        yield request.param
