@@ -1,0 +1,531 @@
+#!/usr/bin/env python
+"""Benchmark of the exchange hot path: Dataset.sort on GraySort rows.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]          # this engine
+  python bench.py --impl reference [--steps K] [--warmup W]   # CPU reference arm
+
+Workload (BASELINE.json configs[1]): int64 key + 90-byte binary payload rows,
+125 M rows per GPU (12.25 GB) in 12 blocks -- 1 B rows at 8 GPUs, weak scaling.
+The 1 B-row config does not fit one GPU (input + output = 196 GB > 180 GB), so
+N=1 runs its per-GPU shard; ``config.workload`` says so.
+
+One step = one full ``Dataset.sort('c_0')`` of the resident blocks: boundary
+sampling (K1), key normalisation + histograms (K2), onesweep radix passes (K3),
+boundary search (K4), key + payload gather (K5) [+ exchange and merge at N>1].
+``value`` has the inputs resident in HBM; ``e2e`` goes through the public
+host-buffer API (``DeviceExchange.sort_blocks``) from pinned host Arrow blocks
+and back, copies inside the timed region.  Prints ONE JSON line.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import shutil
+import statistics
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "Dataset.sort rows/s (GraySort rows: int64 key + 90 B payload)"
+UNIT = "rows/s"
+ROW_BYTES = 98
+PAYLOAD = 90
+
+KERNEL_NAMES = {0: "k_normalize_hist", 1: "k_scan_hist", 2: "k_onesweep", 3: "k_gather_rows",
+                4: "k_gather_fixed", 5: "k_gather_bitmap", 6: "k_lengths_scan", 7: "k_partition_bounds",
+                8: "k_offsets_*", 9: "misc", 10: "k_merge", 11: "k_shuffle", 12: "k_aggregate"}
+# algorithmic bytes per row per launch
+KERNEL_BYTES_PER_ROW = {0: 16, 2: 24, 3: 2 * PAYLOAD}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        if shutil.which("nvidia-smi") is None:
+            return
+        fd, self.path = tempfile.mkstemp(prefix="clocks_", suffix=".csv")
+        os.close(fd)
+        self.proc = subprocess.Popen(
+            ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+             "-i", str(self.idx)], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(",")]
+                if len(f) < 9:
+                    continue
+                try:
+                    sm.append(float(f[1]))
+                    mx.append(float(f[2]))
+                except ValueError:
+                    continue
+                for nm, v in zip(names, f[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+        finally:
+            try:
+                os.unlink(self.path)
+            except OSError:
+                pass
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons),
+                       samples=len(sm))
+        return out
+
+
+# ----------------------------------------------------------------------------
+# CPU reference arm (oracle port of the reference's pyarrow/numpy exchange)
+# ----------------------------------------------------------------------------
+
+def _shm_dir():
+    base = "/dev/shm" if os.path.isdir("/dev/shm") and shutil.disk_usage("/dev/shm").free > (32 << 30) else None
+    return tempfile.mkdtemp(prefix="xchg_cpu_", dir=base)
+
+
+def _write_ipc(path, table):
+    import pyarrow as pa
+
+    with pa.OSFile(path, "wb") as f:
+        with pa.ipc.new_file(f, table.schema) as w:
+            w.write_table(table)
+
+
+def _read_ipc(path):
+    import pyarrow as pa
+
+    return pa.ipc.open_file(pa.memory_map(path, "r")).read_all()
+
+
+def _cpu_map_task(args):
+    """One reference map task (SortTaskSpec.map): block in shared memory -> R sorted
+    partitions in shared memory (as plasma objects would be)."""
+    i, in_path, out_dir, boundaries, null_scan = args
+    from oracle import exchange_oracle as O
+
+    blk = _read_ipc(in_path)
+    parts = O.sort_and_partition(blk, boundaries, ["c_0"], [False], null_scan=null_scan)
+    paths = []
+    for j, p in enumerate(parts):
+        path = os.path.join(out_dir, f"m{i}_{j}.arrow")
+        _write_ipc(path, p)
+        paths.append(path)
+    return paths
+
+
+def _cpu_reduce_task(args):
+    j, paths, out_dir = args
+    from oracle import exchange_oracle as O
+
+    out = O.merge_sorted_blocks([_read_ipc(p) for p in paths], ["c_0"], [False])
+    path = os.path.join(out_dir, f"r{j}.arrow")
+    _write_ipc(path, out)
+    return out.num_rows
+
+
+def make_cpu_blocks(num_blocks: int, rows_per_block: int, seed: int = 2):
+    import numpy as np
+    import pyarrow as pa
+
+    rng = np.random.default_rng(seed)
+    blocks = []
+    offs = np.arange(rows_per_block + 1, dtype=np.int32) * PAYLOAD
+    for _ in range(num_blocks):
+        keys = rng.integers(0, 2**63 - 1, rows_per_block, dtype=np.int64)
+        payload = rng.integers(0, 256, rows_per_block * PAYLOAD, dtype=np.uint8)
+        c1 = pa.Array.from_buffers(pa.binary(), rows_per_block,
+                                   [None, pa.py_buffer(offs), pa.py_buffer(payload)])
+        blocks.append(pa.table({"c_0": keys, "c_1": c1}))
+    return blocks
+
+
+class CpuReference:
+    """The reference's CPU exchange on a bounded sample: the pull-based schedule
+    (all SortTaskSpec.map tasks, then all .reduce tasks --
+    pull_based_shuffle_task_scheduler.py:84-120) on a pool of one process per core,
+    blocks and partitions handed over as Arrow IPC in shared memory (what Ray's
+    plasma store does).  ``null_scan=True`` is the reference as-is (incl. the
+    O(R*N) ``col == None`` scan of find_partition_index, util.py:769)."""
+
+    def __init__(self, cores: int, rows_per_block: int, num_blocks: int):
+        import multiprocessing as mp
+
+        self.cores = cores
+        self.rows_per_block = rows_per_block
+        self.num_blocks = num_blocks
+        self.dir = _shm_dir()
+        blocks = make_cpu_blocks(num_blocks, rows_per_block)
+        self.in_paths = []
+        for i, b in enumerate(blocks):
+            p = os.path.join(self.dir, f"in{i}.arrow")
+            _write_ipc(p, b)
+            self.in_paths.append(p)
+        from oracle import exchange_oracle as O
+        import numpy as np
+
+        # driver-side boundary sampling (sort_task_spec.py:154-226), untimed setup
+        rng = np.random.default_rng(0)
+        n_s = O.samples_per_block(num_blocks, num_blocks)
+        samples = []
+        for b in blocks:
+            idx = rng.choice(b.num_rows, size=min(n_s, b.num_rows), replace=False)
+            samples += [(int(k),) for k in b["c_0"].to_numpy()[idx]]
+        self.boundaries = O.boundaries_from_samples(samples, [False], num_blocks)
+        del blocks
+        self.pool = mp.get_context("fork").Pool(cores)
+        self.total_rows = rows_per_block * num_blocks
+
+    def step(self, null_scan: bool = True) -> float:
+        out_dir = tempfile.mkdtemp(prefix="step_", dir=self.dir)
+        t0 = time.perf_counter()
+        maps = self.pool.map(_cpu_map_task,
+                             [(i, p, out_dir, self.boundaries, null_scan) for i, p in enumerate(self.in_paths)],
+                             chunksize=1)
+        rows = self.pool.map(_cpu_reduce_task,
+                             [(j, [m[j] for m in maps], out_dir) for j in range(self.num_blocks)],
+                             chunksize=1)
+        dt = time.perf_counter() - t0
+        assert sum(rows) == self.total_rows
+        shutil.rmtree(out_dir, ignore_errors=True)
+        return dt
+
+    def close(self):
+        self.pool.close()
+        self.pool.join()
+        shutil.rmtree(self.dir, ignore_errors=True)
+
+
+def run_reference(args):
+    """--impl reference: rank 0 only; other ranks exit 0 without work."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = len(os.sched_getaffinity(0))
+    rows_per_block = args.cpu_rows_per_block
+    nblocks = args.cpu_blocks or cores
+    ref = CpuReference(cores, rows_per_block, nblocks)
+    try:
+        for _ in range(args.warmup):
+            ref.step()
+        times = [ref.step() for _ in range(args.steps)]
+        prim = ref.step(null_scan=False)
+    finally:
+        ref.close()
+    t = sum(times) / len(times)
+    value = ref.total_rows / t
+    sample = (f"{nblocks} blocks x {rows_per_block} GraySort rows ({ref.total_rows * ROW_BYTES / 1e9:.2f} GB), "
+              f"R={nblocks}, pull-based map/reduce on {cores} processes, Arrow IPC hand-off in shared memory")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u64", "data": "synthetic",
+        "config": {"workload": workload_name(args), "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                         "gb_per_s": value * 2 * ROW_BYTES / 1e9,
+                         "primitives_only_value": ref.total_rows / prim,
+                         "note": "oracle port = the reference's own pyarrow/numpy call sequence; "
+                                 "value is the reference as-is, primitives_only_value drops its "
+                                 "O(R*N) `col == None` scan"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------
+# B200 arm
+# ----------------------------------------------------------------------------
+
+def workload_name(args):
+    return (f"GraySort-style Dataset.sort: int64 key + 90 B binary payload, {args.rows_per_gpu} rows/GPU "
+            f"in {args.blocks_per_gpu} blocks ({args.rows_per_gpu * ROW_BYTES / 1e9:.2f} GB/GPU; "
+            f"BASELINE.json configs[1] = 1e9 rows at 8 GPUs, weak-scaled shard at fewer GPUs because "
+            f"1e9 rows x 98 B in + out exceeds one GPU's 180 GB)")
+
+
+def build_resident_dataset(rt, n, blocks, seed):
+    """Synthetic GraySort rows generated directly in HBM (seeded)."""
+    import pyarrow as pa
+    import torch
+
+    from cluster_anywhere_b200 import device as dev
+    from cluster_anywhere_b200.exchange import DeviceDataset
+
+    g = torch.Generator(device=rt.device)
+    g.manual_seed(seed)
+    keys = torch.randint(0, 2**63 - 1, (n,), dtype=torch.int64, device=rt.device, generator=g)
+    data = rt.empty(n * PAYLOAD)
+    chunk = 1 << 28
+    for s in range(0, n * PAYLOAD, chunk):
+        e = min(n * PAYLOAD, s + chunk)
+        data[s:e] = torch.randint(0, 256, (e - s,), dtype=torch.uint8, device=rt.device, generator=g)
+    schema = pa.schema([("c_0", pa.int64()), ("c_1", pa.binary())])
+    c0 = dev.DeviceColumn(pa.int64(), n, "fixed", 8, keys.view(torch.uint8))
+    c1 = dev.DeviceColumn(pa.binary(), n, "var", 1, data, None, None, 0, uniform=PAYLOAD)
+    table = dev.DeviceTable(["c_0", "c_1"], [c0, c1], n, schema)
+    per = n // blocks
+    ranges = [(i * per, (i + 1) * per if i < blocks - 1 else n) for i in range(blocks)]
+    return DeviceDataset(table, ranges), keys, data
+
+
+def host_blocks_from_device(rt, keys, data, ranges):
+    """Pinned-host Arrow blocks holding the same rows (e2e input)."""
+    import numpy as np
+    import pyarrow as pa
+    import torch
+
+    n = keys.numel()
+    keys_h = torch.empty(n, dtype=torch.int64, pin_memory=True)
+    keys_h.copy_(keys)
+    data_h = torch.empty(n * PAYLOAD, dtype=torch.uint8, pin_memory=True)
+    data_h.copy_(data[: n * PAYLOAD])
+    max_rows = max(hi - lo for lo, hi in ranges)
+    offs_h = torch.empty(max_rows + 1, dtype=torch.int32, pin_memory=True)
+    offs_h.copy_(torch.arange(max_rows + 1, dtype=torch.int32) * PAYLOAD)
+    torch.cuda.synchronize()
+    kbuf, dbuf, obuf = pa.py_buffer(keys_h.numpy()), pa.py_buffer(data_h.numpy()), pa.py_buffer(offs_h.numpy())
+    blocks = []
+    for lo, hi in ranges:
+        m = hi - lo
+        c0 = pa.Array.from_buffers(pa.int64(), m, [None, kbuf.slice(lo * 8, m * 8)])
+        c1 = pa.Array.from_buffers(pa.binary(), m, [None, obuf.slice(0, (m + 1) * 4),
+                                                    dbuf.slice(lo * PAYLOAD, m * PAYLOAD)])
+        blocks.append(pa.table({"c_0": c0, "c_1": c1}))
+    return blocks, (keys_h, data_h, offs_h)
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    import __graft_entry__ as ge
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and local_rank != 0:
+        time.sleep(0.5)  # let local rank 0 win the (idempotent) build check
+    ge.build()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    from cluster_anywhere_b200 import SortKey, _cabi
+    from cluster_anywhere_b200 import device as dev
+    from cluster_anywhere_b200.exchange import DeviceExchange
+
+    lib = _cabi.load()
+    rt = dev.Runtime()
+    ex = DeviceExchange(rt)
+    n = args.rows_per_gpu
+    ds, keys, data = build_resident_dataset(rt, n, args.blocks_per_gpu, seed=2 + rank)
+    sk = SortKey("c_0")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def one_step(i):
+        if world > 1:
+            out = ex.sort_distributed(ds, sk, seed=i)
+        else:
+            out = ex.sort(ds, sk, seed=i)
+        return out
+
+    # ---- device-resident timing ----
+    for i in range(args.warmup):
+        out = one_step(i)
+        del out
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    lib.xchg_profile_enable(1)
+    launches0 = lib.xchg_launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for i in range(args.steps):
+        out = one_step(100 + i)
+        if i < args.steps - 1:
+            del out
+    ev1.record()
+    barrier()
+    launches = lib.xchg_launch_count() - launches0
+    lib.xchg_profile_enable(0)
+    clocks = sampler.stop() if rank == 0 else None
+    ms = ev0.elapsed_time(ev1)
+    tmax = torch.tensor([ms], dtype=torch.float64, device=rt.device)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    ms_per_step = float(tmax.item()) / args.steps
+    out_rows = torch.tensor([out.num_rows], dtype=torch.int64, device=rt.device)
+    if world > 1:
+        dist.all_reduce(out_rows)
+    assert int(out_rows.item()) == n * world, "rows lost in the exchange"
+    del out
+    total_rows = n * world
+    value = total_rows / (ms_per_step / 1e3)
+
+    # per-kernel device time over the timed region (rank 0's GPU)
+    import ctypes
+
+    kernels = []
+    for kid, name in KERNEL_NAMES.items():
+        tot, cnt = ctypes.c_double(), ctypes.c_uint64()
+        _cabi.check(lib.xchg_profile_read(kid, ctypes.byref(tot), ctypes.byref(cnt)))
+        if cnt.value:
+            kernels.append({"id": kid, "kernel": name, "launches_per_step": cnt.value / args.steps,
+                            "ms_per_step": tot.value / args.steps, "avg_launch_ms": tot.value / cnt.value})
+    kernels.sort(key=lambda k: -k["ms_per_step"])
+    peak, peak_src = peaks()
+    roofline = None
+    for k in kernels:
+        if k["id"] in KERNEL_BYTES_PER_ROW:
+            rows_per_launch = n  # every launch of these kernels covers the rank's n rows
+            bpl = KERNEL_BYTES_PER_ROW[k["id"]] * rows_per_launch
+            k["achieved_gbs"] = bpl / (k["avg_launch_ms"] * 1e-3) / 1e9
+            k["frac_of_peak"] = k["achieved_gbs"] / peak
+    dom = next((k for k in kernels if "achieved_gbs" in k), None)
+    if dom is not None:
+        roofline = {"bound": "hbm", "kernel": dom["kernel"], "achieved": dom["achieved_gbs"], "peak": peak,
+                    "unit": "GB/s", "frac": dom["achieved_gbs"] / peak, "traffic": None,
+                    "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": KERNEL_BYTES_PER_ROW[dom["id"]] * n,
+                    "share_of_step": dom["ms_per_step"] / ms_per_step}
+        tr = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tr):
+            try:
+                with open(tr) as f:
+                    roofline["traffic"] = json.load(f).get(dom["kernel"])
+            except Exception:
+                pass
+
+    # ---- end to end through the host-buffer API (pinned Arrow blocks in and out) ----
+    e2e = None
+    if not args.no_e2e and world == 1:
+        blocks, keep = host_blocks_from_device(rt, keys, data, ds.block_ranges)
+        h2d = sum(b.nbytes for b in blocks)
+        for i in range(max(1, min(args.warmup, 2))):
+            outs = ex.sort_blocks(blocks, sk, seed=i)
+            del outs
+        e_steps = max(1, min(args.steps, args.e2e_steps))
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        d2h = 0
+        for i in range(e_steps):
+            outs = ex.sort_blocks(blocks, sk, seed=100 + i)
+            d2h = sum(o.nbytes for o in outs)
+            rows = sum(o.num_rows for o in outs)
+            del outs
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / e_steps
+        assert rows == n
+        e2e = {"value": n / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+               "ms_per_step": dt * 1e3, "steps": e_steps,
+               "api": "DeviceExchange.sort_blocks(pinned host Arrow blocks) -> host Arrow blocks"}
+        del blocks, keep
+
+    # ---- CPU baseline (rank 0, N=1 only): bounded sample of the same workload ----
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        del ds, keys, data
+        torch.cuda.empty_cache()
+        cores = len(os.sched_getaffinity(0))
+        ref = CpuReference(cores, args.cpu_rows_per_block, args.cpu_blocks or cores)
+        try:
+            t_cpu = ref.step()
+            t_prim = ref.step(null_scan=False)
+        finally:
+            ref.close()
+        sample = (f"{ref.num_blocks} blocks x {ref.rows_per_block} GraySort rows "
+                  f"({ref.total_rows * ROW_BYTES / 1e9:.2f} GB), R={ref.num_blocks}, pull-based map/reduce on "
+                  f"{cores} processes, Arrow IPC hand-off in shared memory")
+        cpu = {"value": ref.total_rows / t_cpu, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": sample, "gb_per_s": ref.total_rows / t_cpu * 2 * ROW_BYTES / 1e9,
+               "primitives_only_value": ref.total_rows / t_prim}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": {"workload": workload_name(args), "rows_total": total_rows,
+                       "cache": "inputs (12.25 GB/GPU) far exceed the 126 MB L2; no flush needed",
+                       "partitioning": "range (sampled boundaries), R = number of input blocks"},
+            "gb_per_s_algorithmic": value * 2 * ROW_BYTES / 1e9,
+            "frac_of_hbm_roofline": value * 2 * ROW_BYTES / 1e9 / (peak * world),
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": roofline,
+            "kernels": kernels,
+            "e2e": e2e,
+            "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--rows-per-gpu", type=int, default=125_000_000)
+    ap.add_argument("--blocks-per-gpu", type=int, default=12)
+    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-rows-per-block", type=int, default=2_000_000)
+    ap.add_argument("--cpu-blocks", type=int, default=0, help="default: one block per host core")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "b200":
+        args.warmup = 3  # timing rule: at least 3 warm-up steps
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

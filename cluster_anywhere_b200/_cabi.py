@@ -25,6 +25,9 @@ _SIGNATURES = {
     "xchg_abi_version": (c_int, []),
     "xchg_last_error": (c_char_p, []),
     "xchg_device_count": (c_int, []),
+    "xchg_launch_count": (c_uint64, []),
+    "xchg_profile_enable": (c_int, [c_int]),
+    "xchg_profile_read": (c_int, [c_int, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(c_uint64)]),
     "xchg_sort_workspace_bytes": (c_int, [c_uint64, ctypes.POINTER(c_uint64)]),
     "xchg_sort_column": (c_int, [_P, c_int, c_int, _P, c_int64, _P, c_uint64, _P, _P, _P, c_uint64, _P]),
     "xchg_normalize_keys": (c_int, [_P, c_int, c_int, _P, c_int64, _P, c_uint64, _P, _P]),

@@ -1,6 +1,9 @@
 // C-ABI plumbing: thread-local error message, device queries.
 #include <cstdarg>
+#include <atomic>
 #include <cstdio>
+#include <mutex>
+#include <vector>
 
 #include "common.cuh"
 
@@ -34,4 +37,96 @@ extern "C" int xchg_device_count(void) {
     return 0;
   }
   return n;
+}
+
+// ---- measurement hooks ---------------------------------------------------------
+namespace {
+std::atomic<uint64_t> g_launches{0};
+std::atomic<int> g_prof_on{0};
+std::mutex g_prof_mu;
+struct Pending {
+  int id;
+  cudaEvent_t a, b;
+};
+std::vector<Pending> g_pending;
+std::vector<cudaEvent_t> g_free_events;
+double g_ms[XK_COUNT] = {0};
+uint64_t g_cnt[XK_COUNT] = {0};
+thread_local cudaEvent_t t_open = nullptr;
+constexpr size_t MAX_PENDING = 1 << 16;
+
+cudaEvent_t get_event() {
+  if (!g_free_events.empty()) {
+    cudaEvent_t e = g_free_events.back();
+    g_free_events.pop_back();
+    return e;
+  }
+  cudaEvent_t e = nullptr;
+  if (cudaEventCreate(&e) != cudaSuccess) return nullptr;
+  return e;
+}
+
+void drain_locked() {
+  for (auto& p : g_pending) {
+    float ms = 0.f;
+    if (cudaEventSynchronize(p.b) == cudaSuccess && cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) {
+      g_ms[p.id] += ms;
+      g_cnt[p.id] += 1;
+    }
+    g_free_events.push_back(p.a);
+    g_free_events.push_back(p.b);
+  }
+  g_pending.clear();
+}
+}  // namespace
+
+void xchg_prof_begin(int kernel_id, cudaStream_t s) {
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  t_open = nullptr;
+  if (!g_prof_on.load(std::memory_order_relaxed)) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (g_pending.size() >= MAX_PENDING) return;
+  cudaEvent_t e = get_event();
+  if (!e) return;
+  cudaEventRecord(e, s);
+  t_open = e;
+}
+
+void xchg_prof_end(int kernel_id, cudaStream_t s) {
+  if (!t_open) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  cudaEvent_t e = get_event();
+  if (!e) {
+    g_free_events.push_back(t_open);
+    t_open = nullptr;
+    return;
+  }
+  cudaEventRecord(e, s);
+  g_pending.push_back({kernel_id, t_open, e});
+  t_open = nullptr;
+}
+
+extern "C" uint64_t xchg_launch_count(void) { return g_launches.load(); }
+
+extern "C" int xchg_profile_enable(int on) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (on) {
+    drain_locked();
+    for (int i = 0; i < XK_COUNT; ++i) {
+      g_ms[i] = 0;
+      g_cnt[i] = 0;
+    }
+  }
+  g_prof_on.store(on ? 1 : 0);
+  return XCHG_OK;
+}
+
+extern "C" int xchg_profile_read(int kernel_id, double* total_ms, uint64_t* launches) {
+  XCHG_REQUIRE(kernel_id >= 0 && kernel_id < XK_COUNT, "bad kernel id %d", kernel_id);
+  XCHG_REQUIRE(total_ms && launches, "NULL out pointer");
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  drain_locked();
+  *total_ms = g_ms[kernel_id];
+  *launches = g_cnt[kernel_id];
+  return XCHG_OK;
 }

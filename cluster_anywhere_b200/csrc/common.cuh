@@ -54,3 +54,39 @@ __device__ __forceinline__ void st_stream_u4(uint4* p, const uint4& v) {
                "r"(v.y), "r"(v.z), "r"(v.w)
                : "memory");
 }
+
+// ---- measurement hooks (api.cu) ----------------------------------------------
+// Every kernel launch is counted; when profiling is enabled a launch is bracketed
+// by CUDA events on its own stream so bench.py can report per-kernel device time.
+enum XchgKernelId {
+  XK_NORMALIZE = 0,
+  XK_SCAN_HIST = 1,
+  XK_ONESWEEP = 2,
+  XK_GATHER_ROWS = 3,
+  XK_GATHER_FIXED = 4,
+  XK_GATHER_BITMAP = 5,
+  XK_GATHER_OFFSETS = 6,
+  XK_PARTITION = 7,
+  XK_OFFSETS_UTIL = 8,
+  XK_MISC = 9,
+  XK_MERGE = 10,
+  XK_SHUFFLE = 11,
+  XK_AGGREGATE = 12,
+  XK_COUNT = 13
+};
+
+void xchg_prof_begin(int kernel_id, cudaStream_t s);
+void xchg_prof_end(int kernel_id, cudaStream_t s);
+
+struct XchgProfScope {
+  int id;
+  cudaStream_t s;
+  XchgProfScope(int id_, cudaStream_t s_) : id(id_), s(s_) { xchg_prof_begin(id, s); }
+  ~XchgProfScope() { xchg_prof_end(id, s); }
+};
+
+#define XCHG_LAUNCH(id, stream, ...)      \
+  do {                                    \
+    XchgProfScope prof__((id), (stream)); \
+    __VA_ARGS__;                          \
+  } while (0)

@@ -371,15 +371,15 @@ extern "C" int xchg_gather_fixed(const void* in, uint32_t width, const uint32_t*
   const int g = grid_for(n_out, 256, 8);
   const uintptr_t al = (uintptr_t)in | (uintptr_t)out;
   if (width == 1) {
-    k_gather_fixed<uint8_t><<<g, 256, 0, s>>>((const uint8_t*)in, idx, n_out, (uint8_t*)out);
+    XCHG_LAUNCH(XK_GATHER_FIXED, s, k_gather_fixed<uint8_t><<<g, 256, 0, s>>>((const uint8_t*)in, idx, n_out, (uint8_t*)out));
   } else if (width == 2 && al % 2 == 0) {
-    k_gather_fixed<uint16_t><<<g, 256, 0, s>>>((const uint16_t*)in, idx, n_out, (uint16_t*)out);
+    XCHG_LAUNCH(XK_GATHER_FIXED, s, k_gather_fixed<uint16_t><<<g, 256, 0, s>>>((const uint16_t*)in, idx, n_out, (uint16_t*)out));
   } else if (width == 4 && al % 4 == 0) {
-    k_gather_fixed<uint32_t><<<g, 256, 0, s>>>((const uint32_t*)in, idx, n_out, (uint32_t*)out);
+    XCHG_LAUNCH(XK_GATHER_FIXED, s, k_gather_fixed<uint32_t><<<g, 256, 0, s>>>((const uint32_t*)in, idx, n_out, (uint32_t*)out));
   } else if (width == 8 && al % 8 == 0) {
-    k_gather_fixed<uint64_t><<<g, 256, 0, s>>>((const uint64_t*)in, idx, n_out, (uint64_t*)out);
+    XCHG_LAUNCH(XK_GATHER_FIXED, s, k_gather_fixed<uint64_t><<<g, 256, 0, s>>>((const uint64_t*)in, idx, n_out, (uint64_t*)out));
   } else if (width == 16 && al % 16 == 0) {
-    k_gather_fixed<Bytes16><<<g, 256, 0, s>>>((const Bytes16*)in, idx, n_out, (Bytes16*)out);
+    XCHG_LAUNCH(XK_GATHER_FIXED, s, k_gather_fixed<Bytes16><<<g, 256, 0, s>>>((const Bytes16*)in, idx, n_out, (Bytes16*)out));
   } else {
     return xchg_gather_rows((const uint8_t*)in, width, idx, n_out, (uint8_t*)out, stream);
   }
@@ -394,8 +394,8 @@ extern "C" int xchg_gather_bitmap(const uint8_t* in, int64_t in_bit_offset, cons
   XCHG_REQUIRE(in && idx && out, "NULL in / idx / out");
   XCHG_REQUIRE(((uintptr_t)out & 3) == 0, "bitmap output must be 4-byte aligned (and padded to 4 bytes)");
   const int g = grid_for(n_out, 256, 8);
-  k_gather_bitmap<<<g, 256, 0, (cudaStream_t)stream>>>(in, in_bit_offset, idx, n_out, (uint32_t*)out,
-                                                        (unsigned long long*)null_count_out);
+  XCHG_LAUNCH(XK_GATHER_BITMAP, (cudaStream_t)stream, k_gather_bitmap<<<g, 256, 0, (cudaStream_t)stream>>>(in, in_bit_offset, idx, n_out, (uint32_t*)out,
+                                                        (unsigned long long*)null_count_out));
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
 }
@@ -422,11 +422,11 @@ extern "C" int xchg_gather_offsets(const int64_t* in_off, const uint32_t* idx, u
     xchg_set_error("gather_offsets workspace too small");
     return XCHG_ERR_WORKSPACE;
   }
-  k_lengths_reduce<<<(unsigned)ntiles, SC_THREADS, 0, s>>>(in_off, idx, n_out, tiles);
+  XCHG_LAUNCH(XK_GATHER_OFFSETS, s, k_lengths_reduce<<<(unsigned)ntiles, SC_THREADS, 0, s>>>(in_off, idx, n_out, tiles));
   XCHG_LAUNCH_CHECK();
-  k_scan_tiles<<<1, SC_THREADS, 0, s>>>(tiles, ntiles);
+  XCHG_LAUNCH(XK_GATHER_OFFSETS, s, k_scan_tiles<<<1, SC_THREADS, 0, s>>>(tiles, ntiles));
   XCHG_LAUNCH_CHECK();
-  k_lengths_scan<<<(unsigned)ntiles, SC_THREADS, 0, s>>>(in_off, idx, n_out, tiles, out_off);
+  XCHG_LAUNCH(XK_GATHER_OFFSETS, s, k_lengths_scan<<<(unsigned)ntiles, SC_THREADS, 0, s>>>(in_off, idx, n_out, tiles, out_off));
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
 }
@@ -445,11 +445,11 @@ static int launch_gather_rows(bool uniform, const uint8_t* in, const int64_t* in
   const uint64_t ntiles = (n_out + rows_per_tile - 1) / rows_per_tile;
   const int grid = (int)std::min<uint64_t>(ntiles, (uint64_t)xchg_sm_count() * 3 * 4);
   if (uniform)
-    k_gather_rows<true><<<grid, GR_THREADS, GR_SMEM, s>>>(in, in_off, width, idx, n_out, out_off, out,
-                                                          rows_per_tile);
+    XCHG_LAUNCH(XK_GATHER_ROWS, s, k_gather_rows<true><<<grid, GR_THREADS, GR_SMEM, s>>>(in, in_off, width, idx, n_out, out_off, out,
+                                                          rows_per_tile));
   else
-    k_gather_rows<false><<<grid, GR_THREADS, GR_SMEM, s>>>(in, in_off, width, idx, n_out, out_off, out,
-                                                           rows_per_tile);
+    XCHG_LAUNCH(XK_GATHER_ROWS, s, k_gather_rows<false><<<grid, GR_THREADS, GR_SMEM, s>>>(in, in_off, width, idx, n_out, out_off, out,
+                                                           rows_per_tile));
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
 }
@@ -479,7 +479,7 @@ extern "C" int xchg_offsets_widen(const int32_t* in, uint64_t count, int64_t bas
                                   void* stream) {
   if (count == 0) return XCHG_OK;
   XCHG_REQUIRE(in && out, "NULL in / out");
-  k_offsets_widen<<<grid_for(count, 256, 8), 256, 0, (cudaStream_t)stream>>>(in, count, base, out);
+  XCHG_LAUNCH(XK_OFFSETS_UTIL, (cudaStream_t)stream, k_offsets_widen<<<grid_for(count, 256, 8), 256, 0, (cudaStream_t)stream>>>(in, count, base, out));
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
 }
@@ -487,7 +487,7 @@ extern "C" int xchg_offsets_widen(const int32_t* in, uint64_t count, int64_t bas
 extern "C" int xchg_offsets_narrow(const int64_t* in, uint64_t count, int32_t* out, void* stream) {
   if (count == 0) return XCHG_OK;
   XCHG_REQUIRE(in && out, "NULL in / out");
-  k_offsets_narrow<<<grid_for(count, 256, 8), 256, 0, (cudaStream_t)stream>>>(in, count, out);
+  XCHG_LAUNCH(XK_OFFSETS_UTIL, (cudaStream_t)stream, k_offsets_narrow<<<grid_for(count, 256, 8), 256, 0, (cudaStream_t)stream>>>(in, count, out));
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
 }
@@ -500,7 +500,7 @@ extern "C" int xchg_offsets_uniform32(uint64_t count, uint32_t width, int32_t* o
                    (unsigned long long)(count - 1), width);
     return XCHG_ERR_LIMIT;
   }
-  k_offsets_uniform32<<<grid_for(count, 256, 8), 256, 0, (cudaStream_t)stream>>>(count, width, out);
+  XCHG_LAUNCH(XK_OFFSETS_UTIL, (cudaStream_t)stream, k_offsets_uniform32<<<grid_for(count, 256, 8), 256, 0, (cudaStream_t)stream>>>(count, width, out));
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
 }
@@ -509,7 +509,7 @@ extern "C" int xchg_offsets_uniform64(uint64_t count, uint64_t width, int64_t ba
                                       void* stream) {
   if (count == 0) return XCHG_OK;
   XCHG_REQUIRE(out != nullptr, "NULL out");
-  k_offsets_uniform64<<<grid_for(count, 256, 8), 256, 0, (cudaStream_t)stream>>>(count, width, base, out);
+  XCHG_LAUNCH(XK_OFFSETS_UTIL, (cudaStream_t)stream, k_offsets_uniform64<<<grid_for(count, 256, 8), 256, 0, (cudaStream_t)stream>>>(count, width, base, out));
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
 }
@@ -518,8 +518,8 @@ extern "C" int xchg_offsets_check_uniform(const int64_t* off, uint64_t n_rows, u
                                           uint32_t* flag_out, void* stream) {
   if (n_rows == 0) return XCHG_OK;
   XCHG_REQUIRE(off && flag_out, "NULL off / flag_out");
-  k_offsets_check_uniform<<<grid_for(n_rows, 256, 8), 256, 0, (cudaStream_t)stream>>>(off, n_rows, width,
-                                                                                     flag_out);
+  XCHG_LAUNCH(XK_OFFSETS_UTIL, (cudaStream_t)stream, k_offsets_check_uniform<<<grid_for(n_rows, 256, 8), 256, 0, (cudaStream_t)stream>>>(off, n_rows, width,
+                                                                                     flag_out));
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
 }

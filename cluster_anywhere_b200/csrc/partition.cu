@@ -131,8 +131,8 @@ extern "C" int xchg_partition_bounds(const uint64_t* const* norm_cols_host,
     cp.has_last[c] = c < ncols ? has_last_host[c] : 0;
   }
   for (int c = 0; c < ncols; ++c) XCHG_REQUIRE(n == 0 || cp.c[c], "NULL key column %d", c);
-  k_partition_bounds<<<(nb + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
-      cp, ncols, n, lower, upper, flags, nb, first_descending, cuts_out);
+  XCHG_LAUNCH(XK_PARTITION, (cudaStream_t)stream, k_partition_bounds<<<(nb + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+      cp, ncols, n, lower, upper, flags, nb, first_descending, cuts_out));
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
 }

@@ -346,7 +346,7 @@ template <typename T>
 void launch_normalize(const void* keys, const uint32_t* perm, const uint8_t* validity, int64_t vbit,
                       uint32_t n, int desc, uint64_t* out, uint32_t* ghist, cudaStream_t s) {
   int blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)xchg_sm_count() * 8);
-  k_normalize_hist<T><<<blocks, 256, 0, s>>>((const T*)keys, perm, validity, vbit, n, desc, out, ghist);
+  XCHG_LAUNCH(XK_NORMALIZE, s, k_normalize_hist<T><<<blocks, 256, 0, s>>>((const T*)keys, perm, validity, vbit, n, desc, out, ghist));
 }
 
 int dispatch_normalize(const void* keys, int key_type, const uint32_t* perm, const uint8_t* validity,
@@ -386,16 +386,16 @@ int xchg_internal_onesweep_pass(int mode, const uint64_t* kin, const uint32_t* v
                                          (int)RS_SMEM));
       attr_done[0] = true;
     }
-    k_onesweep<0><<<ntiles, RS_THREADS, RS_SMEM, s>>>(kin, vin, kout, vout, n, shift, gexcl, status,
-                                                      tile_counter, validity, vbit);
+    XCHG_LAUNCH(XK_ONESWEEP, s, k_onesweep<0><<<ntiles, RS_THREADS, RS_SMEM, s>>>(kin, vin, kout, vout, n, shift, gexcl, status,
+                                                      tile_counter, validity, vbit));
   } else {
     if (!attr_done[1]) {
       XCHG_CUDA_TRY(cudaFuncSetAttribute(k_onesweep<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)RS_SMEM));
       attr_done[1] = true;
     }
-    k_onesweep<1><<<ntiles, RS_THREADS, RS_SMEM, s>>>(kin, vin, kout, vout, n, shift, gexcl, status,
-                                                      tile_counter, validity, vbit);
+    XCHG_LAUNCH(XK_ONESWEEP, s, k_onesweep<1><<<ntiles, RS_THREADS, RS_SMEM, s>>>(kin, vin, kout, vout, n, shift, gexcl, status,
+                                                      tile_counter, validity, vbit));
   }
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
@@ -451,7 +451,7 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
   int rc = dispatch_normalize(keys, key_type, perm_in, validity, validity_bit_offset, n32, descending,
                               w.norm, w.ghist, s);
   if (rc) return rc;
-  k_scan_hist<<<1, BINS, 0, s>>>(w.ghist, w.gexcl, w.active, n32);
+  XCHG_LAUNCH(XK_SCAN_HIST, s, k_scan_hist<<<1, BINS, 0, s>>>(w.ghist, w.gexcl, w.active, n32));
   XCHG_LAUNCH_CHECK();
   uint32_t active[NUM_PLACES];
   XCHG_CUDA_TRY(cudaMemcpyAsync(active, w.active, sizeof(active), cudaMemcpyDeviceToHost, s));
@@ -468,7 +468,7 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
   if (np == 0) {
     // every key equal: the stable order is the input order
     int blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)xchg_sm_count() * 8);
-    k_iota_or_copy<<<blocks, 256, 0, s>>>(perm_in, perm_out, n32);
+    XCHG_LAUNCH(XK_MISC, s, k_iota_or_copy<<<blocks, 256, 0, s>>>(perm_in, perm_out, n32));
     XCHG_LAUNCH_CHECK();
     if (norm_keys_out)
       XCHG_CUDA_TRY(cudaMemcpyAsync(norm_keys_out, w.norm, n * 8, cudaMemcpyDeviceToDevice, s));

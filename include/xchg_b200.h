@@ -57,6 +57,19 @@ const char* xchg_last_error(void);
 /* Number of visible CUDA devices (0 if none; never fails). */
 int xchg_device_count(void);
 
+/* ------------------------------------------------------- measurement ---- */
+/* No counterpart in the reference (it reports wall-clock task stats,
+ * python/ray/data/block.py:141-207).  Kernels launched by this library since
+ * load; and optional per-kernel device timing: while enabled, every launch is
+ * bracketed by CUDA events on its stream; xchg_profile_read synchronises the
+ * recorded events and returns the accumulated milliseconds / launch count of one
+ * kernel class (ids: 0 normalize+hist, 1 scan_hist, 2 onesweep pass, 3 row
+ * gather, 4 fixed gather, 5 bitmap gather, 6 offsets scan, 7 partition bounds,
+ * 8 offsets utilities, 9 misc, 10 merge, 11 shuffle, 12 aggregate). */
+uint64_t xchg_launch_count(void);
+int xchg_profile_enable(int on);
+int xchg_profile_read(int kernel_id, double* total_ms, uint64_t* launches);
+
 /* ---------------------------------------------------------------- sort ---- */
 
 /* Workspace bytes xchg_sort_column needs for n rows. */
