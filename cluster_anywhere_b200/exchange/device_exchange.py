@@ -70,9 +70,17 @@ class DeviceExchange:
         """HBM -> host Arrow blocks (pinned host buffers, one per output block)."""
         if ds.table is None:
             return [empty_table() for _ in ds.block_ranges]
-        whole = dev.export_table(self.rt, ds.table)
-        return [whole[lo:hi] if hi > lo else (whole[0:0] if ds.table.num_rows else empty_table())
-                for lo, hi in ds.block_ranges]
+        # every block gets its own Arrow buffers (own int32 offsets: a block stays
+        # under 2 GiB per column even when the device table does not); all copies
+        # are queued first, then one stream synchronisation
+        rt, t = self.rt, ds.table
+        builders = []
+        for lo, hi in ds.block_ranges:
+            if hi <= lo:
+                lo = hi = 0
+            builders.append([dev._export_buffers(rt, c, lo, hi, []) for c in t.columns])
+        rt.synchronize()
+        return [pa.Table.from_arrays([b() for b in bs], schema=t.schema) for bs in builders]
 
     # -- sort --------------------------------------------------------------------
     def sample_boundaries(self, ds: DeviceDataset, sort_key: SortKey, num_reducers: int,
