@@ -12,6 +12,7 @@
 // consecutive in the output, so the writes of a tile form one dense stream.
 // Algorithmic bytes: 2 x row bytes (+4 B index, +16 B offsets for var-width).
 #include <algorithm>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -520,6 +521,89 @@ extern "C" int xchg_offsets_check_uniform(const int64_t* off, uint64_t n_rows, u
   XCHG_REQUIRE(off && flag_out, "NULL off / flag_out");
   XCHG_LAUNCH(XK_OFFSETS_UTIL, (cudaStream_t)stream, k_offsets_check_uniform<<<grid_for(n_rows, 256, 8), 256, 0, (cudaStream_t)stream>>>(off, n_rows, width,
                                                                                      flag_out));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+// ------------------------------------------------- allocation-free variant ---
+//
+// xchg_gather_offsets_static: same result as xchg_gather_offsets, but the scan's
+// scratch (one int64 partial sum per 2048-row tile) lives in a fixed array inside
+// the library image instead of a caller-supplied workspace.
+//
+// Who needs it: hosts that receive their input and output device buffers from
+// somebody else and own no device allocator themselves -- a plain ctypes/cffi
+// embedding inside a worker whose GPU memory has been handed over wholesale to
+// another component's pool (a framework caching allocator, an RMM-style arena), or
+// a latency-critical stage that must not call cudaMalloc/cudaFree because those
+// calls serialise with all work on the device.  Such callers can pass the buffers
+// they were given, but cannot produce an extra workspace.
+//
+// Cost and limits: the array (XCHG_STATIC_GATHER_MAX_ROWS / 2048 x 8 bytes =
+// 256 KiB) is part of every CUDA context that loads this library and is held
+// until the process exits.  Requests above XCHG_STATIC_GATHER_MAX_ROWS are
+// refused.  All calls on a device share the one array: two calls whose kernels
+// may overlap on the GPU (different streams, or different host threads on
+// different streams) race on it -- serialise them.  Nothing in the array has to
+// start at zero: every slot a call reads was written earlier by that same call,
+// so contents left behind by the previous call are harmless.
+//
+// Set-up: the array's name is only a host-side handle.  The first call on each
+// device (with that device current) resolves its device address with
+// cudaGetSymbolAddress and caches it; make that first call outside any stream
+// capture.
+constexpr uint64_t STATIC_MAX_TILES = XCHG_STATIC_GATHER_MAX_ROWS / SC_TILE;
+static_assert(XCHG_STATIC_GATHER_MAX_ROWS % SC_TILE == 0, "limit must be a whole number of tiles");
+
+static __device__ __align__(256) int64_t g_static_tile_sums[STATIC_MAX_TILES];
+
+namespace {
+constexpr int MAX_DEVICES = 64;
+std::mutex g_static_mu;
+int64_t* g_static_addr[MAX_DEVICES] = {nullptr};
+
+// Device address of g_static_tile_sums on the current device (resolved once).
+int static_scratch(int64_t** out) {
+  int dev = -1;
+  XCHG_CUDA_TRY(cudaGetDevice(&dev));
+  XCHG_REQUIRE(dev >= 0 && dev < MAX_DEVICES, "device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (g_static_addr[dev] == nullptr) {
+    int64_t* ptr = nullptr;
+    XCHG_CUDA_TRY(cudaGetSymbolAddress((void**)&ptr, g_static_tile_sums));
+    XCHG_REQUIRE(ptr != nullptr, "cudaGetSymbolAddress returned NULL");
+    g_static_addr[dev] = ptr;
+  }
+  *out = g_static_addr[dev];
+  return XCHG_OK;
+}
+}  // namespace
+
+extern "C" int xchg_gather_offsets_static(const int64_t* in_off, const uint32_t* idx,
+                                          uint64_t n_out, int64_t* out_off, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  XCHG_REQUIRE(out_off != nullptr, "out_off is NULL");
+  if (n_out > XCHG_STATIC_GATHER_MAX_ROWS) {
+    xchg_set_error("xchg_gather_offsets_static: n_out=%llu exceeds the built-in scratch "
+                   "(XCHG_STATIC_GATHER_MAX_ROWS=%llu rows); use xchg_gather_offsets with a "
+                   "caller workspace instead",
+                   (unsigned long long)n_out, (unsigned long long)XCHG_STATIC_GATHER_MAX_ROWS);
+    return XCHG_ERR_LIMIT;
+  }
+  if (n_out == 0) {
+    XCHG_CUDA_TRY(cudaMemsetAsync(out_off, 0, 8, s));
+    return XCHG_OK;
+  }
+  XCHG_REQUIRE(in_off && idx, "NULL in_off / idx");
+  int64_t* tiles = nullptr;
+  int rc = static_scratch(&tiles);
+  if (rc) return rc;
+  const uint64_t ntiles = (n_out + SC_TILE - 1) / SC_TILE;
+  XCHG_LAUNCH(XK_GATHER_OFFSETS, s, k_lengths_reduce<<<(unsigned)ntiles, SC_THREADS, 0, s>>>(in_off, idx, n_out, tiles));
+  XCHG_LAUNCH_CHECK();
+  XCHG_LAUNCH(XK_GATHER_OFFSETS, s, k_scan_tiles<<<1, SC_THREADS, 0, s>>>(tiles, ntiles));
+  XCHG_LAUNCH_CHECK();
+  XCHG_LAUNCH(XK_GATHER_OFFSETS, s, k_lengths_scan<<<(unsigned)ntiles, SC_THREADS, 0, s>>>(in_off, idx, n_out, tiles, out_off));
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
 }

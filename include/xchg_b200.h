@@ -168,6 +168,24 @@ int xchg_gather_offsets_workspace_bytes(uint64_t n_out, uint64_t* bytes_out);
 int xchg_gather_offsets(const int64_t* in_off, const uint32_t* idx, uint64_t n_out,
                         int64_t* out_off, void* workspace, uint64_t workspace_bytes,
                         void* stream);
+/*
+ * Allocation-free form of xchg_gather_offsets (no counterpart in the reference).
+ * For hosts that are handed their device buffers by another component and have
+ * no way to obtain scratch memory themselves (all device memory belongs to a
+ * foreign pool, or cudaMalloc's device-wide serialisation is unacceptable in
+ * their loop): the scan's scratch is a fixed 256 KiB array inside the library
+ * image, resident in every context that loads the library until exit.
+ *  - n_out above XCHG_STATIC_GATHER_MAX_ROWS is refused with XCHG_ERR_LIMIT.
+ *  - All calls on a device share that array; calls whose kernels may overlap on
+ *    the GPU race on it, so serialise them.  Left-over contents of an earlier
+ *    call are harmless (each call overwrites every slot before reading it).
+ *  - The first call on each device resolves the array's device address; make it
+ *    outside any stream capture, with the target device current.
+ * Output is identical to xchg_gather_offsets.
+ */
+#define XCHG_STATIC_GATHER_MAX_ROWS ((uint64_t)(64u << 20))
+int xchg_gather_offsets_static(const int64_t* in_off, const uint32_t* idx, uint64_t n_out,
+                               int64_t* out_off, void* stream);
 int xchg_gather_bytes(const uint8_t* in_data, const int64_t* in_off, const uint32_t* idx,
                       uint64_t n_out, const int64_t* out_off, uint8_t* out_data,
                       void* stream);
