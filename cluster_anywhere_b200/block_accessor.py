@@ -27,6 +27,11 @@ def _device_sort(rt: dev.Runtime, dt: dev.DeviceTable, sort_key: SortKey, want_n
     return dev.sort_permutation(rt, dt, sort_key.get_columns(), sort_key.get_descending(), want_norm)
 
 
+def _presorted(sort_key: SortKey, norms):
+    """Primary key column -> its radix keys in output order (see dev.take_table)."""
+    return {sort_key.get_columns()[0]: (norms[0], sort_key.get_descending()[0])}
+
+
 def _cuts_for(rt: dev.Runtime, dt: dev.DeviceTable, norms, boundaries, sort_key: SortKey) -> List[int]:
     cols, desc = sort_key.get_columns(), sort_key.get_descending()
     ktypes = [dev.key_type_of(dt.column(c).type) for c in cols]
@@ -141,8 +146,8 @@ class B200ArrowBlockAccessor:
         sort_key.validate_schema(self._table.schema)
         rt = self.rt
         dt = dev.stage_table(rt, self._table)
-        perm, _ = _device_sort(rt, dt, sort_key, False)
-        return dev.export_table(rt, dev.take_table(rt, dt, perm, dt.num_rows))
+        perm, norms = _device_sort(rt, dt, sort_key, False)
+        return dev.export_table(rt, dev.take_table(rt, dt, perm, dt.num_rows, _presorted(sort_key, norms)))
 
     def sort_and_partition(self, boundaries: List[tuple], sort_key: SortKey) -> List[pa.Table]:
         """arrow_block.py:440-450: sort, then ``len(boundaries)+1`` range partitions
@@ -156,7 +161,7 @@ class B200ArrowBlockAccessor:
         dt = dev.stage_table(rt, self._table)
         want = len(boundaries) > 0
         perm, norms = _device_sort(rt, dt, sort_key, want)
-        sorted_dt = dev.take_table(rt, dt, perm, dt.num_rows)
+        sorted_dt = dev.take_table(rt, dt, perm, dt.num_rows, _presorted(sort_key, norms))
         if not want:
             return [dev.export_table(rt, sorted_dt)]
         cuts = _cuts_for(rt, dt, norms, boundaries, sort_key)

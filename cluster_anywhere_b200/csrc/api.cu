@@ -130,3 +130,9 @@ extern "C" int xchg_profile_read(int kernel_id, double* total_ms, uint64_t* laun
   *launches = g_cnt[kernel_id];
   return XCHG_OK;
 }
+
+extern "C" int xchg_set_l2_fetch_granularity(int bytes) {
+  XCHG_REQUIRE(bytes == 32 || bytes == 64 || bytes == 128, "granularity must be 32, 64 or 128");
+  XCHG_CUDA_TRY(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)bytes));
+  return XCHG_OK;
+}

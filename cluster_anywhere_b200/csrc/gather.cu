@@ -362,6 +362,8 @@ struct alignas(16) Bytes16 {
 
 extern "C" int xchg_gather_rows(const uint8_t* in_data, uint32_t width, const uint32_t* idx,
                                 uint64_t n_out, uint8_t* out_data, void* stream);
+int xchg_internal_gather_rows_uniform(const uint8_t* in, uint32_t w, const uint32_t* idx,
+                                      uint64_t n_out, uint8_t* out, cudaStream_t s);
 
 extern "C" int xchg_gather_fixed(const void* in, uint32_t width, const uint32_t* idx, uint64_t n_out,
                                  void* out, void* stream) {
@@ -459,6 +461,12 @@ extern "C" int xchg_gather_rows(const uint8_t* in_data, uint32_t width, const ui
                                 uint64_t n_out, uint8_t* out_data, void* stream) {
   if (n_out == 0 || width == 0) return XCHG_OK;
   XCHG_REQUIRE(in_data && idx && out_data, "NULL in / idx / out");
+  {
+    // flat word-per-thread kernel (gather_uniform.cu); rc 1 = row too wide for it
+    const int rc = xchg_internal_gather_rows_uniform(in_data, width, idx, n_out, out_data,
+                                                     (cudaStream_t)stream);
+    if (rc != 1) return rc;
+  }
   // rows per tile: fill the staging buffer (slot <= width + 30 bytes)
   const uint32_t slot = (width + 15u + 15u) & ~15u;
   uint32_t rpt = std::max<uint32_t>(1, std::min<uint32_t>(GR_MAX_ROWS, GR_STAGE / slot));

@@ -1,0 +1,160 @@
+// K5, uniform-width rows (GraySort 90-byte payloads, 1 KiB tensor rows): the
+// payload hot loop of Dataset.sort / random_shuffle.  Replaces Table.take on the
+// payload column (python/ray/data/_internal/arrow_ops/transform_pyarrow.py:45-71).
+//
+// out row i = in row idx[i], every row `w` bytes.  Per CTA and tile of T rows:
+//   phase 0  idx -> source byte offsets in shared memory (coalesced);
+//   phase 1  every 16-byte window of every source row -> stage via cp.async.cg, the
+//            row keeping its source alignment inside a fixed slot (no registers
+//            held while the random reads are in flight: T*ceil16(w+15) bytes of
+//            loads outstanding per CTA, 3 CTAs per SM);
+//   phase 2  FLAT mapping: thread q produces the q-th 4-byte-aligned word of the
+//            tile's contiguous output range; row = word_byte / w by multiply-high,
+//            two aligned LDS + one funnel shift re-align source to destination;
+//            words that straddle two rows are assembled bytewise.  Stores are dense
+//            128-byte warp writes.
+// The first round-1 version used one warp per row for phase 2 (105 warp
+// instructions per 90-byte row, issue-bound at 1.3 TB/s, profiles/r01_summary.md);
+// this mapping needs ~10.
+// Algorithmic bytes: 2*w + 4 per row.  Rows whose width and both base pointers are
+// multiples of 16 take the vector variant (16-byte words, no re-alignment).
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int GU_THREADS = 256;
+constexpr int GU_STAGE = 56 * 1024;
+constexpr int GU_MAX_ROWS = 1024;
+// stage | pad | int64 src[GU_MAX_ROWS] | uint32 a0[GU_MAX_ROWS]
+constexpr size_t GU_SMEM = GU_STAGE + 32 + (size_t)GU_MAX_ROWS * (8 + 4);
+
+__device__ __forceinline__ void cp_async16_cg(uint32_t smem_addr, const void* g) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async_drain() {
+  asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
+// x / d for a precomputed magic = ceil(2^32 / d); magic == 0 encodes d == 1
+__device__ __forceinline__ uint32_t udiv_magic(uint32_t x, uint32_t magic) {
+  return magic ? __umulhi(x, magic) : x;
+}
+
+template <bool VEC16>
+__global__ void __launch_bounds__(GU_THREADS)
+k_gather_rows_uniform(const uint8_t* __restrict__ in, uint32_t w, const uint32_t* __restrict__ idx,
+                      uint64_t n_out, uint8_t* __restrict__ out, uint32_t rows_per_tile,
+                      uint32_t slot, uint32_t magic_w, uint32_t magic_cpr) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  uint8_t* stage = smem;
+  int64_t* m_src = reinterpret_cast<int64_t*>(smem + GU_STAGE + 32);
+  uint32_t* m_a0 = reinterpret_cast<uint32_t*>(m_src + GU_MAX_ROWS);
+  const uint32_t stage_s = (uint32_t)__cvta_generic_to_shared(stage);
+  const int tid = threadIdx.x;
+  const uint64_t ntiles = (n_out + rows_per_tile - 1) / rows_per_tile;
+  const uint32_t cpr = slot >> 4;  // 16-byte chunks per slot
+
+  for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const uint64_t r0 = tile * rows_per_tile;
+    const uint32_t T = (uint32_t)min((uint64_t)rows_per_tile, n_out - r0);
+
+    // ---- phase 0 ----
+    for (uint32_t j = tid; j < T; j += GU_THREADS) {
+      const int64_t s = (int64_t)idx[r0 + j] * w;
+      m_src[j] = s;
+      m_a0[j] = j * slot + (VEC16 ? 0u : (uint32_t)(((uintptr_t)in + s) & 15));
+    }
+    __syncthreads();
+
+    // ---- phase 1: global -> stage ----
+    const uint32_t nchunks = T * cpr;
+    for (uint32_t c = tid; c < nchunks; c += GU_THREADS) {
+      const uint32_t j = udiv_magic(c, magic_cpr);
+      const uint32_t k = c - j * cpr;
+      const uint8_t* g = in + m_src[j];
+      const uint32_t mis = VEC16 ? 0u : (uint32_t)((uintptr_t)g & 15);
+      if (16 * k < mis + w) cp_async16_cg(stage_s + j * slot + 16 * k, g - mis + 16 * (size_t)k);
+    }
+    cp_async_drain();
+    __syncthreads();
+
+    // ---- phase 2: stage -> global ----
+    uint8_t* o = out + r0 * w;  // the tile's output range is contiguous
+    const uint32_t nbytes = T * w;
+    if constexpr (VEC16) {
+      // slot == w, everything 16-byte aligned: the stage IS the output layout
+      const uint4* s4 = reinterpret_cast<const uint4*>(stage);
+      uint4* o4 = reinterpret_cast<uint4*>(o);
+      for (uint32_t q = tid; q < (nbytes >> 4); q += GU_THREADS) o4[q] = s4[q];
+    } else {
+      const uint32_t head = min(nbytes, (uint32_t)((4 - ((uintptr_t)o & 3)) & 3));
+      const uint32_t nwords = (nbytes - head) >> 2;
+      const uint32_t tail0 = head + (nwords << 2);
+      uint32_t* ow = reinterpret_cast<uint32_t*>(o + head);
+      const uint32_t* sw = reinterpret_cast<const uint32_t*>(stage);
+      for (uint32_t q = tid; q < nwords; q += GU_THREADS) {
+        const uint32_t t = head + (q << 2);  // tile-relative byte of this word
+        const uint32_t j = udiv_magic(t, magic_w);
+        const uint32_t r = t - j * w;
+        uint32_t v;
+        if (r + 4 <= w) {
+          const uint32_t a = m_a0[j] + r;
+          v = __funnelshift_r(sw[a >> 2], sw[(a >> 2) + 1], (a & 3) * 8);
+        } else {
+          v = 0;
+#pragma unroll
+          for (uint32_t b = 0; b < 4; ++b) {
+            uint32_t jb = j, rb = r + b;
+            while (rb >= w) {  // w < 4 can put several rows into one word
+              rb -= w;
+              ++jb;
+            }
+            v |= (uint32_t)stage[m_a0[jb] + rb] << (8 * b);
+          }
+        }
+        ow[q] = v;
+      }
+      // head and tail bytes of the tile (at most 3 each)
+      if ((uint32_t)tid < head + (nbytes - tail0)) {
+        const uint32_t t = (uint32_t)tid < head ? (uint32_t)tid : tail0 + ((uint32_t)tid - head);
+        const uint32_t j = udiv_magic(t, magic_w);
+        o[t] = stage[m_a0[j] + (t - j * w)];
+      }
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace
+
+int xchg_internal_gather_rows_uniform(const uint8_t* in, uint32_t w, const uint32_t* idx,
+                                      uint64_t n_out, uint8_t* out, cudaStream_t s) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<false>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GU_SMEM));
+    XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<true>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GU_SMEM));
+    attr_done = true;
+  }
+  const bool vec16 = (w % 16 == 0) && ((((uintptr_t)in) | ((uintptr_t)out)) % 16 == 0);
+  const uint32_t slot = vec16 ? w : ((w + 15u + 15u) & ~15u);
+  const uint32_t rpt = std::min<uint32_t>(GU_MAX_ROWS, GU_STAGE / slot);
+  if (rpt == 0) return 1;  // row wider than the stage: caller takes the generic path
+  const uint32_t cpr = slot >> 4;
+  // exact for every dividend below 2^32 / divisor, which bounds all uses (tile bytes, chunks)
+  const uint32_t magic_w = w == 1 ? 0u : (uint32_t)((0x100000000ull + w - 1) / w);
+  const uint32_t magic_cpr = cpr == 1 ? 0u : (uint32_t)((0x100000000ull + cpr - 1) / cpr);
+  const uint64_t ntiles = (n_out + rpt - 1) / rpt;
+  const int grid = (int)std::min<uint64_t>(ntiles, (uint64_t)xchg_sm_count() * 3 * 8);
+  if (vec16)
+    XCHG_LAUNCH(XK_GATHER_ROWS, s, k_gather_rows_uniform<true><<<grid, GU_THREADS, GU_SMEM, s>>>(
+        in, w, idx, n_out, out, rpt, slot, magic_w, magic_cpr));
+  else
+    XCHG_LAUNCH(XK_GATHER_ROWS, s, k_gather_rows_uniform<false><<<grid, GU_THREADS, GU_SMEM, s>>>(
+        in, w, idx, n_out, out, rpt, slot, magic_w, magic_cpr));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}

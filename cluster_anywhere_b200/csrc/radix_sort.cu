@@ -196,32 +196,50 @@ k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ va
   }
 
   // ---- rank inside the warp, in (i, lane) = memory order: stable ----
+  // Eight items at a time, three independent sweeps (match masks, leader atomics on
+  // the warp's private counters, broadcasts) so that the ~30-cycle shared-memory
+  // round trips of different items overlap instead of forming one serial chain per
+  // item (the first version did: 52 % short-scoreboard stalls, profiles/r01_summary.md).
+  // The atomics of successive items are issued in program order by one warp to its
+  // own counter row, so equal digits receive increasing bases in item order.
   uint32_t* myhist = whist + warp * BINS;
   uint32_t rank[RS_ITEMS];
+  const unsigned lt_mask = lanemask_lt();
 #pragma unroll
-  for (int i = 0; i < RS_ITEMS; ++i) {
-    const uint32_t d = digit_of<MODE>(key[i], val[i], shift, validity, vbit);
-    const unsigned m = __match_any_sync(0xffffffffu, d);
-    const int leader = __ffs(m) - 1;
-    uint32_t prev = 0;
-    if (lane == leader) {
-      prev = myhist[d];
-      myhist[d] = prev + (uint32_t)__popc(m);
+  for (int h = 0; h < RS_ITEMS; h += 8) {
+    uint32_t info[8];  // leader | lanes-before-me << 8 | group size << 16
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const uint32_t d = digit_of<MODE>(key[h + u], val[h + u], shift, validity, vbit);
+      const unsigned m = __match_any_sync(0xffffffffu, d);
+      info[u] = (uint32_t)(__ffs(m) - 1) | ((uint32_t)__popc(m & lt_mask) << 8) |
+                ((uint32_t)__popc(m) << 16);
     }
-    prev = __shfl_sync(0xffffffffu, prev, leader);
-    rank[i] = prev + (uint32_t)__popc(m & lanemask_lt());
-    __syncwarp();
+    uint32_t prev[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      prev[u] = 0;
+      if (lane == (int)(info[u] & 31u)) {
+        const uint32_t d = digit_of<MODE>(key[h + u], val[h + u], shift, validity, vbit);
+        prev[u] = atomicAdd(&myhist[d], info[u] >> 16);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      rank[h + u] = __shfl_sync(0xffffffffu, prev[u], (int)(info[u] & 31u)) + ((info[u] >> 8) & 63u);
   }
   __syncthreads();
 
   // ---- per digit: exclusive offsets across warps, tile totals, digit scan ----
   uint32_t total = 0, incl = 0;
   if (tid < BINS) {
+    uint32_t c[RS_WARPS];
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; ++w) c[w] = whist[w * BINS + tid];
 #pragma unroll
     for (int w = 0; w < RS_WARPS; ++w) {
-      const uint32_t c = whist[w * BINS + tid];
       whist[w * BINS + tid] = total;
-      total += c;
+      total += c[w];
     }
     incl = total;
 #pragma unroll
@@ -299,6 +317,21 @@ k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ va
       keys_out[g] = k;
       vals_out[g] = v;
     }
+  }
+}
+
+// Inverse of norm_value for integer keys: sorted radix keys -> sorted raw keys
+// (sequential, instead of a random gather of the key column through the permutation).
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_denormalize(const uint64_t* __restrict__ norm, uint32_t n, int desc, T* __restrict__ out) {
+  using U = typename std::make_unsigned<T>::type;
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    U u = (U)norm[i];
+    if (desc) u = (U)~u;
+    if constexpr (std::is_signed<T>::value) u ^= (U)((U)1 << (sizeof(T) * 8 - 1));
+    out[i] = (T)u;
   }
 }
 
@@ -490,5 +523,37 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
     kin = kout;
     vin = vout;
   }
+  return XCHG_OK;
+}
+
+extern "C" int xchg_denormalize_keys(const uint64_t* norm, int key_type, int descending, uint64_t n,
+                                     void* out, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  if (n == 0) return XCHG_OK;
+  XCHG_REQUIRE(norm && out, "NULL norm / out");
+  if (n > XCHG_MAX_ROWS) {
+    xchg_set_error("n=%llu exceeds XCHG_MAX_ROWS", (unsigned long long)n);
+    return XCHG_ERR_LIMIT;
+  }
+  const uint32_t n32 = (uint32_t)n;
+  const int blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)xchg_sm_count() * 8);
+#define XCHG_DENORM(T) \
+  XCHG_LAUNCH(XK_NORMALIZE, s, k_denormalize<T><<<blocks, 256, 0, s>>>(norm, n32, descending, (T*)out))
+  switch (key_type) {
+    case XCHG_I8: XCHG_DENORM(int8_t); break;
+    case XCHG_I16: XCHG_DENORM(int16_t); break;
+    case XCHG_I32: XCHG_DENORM(int32_t); break;
+    case XCHG_I64: XCHG_DENORM(int64_t); break;
+    case XCHG_U8: XCHG_DENORM(uint8_t); break;
+    case XCHG_U16: XCHG_DENORM(uint16_t); break;
+    case XCHG_U32: XCHG_DENORM(uint32_t); break;
+    case XCHG_U64: XCHG_DENORM(uint64_t); break;
+    default:
+      xchg_set_error("xchg_denormalize_keys: integer key types only (float keys keep NaN payloads and "
+                     "signed zeros only through a gather), got %d", key_type);
+      return XCHG_ERR_INVALID;
+  }
+#undef XCHG_DENORM
+  XCHG_LAUNCH_CHECK();
   return XCHG_OK;
 }

@@ -20,6 +20,7 @@ Device layout of a column (SoA, one allocation per buffer):
 from __future__ import annotations
 
 import ctypes
+import os
 import warnings
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Sequence
@@ -58,6 +59,12 @@ class Runtime:
         if not self.is_cuda and _cabi._test_double is None:
             raise XchgError("CPU device requested but the engine has no CPU path")
         self.launches = 0  # kernels launched through this runtime (bench bookkeeping)
+        if self.is_cuda:
+            # random row / key gathers: fetch sectors, not 128-byte lines, from HBM
+            gran = int(os.environ.get("XCHG_L2_FETCH_GRANULARITY", "32"))
+            if gran:
+                with torch.cuda.device(self.device):
+                    _cabi.call("xchg_set_l2_fetch_granularity", gran)
 
     # -- allocation ---------------------------------------------------------
     def empty(self, n: int, dtype=torch.uint8) -> torch.Tensor:
@@ -367,9 +374,36 @@ def take_column(rt: Runtime, col: DeviceColumn, idx: torch.Tensor, n_out: int) -
     return DeviceColumn(col.type, n_out, "var", col.width, out, out_off, validity, null_count)
 
 
-def take_table(rt: Runtime, table: DeviceTable, idx: torch.Tensor, n_out: Optional[int] = None) -> DeviceTable:
+def _is_int_key(kt: int) -> bool:
+    return kt not in (_cabi.F32, _cabi.F64)
+
+
+def take_table(rt: Runtime, table: DeviceTable, idx: torch.Tensor, n_out: Optional[int] = None,
+               presorted: Optional[dict] = None) -> DeviceTable:
+    """Device ``Table.take``.  ``presorted`` maps a column name to ``(norm_keys,
+    descending)`` when ``idx`` is the sort permutation and ``norm_keys`` holds that
+    column's radix keys already in output order: integer key columns are then
+    rebuilt sequentially from the radix keys instead of being gathered."""
     n_out = int(idx.numel()) if n_out is None else n_out
-    cols = [take_column(rt, c, idx, n_out) for c in table.columns]
+    cols = []
+    for name, c in zip(table.names, table.columns):
+        pre = (presorted or {}).get(name)
+        if (pre is not None and c.kind == "fixed" and n_out == c.n and n_out > 0
+                and _is_int_key(key_type_of(c.type))):
+            norm, desc = pre
+            out = rt.empty(n_out * c.width)
+            rt.call("xchg_denormalize_keys", _vp(norm), key_type_of(c.type), int(bool(desc)), n_out,
+                    _vp(out), rt.stream)
+            validity, null_count = None, 0
+            if c.validity is not None:
+                validity = rt.zeros(((n_out + 31) // 32) * 4)
+                cnt = rt.zeros(1, torch.int64)
+                rt.call("xchg_gather_bitmap", _vp(c.validity), 0, _vp(idx), n_out, _vp(validity),
+                        _vp(cnt), rt.stream)
+                null_count = cnt
+            cols.append(DeviceColumn(c.type, n_out, "fixed", c.width, out, None, validity, null_count))
+        else:
+            cols.append(take_column(rt, c, idx, n_out))
     return DeviceTable(list(table.names), cols, n_out, table.schema)
 
 
@@ -520,15 +554,14 @@ def sort_permutation(rt: Runtime, table: DeviceTable, columns: Sequence[str],
             raise NotImplementedError(f"sort key column {name!r} of type {col.type} is not supported")
         kt = key_type_of(col.type)
         out = rt.empty(n, torch.int32)
-        norm = rt.empty(n, torch.int64) if (want_norm and ci == 0) else None
+        norm = rt.empty(n, torch.int64) if ci == 0 else None  # primary key: always kept
         rt.call("xchg_sort_column", _vp(col.data), kt, int(bool(desc)), _vp(col.validity), 0,
                 _vp(perm), n, _vp(out), _vp(norm), _vp(ws), ws_bytes, rt.stream, launches=10)
         perm = out
         if ci == 0:
             norm_primary = norm
-    norms = None
+    norms = [norm_primary]
     if want_norm:
-        norms = [norm_primary]
         for name, desc in order[1:]:
             col = table.column(name)
             nk = rt.empty(n, torch.int64)

@@ -26,6 +26,7 @@ import torch
 from .. import device as dev
 from ..block import empty_table
 from ..block_accessor import _cuts_for as cuts_for
+from ..block_accessor import _presorted
 from ..sort_key import SortKey
 from .sort_task_spec import SortTaskSpec
 
@@ -138,7 +139,7 @@ class DeviceExchange:
         perm, norms = dev.sort_permutation(rt, ds.table, sort_key.get_columns(),
                                            sort_key.get_descending(), want_norm=len(boundaries) > 0)
         cuts = cuts_for(rt, ds.table, norms, boundaries, sort_key) if boundaries else []
-        out = dev.take_table(rt, ds.table, perm, n)
+        out = dev.take_table(rt, ds.table, perm, n, _presorted(sort_key, norms))
         ranges, last = [], 0
         for c in cuts:
             ranges.append((last, c))

@@ -70,6 +70,13 @@ uint64_t xchg_launch_count(void);
 int xchg_profile_enable(int on);
 int xchg_profile_read(int kernel_id, double* total_ms, uint64_t* launches);
 
+/* Device-wide hint (cudaLimitMaxL2FetchGranularity) for the CURRENT device: how
+ * many bytes the L2 fetches from HBM per miss.  The gathers of this engine read
+ * random 8..128-byte rows; with the 128-byte default a 90-byte row costs ~219 B of
+ * DRAM reads (profiles/r01_summary.md), with 32 it costs its sectors.  No
+ * counterpart in the reference.  bytes = 32, 64 or 128. */
+int xchg_set_l2_fetch_granularity(int bytes);
+
 /* ---------------------------------------------------------------- sort ---- */
 
 /* Workspace bytes xchg_sort_column needs for n rows. */
@@ -112,6 +119,17 @@ int xchg_normalize_keys(const void* keys, int key_type, int descending,
                         const uint8_t* validity, int64_t validity_bit_offset,
                         const uint32_t* perm, uint64_t n, uint64_t* norm_out,
                         void* stream);
+
+/*
+ * Inverse of the key normalisation for INTEGER key types: sorted radix keys ->
+ * sorted raw key values, out[i] = key whose radix key is norm[i].  Produces the
+ * sorted key column sequentially instead of gathering it through the
+ * permutation (Table.take on the key column,
+ * python/ray/data/_internal/arrow_ops/transform_pyarrow.py:70).  Slots of null
+ * rows receive an unspecified value (they are masked by the validity bitmap).
+ */
+int xchg_denormalize_keys(const uint64_t* norm, int key_type, int descending, uint64_t n,
+                          void* out, void* stream);
 
 /*
  * Boundary search on sorted normalised keys -> partition cut indices.

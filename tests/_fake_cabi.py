@@ -125,6 +125,28 @@ class FakeLib:
         _arr(out, np.uint64, n)[:] = nk
         return 0
 
+    def xchg_set_l2_fetch_granularity(self, b):
+        return 0
+
+    def xchg_denormalize_keys(self, norm, kt, desc, n, out, stream):
+        dt = np.dtype(_KT[kt])
+        assert dt.kind in "iu"
+        bits = dt.itemsize * 8
+        mask = (1 << bits) - 1
+        u = _arr(norm, np.uint64, n).astype(object)
+        res = []
+        for x in u:
+            x = int(x) & mask
+            if desc:
+                x = ~x & mask
+            if dt.kind == "i":
+                x ^= 1 << (bits - 1)
+                if x >= 1 << (bits - 1):
+                    x -= 1 << bits
+            res.append(x)
+        _arr(out, dt, n)[:] = np.array(res, dtype=dt)
+        return 0
+
     def xchg_partition_bounds(self, cols, col_desc, last_thr, has_last, ncols, n, lower, upper, flags,
                               nb, first_desc, cuts, stream):
         lo_a = _arr(lower, np.uint64, nb * ncols)
