@@ -441,27 +441,42 @@ def run_b200(args):
 
     # ---- end to end through the host-buffer API (pinned Arrow blocks in and out) ----
     e2e = None
-    if not args.no_e2e and world == 1:
+    if not args.no_e2e:
         blocks, keep = host_blocks_from_device(rt, keys, data, ds.block_ranges)
         h2d = sum(b.nbytes for b in blocks)
+
+        def e2e_step(i):
+            if world > 1:
+                return ex.sort_blocks_distributed(blocks, sk, seed=i)
+            return ex.sort_blocks(blocks, sk, seed=i)
+
         for i in range(max(1, min(args.warmup, 2))):
-            outs = ex.sort_blocks(blocks, sk, seed=i)
+            outs = e2e_step(i)
             del outs
         e_steps = max(1, min(args.steps, args.e2e_steps))
-        torch.cuda.synchronize()
+        barrier()
         t0 = time.perf_counter()
         d2h = 0
         for i in range(e_steps):
-            outs = ex.sort_blocks(blocks, sk, seed=100 + i)
+            outs = e2e_step(100 + i)
             d2h = sum(o.nbytes for o in outs)
             rows = sum(o.num_rows for o in outs)
             del outs
         torch.cuda.synchronize()
         dt = (time.perf_counter() - t0) / e_steps
-        assert rows == n
-        e2e = {"value": n / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+        agg = torch.tensor([dt, -float(rows), -float(h2d), -float(d2h)], dtype=torch.float64, device=rt.device)
+        if world > 1:
+            # slowest rank's time; rows and bytes summed over ranks
+            tm = agg[:1].clone()
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            sums = -agg[1:].clone()
+            dist.all_reduce(sums)
+            dt, rows, h2d, d2h = float(tm.item()), int(sums[0].item()), int(sums[1].item()), int(sums[2].item())
+        assert rows == total_rows
+        e2e = {"value": total_rows / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                "ms_per_step": dt * 1e3, "steps": e_steps,
-               "api": "DeviceExchange.sort_blocks(pinned host Arrow blocks) -> host Arrow blocks"}
+               "api": ("DeviceExchange.sort_blocks_distributed" if world > 1 else "DeviceExchange.sort_blocks")
+                      + "(pinned host Arrow blocks) -> host Arrow blocks; wall clock, max over ranks"}
         del blocks, keep
 
     # ---- CPU baseline (rank 0, N=1 only): bounded sample of the same workload ----

@@ -615,3 +615,75 @@ extern "C" int xchg_gather_offsets_static(const int64_t* in_off, const uint32_t*
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
 }
+
+// ------------------------------------------------ exchange-side utilities ---
+// Validity bitmaps cross the all-to-all as one byte per row (per-destination row
+// ranges of a bit-packed buffer are not byte aligned); offsets cross as the
+// sender's absolute values and are re-based on arrival.
+namespace {
+
+__global__ void __launch_bounds__(256)
+k_bitmap_unpack(const uint8_t* __restrict__ in, int64_t bit0, uint64_t n, uint8_t* __restrict__ out) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    out[i] = bit_is_set(in, (int64_t)i + bit0) ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(256)
+k_bitmap_pack(const uint8_t* __restrict__ in, uint64_t n, uint32_t* __restrict__ out_words,
+              unsigned long long* zero_count) {
+  const uint64_t nwords = (n + 31) / 32;
+  const int lane = threadIdx.x & 31;
+  const uint64_t warp0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  unsigned long long zeros = 0;
+  for (uint64_t w = warp0; w < nwords; w += nwarps) {
+    const uint64_t i = w * 32 + lane;
+    const bool bit = i < n ? in[i] != 0 : false;
+    const unsigned word = __ballot_sync(0xffffffffu, bit);
+    if (lane == 0) {
+      out_words[w] = word;
+      const unsigned live = (w * 32 + 32 <= n) ? 0xffffffffu : ((1u << (n - w * 32)) - 1u);
+      zeros += __popc(~word & live);
+    }
+  }
+  if (zero_count && lane == 0 && zeros) atomicAdd(zero_count, zeros);
+}
+
+__global__ void k_offsets_rebase(const int64_t* __restrict__ in, uint64_t count, int64_t base,
+                                 int64_t* __restrict__ out) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  const int64_t first = in[0];
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride)
+    out[i] = in[i] - first + base;
+}
+
+}  // namespace
+
+extern "C" int xchg_bitmap_unpack(const uint8_t* in, int64_t in_bit_offset, uint64_t n, uint8_t* out,
+                                  void* stream) {
+  if (n == 0) return XCHG_OK;
+  XCHG_REQUIRE(in && out, "NULL in / out");
+  XCHG_LAUNCH(XK_GATHER_BITMAP, (cudaStream_t)stream, k_bitmap_unpack<<<grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(in, in_bit_offset, n, out));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+extern "C" int xchg_bitmap_pack(const uint8_t* in, uint64_t n, uint8_t* out, uint64_t* zero_count_out,
+                                void* stream) {
+  if (n == 0) return XCHG_OK;
+  XCHG_REQUIRE(in && out, "NULL in / out");
+  XCHG_REQUIRE(((uintptr_t)out & 3) == 0, "bitmap output must be 4-byte aligned (and padded to 4 bytes)");
+  XCHG_LAUNCH(XK_GATHER_BITMAP, (cudaStream_t)stream, k_bitmap_pack<<<grid_for(n, 256, 8), 256, 0, (cudaStream_t)stream>>>(in, n, (uint32_t*)out, (unsigned long long*)zero_count_out));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+extern "C" int xchg_offsets_rebase(const int64_t* in, uint64_t count, int64_t base, int64_t* out,
+                                   void* stream) {
+  if (count == 0) return XCHG_OK;
+  XCHG_REQUIRE(in && out, "NULL in / out");
+  XCHG_LAUNCH(XK_OFFSETS_UTIL, (cudaStream_t)stream, k_offsets_rebase<<<grid_for(count, 256, 8), 256, 0, (cudaStream_t)stream>>>(in, count, base, out));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}

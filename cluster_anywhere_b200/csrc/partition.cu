@@ -8,6 +8,8 @@
 // every column -- whatever its direction -- is one lower_bound and one upper_bound
 // inside the run left by the previous column.  One thread per boundary: the work
 // is O(nb * ncols * log n) dependent loads, nowhere near any roofline.
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace {
@@ -56,8 +58,13 @@ __global__ void k_partition_bounds(ColPtrs cols, int ncols, uint64_t n,
     const int e = b * ncols + c;
     const uint8_t f = flags ? flags[e] : 0;
     if (f & 2) break;  // boundary tuple shorter than the key list
-    if (f & 4) {       // boundary sorts after every row of the current run (None boundary)
-      lo = hi;
+    if (f & 4) {
+      // None boundary component: NULL_SENTINEL compares greater than every value
+      // (util.py:67-89, :765-766).  Ascending column: it sorts after every row of the
+      // current run (lo = hi = run end).  Descending column: the reversed search puts
+      // it BEFORE every row (util.py:775-799 -> lo = hi = run start).
+      if (cols.desc[c]) hi = lo;
+      else lo = hi;
       continue;
     }
     const uint64_t L = lower[e], U = upper[e];
@@ -133,6 +140,118 @@ extern "C" int xchg_partition_bounds(const uint64_t* const* norm_cols_host,
   for (int c = 0; c < ncols; ++c) XCHG_REQUIRE(n == 0 || cp.c[c], "NULL key column %d", c);
   XCHG_LAUNCH(XK_PARTITION, (cudaStream_t)stream, k_partition_bounds<<<(nb + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
       cp, ncols, n, lower, upper, flags, nb, first_descending, cuts_out));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+// ------------------------------------------------------- per-row assignment ---
+//
+// xchg_assign_partitions: the same boundary rule as xchg_partition_bounds, stated
+// per ROW instead of per boundary, for rows that are NOT sorted yet.  The
+// reference only ever partitions a sorted block (find_partitions,
+// python/ray/data/_internal/util.py:806-828: partition i = table[cut[i-1]:cut[i]]);
+// a row therefore lands in partition  #(boundaries whose cut index is <= the row's
+// sorted position).  With cut = lo (first key ascending) that is the number of
+// boundaries the row is NOT strictly before; with cut = hi (first key descending)
+// the number of boundaries the row is strictly AFTER (util.py:803).  Evaluating
+// that predicate row by row lets a rank split its rows by destination GPU before
+// any sort (the exchange's "map" side), and is what the reduce side re-derives
+// with xchg_partition_bounds on the merged, sorted rows.
+//
+// Column-wise comparison of row key t against boundary component (L, U, flags):
+//   bit1 (tuple ended)      -> equal on all remaining columns
+//   bit2 (None component)   -> the boundary sorts after the row (ascending column) /
+//                              before the row (descending column)
+//   t <  L                  -> row before boundary
+//   bit0 (no equal value)   -> t >= L: row after boundary
+//   t >  U                  -> row after boundary;  else equal, next column
+namespace {
+
+constexpr int AP_THREADS = 256;
+constexpr int AP_MAX_SMEM_BINS = 8192;
+
+// -1 row before boundary b, 0 equal, +1 row after
+__device__ __forceinline__ int cmp_row_boundary(const ColPtrs& cols, int ncols, uint64_t row, uint64_t t0,
+                                                const uint64_t* __restrict__ lower,
+                                                const uint64_t* __restrict__ upper,
+                                                const uint8_t* __restrict__ flags, int b) {
+  for (int c = 0; c < ncols; ++c) {
+    const int e = b * ncols + c;
+    const uint8_t f = flags ? flags[e] : 0;
+    if (f & 2) return 0;
+    if (f & 4) return cols.desc[c] ? 1 : -1;
+    const uint64_t t = c == 0 ? t0 : cols.c[c][row];
+    const uint64_t L = lower[e];
+    if (t < L) return -1;
+    if (f & 1) return 1;
+    if (t > upper[e]) return 1;
+  }
+  return 0;
+}
+
+__global__ void __launch_bounds__(AP_THREADS)
+k_assign_partitions(ColPtrs cols, int ncols, uint64_t n, const uint64_t* __restrict__ lower,
+                    const uint64_t* __restrict__ upper, const uint8_t* __restrict__ flags, int nb,
+                    int first_desc, uint32_t* __restrict__ dest, unsigned long long* counts,
+                    int smem_bins) {
+  extern __shared__ uint32_t s_cnt[];
+  for (int j = threadIdx.x; j < smem_bins; j += blockDim.x) s_cnt[j] = 0;
+  __syncthreads();
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint64_t t0 = cols.c[0][i];
+    // boundaries are in sort order, so "row is right of boundary b" is monotone in b:
+    // binary search for the first boundary the row is left of
+    int lo = 0, hi = nb;
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      const int c = cmp_row_boundary(cols, ncols, i, t0, lower, upper, flags, mid);
+      const bool right = first_desc ? (c > 0) : (c >= 0);
+      if (right) lo = mid + 1;
+      else hi = mid;
+    }
+    dest[i] = (uint32_t)lo;
+    if (counts) {
+      if (smem_bins) atomicAdd(&s_cnt[lo], 1u);
+      else atomicAdd(&counts[lo], 1ull);
+    }
+  }
+  if (counts && smem_bins) {
+    __syncthreads();
+    for (int j = threadIdx.x; j < smem_bins; j += blockDim.x)
+      if (s_cnt[j]) atomicAdd(&counts[j], (unsigned long long)s_cnt[j]);
+  }
+}
+
+}  // namespace
+
+extern "C" int xchg_assign_partitions(const uint64_t* const* norm_cols_host,
+                                      const uint8_t* col_desc_host, int ncols, uint64_t n,
+                                      const uint64_t* lower, const uint64_t* upper,
+                                      const uint8_t* flags, int nb, int first_descending,
+                                      uint32_t* dest_out, uint64_t* counts_out, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  XCHG_REQUIRE(nb >= 0, "nb must be >= 0");
+  if (counts_out) XCHG_CUDA_TRY(cudaMemsetAsync(counts_out, 0, (size_t)(nb + 1) * 8, s));
+  if (n == 0) return XCHG_OK;
+  XCHG_REQUIRE(norm_cols_host && col_desc_host && dest_out, "NULL argument");
+  XCHG_REQUIRE(nb == 0 || (lower && upper), "NULL boundaries");
+  XCHG_REQUIRE(ncols >= 1 && ncols <= MAX_KEY_COLS, "ncols must be in [1, %d]", MAX_KEY_COLS);
+  ColPtrs cp;
+  for (int c = 0; c < MAX_KEY_COLS; ++c) {
+    cp.c[c] = c < ncols ? norm_cols_host[c] : nullptr;
+    cp.last_thr[c] = ~0ull;
+    cp.desc[c] = c < ncols ? col_desc_host[c] : 0;
+    cp.has_last[c] = 0;
+  }
+  for (int c = 0; c < ncols; ++c) XCHG_REQUIRE(cp.c[c], "NULL key column %d", c);
+  const int bins = (counts_out && nb + 1 <= AP_MAX_SMEM_BINS) ? nb + 1 : 0;
+  const int grid = (int)std::max<uint64_t>(
+      1, std::min<uint64_t>((n + AP_THREADS - 1) / AP_THREADS, (uint64_t)xchg_sm_count() * 8));
+  XCHG_LAUNCH(XK_PARTITION, s,
+              k_assign_partitions<<<grid, AP_THREADS, (size_t)bins * 4, s>>>(
+                  cp, ncols, n, lower, upper, flags, nb, first_descending, dest_out,
+                  (unsigned long long*)counts_out, bins));
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
 }

@@ -592,3 +592,63 @@ def partition_cuts(rt: Runtime, norms: List[torch.Tensor], n: int, lower: np.nda
     rt.call("xchg_partition_bounds", ptrs, cdesc, thr, hl, ncols, n, _vp(lo_d), _vp(up_d), _vp(fl_d),
             nb, int(bool(descending[0])), _vp(cuts), rt.stream)
     return [int(x) for x in cuts.tolist()]
+
+
+# ---------------------------------------------------------------------------
+# Per-row range partitioning (the exchange's map side on unsorted rows)
+# ---------------------------------------------------------------------------
+
+def normalized_key_columns(rt: Runtime, table: DeviceTable, columns: Sequence[str],
+                           descending: Sequence[bool]) -> List[torch.Tensor]:
+    """Radix keys of every key column in ROW order (K2 without the sort)."""
+    n = table.num_rows
+    out = []
+    for name, desc in zip(columns, descending):
+        col = table.column(name)
+        if col.kind != "fixed":
+            raise NotImplementedError(f"sort key column {name!r} of type {col.type} is not supported")
+        nk = rt.empty(n, torch.int64)
+        rt.call("xchg_normalize_keys", _vp(col.data), key_type_of(col.type), int(bool(desc)),
+                _vp(col.validity), 0, None, n, _vp(nk), rt.stream)
+        out.append(nk)
+    return out
+
+
+def assign_partitions(rt: Runtime, table: DeviceTable, boundaries: Sequence[tuple], sort_key):
+    """-> (dest uint32[n] as int32 tensor, counts int64[len(boundaries)+1]): the range
+    partition of every row under the reference's boundary rule (xchg_assign_partitions)."""
+    from . import keys as keymod
+
+    cols, desc = sort_key.get_columns(), sort_key.get_descending()
+    n, nb = table.num_rows, len(boundaries)
+    ktypes = [key_type_of(table.column(c).type) for c in cols]
+    lower, upper, flags = keymod.normalize_boundaries(boundaries, ktypes, desc)
+    norms = normalized_key_columns(rt, table, cols, desc)
+    ncols = len(cols)
+    lo_d = rt.empty(max(1, nb * ncols), torch.int64)
+    up_d = rt.empty(max(1, nb * ncols), torch.int64)
+    fl_d = rt.empty(max(1, nb * ncols), torch.uint8)
+    if nb:
+        _h2d(lo_d.view(torch.uint8)[: nb * ncols * 8],
+             np.ascontiguousarray(lower, dtype=np.uint64).view(np.uint8).reshape(-1))
+        _h2d(up_d.view(torch.uint8)[: nb * ncols * 8],
+             np.ascontiguousarray(upper, dtype=np.uint64).view(np.uint8).reshape(-1))
+        _h2d(fl_d[: nb * ncols], np.ascontiguousarray(flags, dtype=np.uint8).reshape(-1))
+    dest = rt.empty(n, torch.int32)
+    counts = rt.zeros(nb + 1, torch.int64)
+    ptrs = (ctypes.c_void_p * ncols)(*[t.data_ptr() for t in norms])
+    cdesc = (ctypes.c_uint8 * ncols)(*[int(bool(d)) for d in desc[:ncols]])
+    rt.call("xchg_assign_partitions", ptrs, cdesc, ncols, n, _vp(lo_d), _vp(up_d), _vp(fl_d), nb,
+            int(bool(desc[0])), _vp(dest), _vp(counts), rt.stream)
+    return dest, counts
+
+
+def sort_u32(rt: Runtime, keys: torch.Tensor, n: int) -> torch.Tensor:
+    """Stable ascending sort of a uint32 key array -> row permutation (K2 + as many
+    K3 passes as the keys have non-trivial digit places: one for <= 256 partitions)."""
+    ws_bytes = sort_workspace_bytes(n)
+    ws = rt.empty(ws_bytes)
+    perm = rt.empty(n, torch.int32)
+    rt.call("xchg_sort_column", _vp(keys), _cabi.U32, 0, None, 0, None, n, _vp(perm), None, _vp(ws),
+            ws_bytes, rt.stream, launches=6)
+    return perm

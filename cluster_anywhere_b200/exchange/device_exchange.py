@@ -84,6 +84,36 @@ class DeviceExchange:
         return [pa.Table.from_arrays([b() for b in bs], schema=t.schema) for bs in builders]
 
     # -- sort --------------------------------------------------------------------
+    def sample_keys(self, ds: DeviceDataset, sort_key: SortKey, n_samples: int, seed: int = 0,
+                    first_block: int = 0) -> List[tuple]:
+        """K1: key tuples of ``min(n_samples, rows)`` random rows of every block
+        (SortTaskSpec._sample_block, sort_task_spec.py:229 ->
+        ArrowBlockAccessor._sample, arrow_block.py:341-344).  Row indices are drawn on
+        the host (Philox, keyed by (seed, global block index)); the key columns are
+        gathered on the device (K5) and only the samples come back."""
+        if ds.table is None or ds.num_rows == 0 or n_samples <= 0:
+            return []
+        picks = []
+        for b, (lo, hi) in enumerate(ds.block_ranges):
+            rows = hi - lo
+            k = min(n_samples, rows)
+            if k <= 0:
+                continue
+            g = np.random.Generator(np.random.Philox(key=[seed, first_block + b]))
+            picks.append(lo + g.choice(rows, size=k, replace=False))
+        if not picks:
+            return []
+        idx = np.concatenate(picks).astype(np.uint32)
+        rt = self.rt
+        idx_d = rt.empty(idx.size, torch.int32)
+        dev._h2d(idx_d.view(torch.uint8), idx.view(np.uint8))
+        cols = sort_key.get_columns()
+        key_cols = [dev.take_column(rt, ds.table.column(c), idx_d, idx.size) for c in cols]
+        kt = dev.DeviceTable(list(cols), key_cols, idx.size,
+                             pa.schema([ds.table.schema.field(c) for c in cols]))
+        host = dev.export_table(rt, kt)
+        return list(zip(*[host[c].to_pylist() for c in cols]))
+
     def sample_boundaries(self, ds: DeviceDataset, sort_key: SortKey, num_reducers: int,
                           seed: int = 0) -> list:
         """K1 + the driver half of SortTaskSpec.sample_boundaries
@@ -94,27 +124,7 @@ class DeviceExchange:
         if ds.table is None or ds.num_rows == 0:
             return [None] * (num_reducers - 1)
         m = max(1, ds.num_blocks)
-        n_samples = int(num_reducers * 10 / m)
-        picks = []
-        for b, (lo, hi) in enumerate(ds.block_ranges):
-            rows = hi - lo
-            k = min(n_samples, rows)
-            if k <= 0:
-                continue
-            g = np.random.Generator(np.random.Philox(key=[seed, b]))
-            picks.append(lo + g.choice(rows, size=k, replace=False))
-        if not picks:
-            return [None] * (num_reducers - 1)
-        idx = np.concatenate(picks).astype(np.uint32)
-        rt = self.rt
-        idx_d = rt.empty(idx.size, torch.int32)
-        dev._h2d(idx_d.view(torch.uint8), idx.view(np.uint8))
-        cols = sort_key.get_columns()
-        key_cols = [dev.take_column(rt, ds.table.column(c), idx_d, idx.size) for c in cols]
-        kt = dev.DeviceTable(list(cols), key_cols, idx.size,
-                             pa.schema([ds.table.schema.field(c) for c in cols]))
-        host = dev.export_table(rt, kt)
-        tuples = list(zip(*[host[c].to_pylist() for c in cols]))
+        tuples = self.sample_keys(ds, sort_key, int(num_reducers * 10 / m), seed)
         return SortTaskSpec.boundaries_from_samples(tuples, sort_key, num_reducers)
 
     def sort(self, ds: DeviceDataset, sort_key: SortKey, num_outputs: Optional[int] = None,
@@ -152,3 +162,93 @@ class DeviceExchange:
                     seed: int = 0) -> List[pa.Table]:
         """Host blocks in, sorted host blocks out (stage + sort + export)."""
         return self.export(self.sort(self.stage(blocks), sort_key, num_outputs, boundaries, seed))
+
+    # -- multi-GPU sort ------------------------------------------------------------
+    def sort_distributed(self, ds: DeviceDataset, sort_key: SortKey,
+                         boundaries: Optional[list] = None, seed: int = 0,
+                         group=None, force_exchange: bool = False) -> DeviceDataset:
+        """``Dataset.sort`` over the blocks of ALL ranks (one process per GPU).
+
+        Rank g holds a contiguous run of the dataset's input blocks (rank order =
+        block order).  The global result is what the reference computes: the R range
+        partitions, by ``boundaries``, of the stable sort of all rows in (block, row)
+        order; rank g ends up with a contiguous run of the R output blocks.
+
+          map     (SortTaskSpec.map, sort_task_spec.py:127-138) every row gets its
+                  destination rank from the G-1 splitters -- the block boundaries at
+                  the rank cuts -- with the reference's own partition rule stated per
+                  row (xchg_assign_partitions); a stable one-digit radix pass orders
+                  the row ids by destination; K5 gathers every column in that order.
+          exchange  one all-to-all-v per column buffer over NVLink instead of M x R
+                  plasma objects (pull_based_shuffle_task_scheduler.py:84-120).
+          reduce  (SortTaskSpec.reduce, :140-152 -> merge_sorted_blocks) rows arrive in
+                  (source rank, source position) order; one stable sort (K2+K3), the
+                  boundary search for this rank's block cuts (K4), one gather (K5).
+        """
+        from . import collective as coll
+
+        rank, G = coll.world(group)
+        if G == 1 and not force_exchange:  # force_exchange: run the map/exchange/reduce path anyway
+            return self.sort(ds, sort_key, boundaries=boundaries, seed=seed)
+        rt = self.rt
+        schema = None if ds.table is None else ds.table.schema
+        info = coll.all_gather_object((ds.num_blocks, ds.num_rows, schema), group)
+        blocks_per_rank = [i[0] for i in info]
+        total_rows = sum(i[1] for i in info)
+        schema = next((i[2] for i in info if i[2] is not None), None)
+        r_total = sum(blocks_per_rank) if boundaries is None else len(boundaries) + 1
+        r_total = max(1, r_total)
+        # output blocks per rank: as many as it brought in; evenly when that would
+        # leave a gap (user boundaries, or a rank without input blocks)
+        if boundaries is None and all(b > 0 for b in blocks_per_rank):
+            out_per_rank = list(blocks_per_rank)
+        else:
+            out_per_rank = [r_total // G + (1 if g < r_total % G else 0) for g in range(G)]
+        ob = np.concatenate([[0], np.cumsum(out_per_rank)]).astype(int)
+        my_blocks = int(out_per_rank[rank])
+        if total_rows == 0 or schema is None:
+            return DeviceDataset(None, [(0, 0)] * my_blocks)
+        sort_key.validate_schema(schema)
+        table = ds.table if ds.table is not None else coll.empty_device_table(rt, schema)
+
+        if boundaries is None:
+            first_block = int(sum(blocks_per_rank[:rank]))
+            m = max(1, sum(blocks_per_rank))
+            mine = self.sample_keys(ds, sort_key, int(r_total * 10 / m), seed, first_block)
+            samples = [t for part in coll.all_gather_object(mine, group) for t in part]
+            boundaries = (SortTaskSpec.boundaries_from_samples(samples, sort_key, r_total)
+                          if r_total > 1 else [])
+        ncols = len(sort_key.get_columns())
+        none_tuple = (None,) * ncols
+        # splitters sit between consecutive ranks that own output blocks: the block
+        # boundary at the end of the earlier owner's run
+        owners = [g for g in range(G) if out_per_rank[g] > 0]
+        splitters = [boundaries[int(ob[g + 1]) - 1] for g in owners[:-1]]
+        splitters = [none_tuple if s is None else s for s in splitters]
+
+        # ---- map: destination of every row, stable order by destination ----
+        n = table.num_rows
+        send_counts = [0] * G
+        send_table = table
+        if n > 0:
+            dest, counts = dev.assign_partitions(rt, table, splitters, sort_key)
+            perm = dev.sort_u32(rt, dest, n)
+            for d, cnt in enumerate(counts.tolist()):
+                send_counts[owners[d]] = int(cnt)
+            send_table = dev.take_table(rt, table, perm, n)
+        recv = coll.exchange_table(rt, send_table, send_counts, group)
+
+        # ---- reduce: stable sort of the received runs, cut into this rank's blocks ----
+        if my_blocks == 0:
+            assert recv.num_rows == 0
+            return DeviceDataset(None, [])
+        lo_b, hi_b = int(ob[rank]), int(ob[rank + 1])
+        local_bounds = list(boundaries[lo_b:hi_b - 1])
+        return self.sort(DeviceDataset(recv, [(0, recv.num_rows)]), sort_key,
+                         boundaries=local_bounds)
+
+    def sort_blocks_distributed(self, blocks: Sequence[pa.Table], sort_key: SortKey,
+                                boundaries: Optional[list] = None, seed: int = 0,
+                                group=None) -> List[pa.Table]:
+        """This rank's host blocks in, this rank's run of the sorted output blocks out."""
+        return self.export(self.sort_distributed(self.stage(blocks), sort_key, boundaries, seed, group))

@@ -139,7 +139,9 @@ int xchg_denormalize_keys(const uint64_t* norm, int key_type, int descending, ui
  * in [lower[b*ncols+c], upper[b*ncols+c]]; stop early when lo == hi; result is
  * hi if first_descending else lo.  flags per (boundary, column): bit0 = the equal
  * range is empty (hi = lo = lower_bound), bit1 = boundary tuple ends before this
- * column, bit2 = boundary sorts after every row (a None boundary: lo = hi),
+ * column, bit2 = None boundary component (sorts after every row of the run on an
+ * ascending column: lo = hi = run end; before every row on a descending one:
+ * lo = hi = run start -- util.py:765-766 with :775-799),
  * bit3 = boundary is NaN.
  * Descending columns reproduce numpy.searchsorted over the reference's reversed
  * view probe by probe (util.py:775-799), so that cut points stay identical even
@@ -158,6 +160,31 @@ int xchg_partition_bounds(const uint64_t* const* norm_cols_host, const uint8_t* 
                           const uint64_t* lower, const uint64_t* upper,
                           const uint8_t* flags, int nb, int first_descending,
                           uint64_t* cuts_out, void* stream);
+
+/*
+ * The same boundary rule stated per ROW, for rows that are not sorted yet:
+ * dest_out[i] = index of the range partition row i belongs to (0..nb), i.e. the
+ * partition find_partitions (python/ray/data/_internal/util.py:806-828) would
+ * slice it into after the sort: the number of boundaries whose cut index is <= the
+ * row's sorted position (cut = lo -> boundaries the row is not strictly before;
+ * cut = hi when first_descending -> boundaries the row is strictly after,
+ * util.py:803).  Used by the multi-GPU exchange to split a rank's rows by
+ * destination before the sort (the "map" side of SortTaskSpec,
+ * python/ray/data/_internal/planner/exchange/sort_task_spec.py:127-138, without
+ * sorting first).  Boundaries must be in sort order.
+ *
+ *  norm_cols_host  HOST array of ncols device pointers: normalised keys of every
+ *                  key column in ROW order (xchg_normalize_keys with perm = NULL);
+ *                  col_desc_host: HOST array of ncols direction flags
+ *  lower/upper/flags  as xchg_partition_bounds (nb*ncols entries, device)
+ *  dest_out     n uint32, device
+ *  counts_out   optional: nb+1 uint64 rows per partition, device (zeroed here)
+ */
+int xchg_assign_partitions(const uint64_t* const* norm_cols_host, const uint8_t* col_desc_host,
+                           int ncols, uint64_t n,
+                           const uint64_t* lower, const uint64_t* upper, const uint8_t* flags,
+                           int nb, int first_descending, uint32_t* dest_out,
+                           uint64_t* counts_out, void* stream);
 
 /* -------------------------------------------------------------- gather ---- */
 
@@ -223,6 +250,24 @@ int xchg_offsets_uniform64(uint64_t count, uint64_t width, int64_t base, int64_t
  * `width` bytes. */
 int xchg_offsets_check_uniform(const int64_t* off, uint64_t n_rows, uint64_t width,
                                uint32_t* flag_out, void* stream);
+
+/*
+ * Exchange-side utilities.  The reference moves map outputs between tasks as
+ * Arrow IPC objects through the plasma store
+ * (python/ray/_private/arrow_serialization.py:103,
+ * pull_based_shuffle_task_scheduler.py:84-120); here the column buffers cross an
+ * all-to-all directly, and these three kernels convert what does not split at
+ * byte granularity: validity bitmaps travel as one byte per row, offsets travel
+ * as the sender's absolute values and are re-based on arrival
+ * (out[i] = in[i] - in[0] + base).
+ * xchg_bitmap_pack also counts zero bits into *zero_count_out (device uint64,
+ * caller zeroes; may be NULL); out must be 4-byte aligned and padded to 4 bytes.
+ */
+int xchg_bitmap_unpack(const uint8_t* in, int64_t in_bit_offset, uint64_t n, uint8_t* out_bytes,
+                       void* stream);
+int xchg_bitmap_pack(const uint8_t* in_bytes, uint64_t n, uint8_t* out, uint64_t* zero_count_out,
+                     void* stream);
+int xchg_offsets_rebase(const int64_t* in, uint64_t count, int64_t base, int64_t* out, void* stream);
 
 #ifdef __cplusplus
 }

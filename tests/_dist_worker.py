@@ -1,0 +1,78 @@
+"""Worker of tests/test_distributed.py: one rank of a world_size-N `gloo` run of the
+multi-GPU sort on the host-memory test double (host logic + collectives, no GPU)."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import numpy as np
+import pyarrow as pa
+import torch.distributed as dist
+
+from _fake_cabi import FakeLib
+from _golden import tables_equal
+from cluster_anywhere_b200 import SortKey, _cabi
+from cluster_anywhere_b200.exchange import DeviceExchange
+from oracle import exchange_oracle as O
+
+
+def make_block(rng, n):
+    k = rng.integers(-50, 50, n)
+    f = rng.standard_normal(n)
+    f[rng.random(n) < 0.1] = np.nan
+    s = [None if rng.random() < 0.1 else ("s%d" % rng.integers(0, 1000)) * int(rng.integers(0, 4))
+         for _ in range(n)]
+    return pa.table({
+        "k": pa.array(k, pa.int32()),
+        "f": pa.array(f, pa.float64(), mask=rng.random(n) < 0.1),
+        "s": pa.array(s, pa.string()),
+        "b": pa.array(rng.random(n) < 0.5),
+        "p": pa.array([bytes(rng.integers(0, 256, 10, dtype=np.uint8)) for _ in range(n)], pa.binary()),
+    })
+
+
+def main():
+    _cabi._install_test_double(FakeLib())
+    dist.init_process_group("gloo")
+    r, w = dist.get_rank(), dist.get_world_size()
+    rng = np.random.default_rng(7)  # same stream on every rank: all ranks know all blocks
+    sizes = (1000, 0, 300, 2000, 17) if w == 2 else (400, 0, 300, 0, 0, 900, 17)
+    all_blocks = [make_block(rng, n) for n in sizes]
+    cut = [len(all_blocks) * g // w for g in range(w + 1)]
+    if "--empty-rank" in sys.argv:
+        cut = [0] + [len(all_blocks)] * w  # rank 0 brings everything, the others nothing
+    mine = all_blocks[cut[r]:cut[r + 1]]
+    ex = DeviceExchange()
+    full = pa.concat_tables([b for b in all_blocks if b.num_rows])
+    cases = [(["k"], [False], None), (["k", "f"], [True, False], None), (["f"], [True], None),
+             (["f", "k"], [True, True], None),
+             (["k"], [False], [(-20,), (0,), (0,), (31,)]), (["k"], [True], [(10,), (-10,)])]
+    for cols, desc, bounds in cases:
+        sk = SortKey(cols, desc)
+        out = ex.sort_blocks_distributed(mine, sk, boundaries=bounds, seed=3)
+        outs = [None] * w
+        dist.all_gather_object(outs, out)
+        got = [b for part in outs for b in part]
+        exp = O.sort_table(full, cols, desc)
+        nonempty = [g for g in got if g.num_rows]
+        assert tables_equal(pa.concat_tables(nonempty), exp), (cols, desc, bounds)
+        if bounds is None:
+            assert len(got) == len(all_blocks), len(got)
+        else:
+            # per-block contents = the reference's range partitions of the sorted rows
+            parts = O.find_partitions(exp, bounds, cols, desc)
+            assert len(got) == len(parts)
+            for g, e in zip(got, parts):
+                assert g.num_rows == e.num_rows
+                if e.num_rows:
+                    assert tables_equal(g, e)
+    dist.barrier()
+    if r == 0:
+        print("DIST-OK", w)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

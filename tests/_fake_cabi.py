@@ -168,7 +168,10 @@ class FakeLib:
                 if f & 2:
                     break
                 if f & 4:
-                    lo = hi
+                    if cdesc[c]:
+                        hi = lo
+                    else:
+                        lo = hi
                     continue
                 L, U = int(lo_a[b * ncols + c]), int(up_a[b * ncols + c])
                 if not cdesc[c]:
@@ -286,4 +289,76 @@ class FakeLib:
         o = _arr(off, np.int64, n_rows + 1)
         if (np.diff(o) != width).any():
             _arr(flag, np.uint32, 1)[0] |= 1
+        return 0
+
+    # -- exchange-side entry points ------------------------------------------
+    def xchg_assign_partitions(self, cols, col_desc, ncols, n, lower, upper, flags, nb, first_desc, dest, counts,
+                               stream):
+        """Independent statement: sort the rows (stable, lexicographic over the
+        normalised key columns), cut the sorted order exactly as
+        xchg_partition_bounds does, and give every row the partition its sorted
+        position falls into."""
+        if _addr(counts):
+            _arr(counts, np.uint64, nb + 1)[:] = 0
+        if n == 0:
+            return 0
+        arrays = [_arr(cols[c], np.uint64, n) for c in range(ncols)]
+        order = np.lexsort(tuple(arrays[::-1]))  # stable; first column is the primary key
+        sorted_cols = [a[order] for a in arrays]
+        lo_a = _arr(lower, np.uint64, nb * ncols)
+        up_a = _arr(upper, np.uint64, nb * ncols)
+        fl_a = _arr(flags, np.uint8, nb * ncols) if _addr(flags) else np.zeros(nb * ncols, np.uint8)
+        cuts = []
+        for b in range(nb):
+            lo, hi = 0, n
+            early = False
+            for c in range(ncols):
+                if lo == hi:
+                    early = True
+                    break
+                f = int(fl_a[b * ncols + c])
+                if f & 2:
+                    break
+                if f & 4:
+                    if col_desc[c]:
+                        hi = lo
+                    else:
+                        lo = hi
+                    continue
+                seg = sorted_cols[c][lo:hi]
+                l2 = lo + int(np.searchsorted(seg, lo_a[b * ncols + c], side="left"))
+                h2 = l2 if (f & 1) else lo + int(np.searchsorted(seg, up_a[b * ncols + c], side="right"))
+                lo, hi = l2, h2
+            cuts.append(hi if (early or first_desc) else lo)
+        pos_part = np.searchsorted(np.asarray(cuts, dtype=np.int64), np.arange(n), side="right") if nb else np.zeros(n, np.int64)
+        d = np.empty(n, dtype=np.uint32)
+        d[order] = pos_part.astype(np.uint32)
+        _arr(dest, np.uint32, n)[:] = d
+        if _addr(counts):
+            _arr(counts, np.uint64, nb + 1)[:] = np.bincount(d, minlength=nb + 1).astype(np.uint64)
+        return 0
+
+    def xchg_bitmap_unpack(self, inp, bit_off, n, out, stream):
+        if n == 0:
+            return 0
+        _arr(out, np.uint8, n)[:] = _bits(inp, bit_off, np.arange(n, dtype=np.int64)).astype(np.uint8)
+        return 0
+
+    def xchg_bitmap_pack(self, inp, n, out, zero_count, stream):
+        if n == 0:
+            return 0
+        bits = _arr(inp, np.uint8, n) != 0
+        packed = np.packbits(bits, bitorder="little")
+        o = _arr(out, np.uint8, ((n + 31) // 32) * 4)
+        o[:] = 0
+        o[: len(packed)] = packed
+        if _addr(zero_count):
+            _arr(zero_count, np.uint64, 1)[0] += int((~bits).sum())
+        return 0
+
+    def xchg_offsets_rebase(self, inp, count, base, out, stream):
+        if count == 0:
+            return 0
+        i = _arr(inp, np.int64, count)
+        _arr(out, np.int64, count)[:] = i - i[0] + base
         return 0

@@ -49,6 +49,21 @@ def test_kat_find_partitions(engine):
     assert [x.num_rows for x in p] == [5, 0]
     p = parts(pa.table({"value": [2, 2, 2, 2, 2]}), [(2,), (1,)], ["value"], [True])
     assert [x.num_rows for x in p] == [5, 0, 0]
+    # None boundary components (NULL_SENTINEL, util.py:67-89): after every row on an
+    # ascending column, BEFORE every row on a descending one (reversed search,
+    # util.py:775-799).  Row counts taken from the reference itself (slices may overlap
+    # when the cuts are not monotone -- util.py:823-827 slices regardless).
+    for vals in ([5, 3, 2, 2, 1], [5, 3, None, 2, 1, None]):
+        n = len(vals)
+        t = pa.table({"value": pa.array(vals, pa.int64())})
+        assert [x.num_rows for x in parts(t, [(None,)], ["value"], [True])] == [0, n]
+        assert [x.num_rows for x in parts(t, [(3,), (None,)], ["value"], [True])] == [2, 0, n]
+        assert [x.num_rows for x in parts(t, [(None,), (3,)], ["value"], [True])] == [0, 2, n - 2]
+        assert [x.num_rows for x in parts(t, [(None,), (3,)], ["value"], [False])] == [n, 0, 2 * n - 8]
+    t = pa.table({"k": [0, 0, 0, 0, 1, 1], "g": [2.0, 1.0, 0.0, -1.0, 5.0, 4.0]})
+    assert [x.num_rows for x in parts(t, [(0, None)], ["k", "g"], [False, True])] == [0, 6]
+    assert [x.num_rows for x in parts(t, [(0, None)], ["k", "g"], [False, False])] == [4, 2]
+    assert [x.num_rows for x in parts(t, [(0, None)], ["k", "g"], [True, True])] == [2, 4]
 
 
 def test_kat_seeded_two_key_sort(engine):
