@@ -35,6 +35,9 @@ _SIGNATURES = {
     "xchg_set_l2_fetch_granularity": (c_int, [c_int]),
     "xchg_partition_bounds": (c_int, [ctypes.POINTER(c_void_p), _P, _P, _P, c_int, c_uint64, _P, _P, _P, c_int, c_int, _P, _P]),
     "xchg_assign_partitions": (c_int, [ctypes.POINTER(c_void_p), _P, c_int, c_uint64, _P, _P, _P, c_int, c_int, _P, _P, _P]),
+    "xchg_shuffle_positions": (c_int, [c_uint64, c_uint64, c_uint64, c_uint64, c_int, _P, _P]),
+    "xchg_invert_permutation": (c_int, [_P, c_uint64, c_uint64, _P, _P]),
+    "xchg_even_split_dest": (c_int, [_P, c_uint64, c_uint64, c_uint32, _P, _P, _P]),
     "xchg_bitmap_unpack": (c_int, [_P, c_int64, c_uint64, _P, _P]),
     "xchg_bitmap_pack": (c_int, [_P, c_uint64, _P, _P, _P]),
     "xchg_offsets_rebase": (c_int, [_P, c_uint64, c_int64, _P, _P]),

@@ -135,6 +135,18 @@ class B200ArrowBlockAccessor:
         keys_only = B200ArrowBlockAccessor(self._table.select(sort_key.get_columns()), self._rt)
         return keys_only.take(indices)
 
+    def random_shuffle(self, random_seed: Optional[int]) -> pa.Table:
+        """arrow_block.py:225-231: a seeded random permutation of the rows.  The
+        reference draws ``RandomState(seed).permutation(n)`` (MT19937, values unpinned
+        by its tests); here the permutation is the Philox-keyed bijection of K7 and
+        the gather is K5.  ``None`` draws a fresh seed."""
+        n = self.num_rows()
+        if n == 0:
+            return self._table
+        rt = self.rt
+        dt = dev.stage_table(rt, self._table)
+        return dev.export_table(rt, dev.shuffle_table(rt, dt, random_seed))
+
     # -- sort ------------------------------------------------------------------
     def sort(self, sort_key: SortKey) -> pa.Table:
         """arrow_block.py:425-438."""

@@ -1,0 +1,180 @@
+// K7: seeded random permutation for Dataset.random_shuffle, for sm_100a.
+//
+// Replaces numpy.random.RandomState(seed).permutation(n) as the reference calls it
+// from python/ray/data/_internal/arrow_block.py:225-231 (ArrowBlockAccessor.
+// random_shuffle; map side shuffle_task_spec.py:81-84, reduce side :120-123).  The
+// reference's generator is MT19937 driving a sequential Fisher-Yates; its VALUES are
+// not pinned by any reference test (only same-seed-equal,
+// different-seed-different and multiset preservation are), so the device uses a
+// counter-based construction instead that needs no sequential state and no sort:
+//
+//   a 4-round balanced Feistel network over 2^b (b = even bit width covering n) whose
+//   round function is Philox-2x32-10 keyed by the seed, restricted to [0, n) by cycle
+//   walking (apply again while the value is >= n; the domain is < 4n, so < 4
+//   applications on average).  It is a bijection of [0, n) for every seed, both
+//   directions are computable per element (forward = output position of a source row,
+//   inverse = source row of an output position), and any sub-range can be evaluated
+//   independently -- which is what lets every GPU compute the destination of its own
+//   rows of ONE global permutation without communication.
+//
+// Pure ALU work (~100 integer multiplies per row), 4 bytes written per row: the
+// permutation itself is far from any roofline; the payload gather that consumes it
+// (K5) is the HBM-bound part.
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace {
+
+__host__ __device__ __forceinline__ uint32_t philox2x32_10(uint32_t c0, uint32_t c1, uint32_t key) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint64_t p = (uint64_t)0xD256D193u * c0;
+    const uint32_t hi = (uint32_t)(p >> 32), lo = (uint32_t)p;
+    c0 = hi ^ key ^ c1;
+    c1 = lo;
+    key += 0x9E3779B9u;
+  }
+  return c0;
+}
+
+struct Feistel {
+  uint32_t key, tweak;  // seed low / high words
+  uint32_t half_bits;   // bits per half
+  uint64_t half_mask;
+  uint64_t n;
+};
+
+constexpr int FEISTEL_ROUNDS = 4;
+
+__host__ __device__ __forceinline__ uint64_t feistel_once(const Feistel& f, uint64_t x, bool inverse) {
+  uint32_t L = (uint32_t)(x >> f.half_bits), R = (uint32_t)(x & f.half_mask);
+  if (!inverse) {
+#pragma unroll
+    for (int r = 0; r < FEISTEL_ROUNDS; ++r) {
+      const uint32_t t = L ^ (philox2x32_10(R, f.tweak ^ (0x9E3779B9u * (uint32_t)(r + 1)), f.key) &
+                              (uint32_t)f.half_mask);
+      L = R;
+      R = t;
+    }
+  } else {
+#pragma unroll
+    for (int r = FEISTEL_ROUNDS - 1; r >= 0; --r) {
+      const uint32_t t = R ^ (philox2x32_10(L, f.tweak ^ (0x9E3779B9u * (uint32_t)(r + 1)), f.key) &
+                              (uint32_t)f.half_mask);
+      R = L;
+      L = t;
+    }
+  }
+  return ((uint64_t)L << f.half_bits) | R;
+}
+
+__host__ __device__ __forceinline__ uint64_t feistel_walk(const Feistel& f, uint64_t x, bool inverse) {
+  do {
+    x = feistel_once(f, x, inverse);
+  } while (x >= f.n);
+  return x;
+}
+
+__global__ void __launch_bounds__(256)
+k_shuffle_positions(Feistel f, uint64_t first, uint64_t count, int inverse, uint32_t* __restrict__ out) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride)
+    out[i] = (uint32_t)feistel_walk(f, first + i, inverse != 0);
+}
+
+__global__ void __launch_bounds__(256)
+k_invert_permutation(const uint32_t* __restrict__ pos, uint64_t n, uint64_t base,
+                     uint32_t* __restrict__ inv) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    inv[(uint64_t)pos[i] - base] = (uint32_t)i;
+}
+
+// destination partition of a position under an even split of n_total into parts:
+// partition p owns [p*n/parts, (p+1)*n/parts) (floor), i.e. p = the largest p with
+// floor(p*n/parts) <= pos
+__global__ void __launch_bounds__(256)
+k_even_split_dest(const uint32_t* __restrict__ pos, uint64_t n, uint64_t n_total, uint32_t parts,
+                  uint32_t* __restrict__ dest, unsigned long long* counts) {
+  extern __shared__ uint32_t s_cnt[];
+  for (uint32_t j = threadIdx.x; j < parts; j += blockDim.x) s_cnt[j] = 0;
+  __syncthreads();
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint64_t p = pos[i];
+    // first guess, then fix up the floor effects
+    uint64_t d = (p * parts + parts - 1) / n_total;
+    if (d >= parts) d = parts - 1;
+    while (d > 0 && (d * n_total) / parts > p) --d;
+    while (d + 1 < parts && ((d + 1) * n_total) / parts <= p) ++d;
+    dest[i] = (uint32_t)d;
+    atomicAdd(&s_cnt[d], 1u);
+  }
+  __syncthreads();
+  for (uint32_t j = threadIdx.x; j < parts; j += blockDim.x)
+    if (s_cnt[j]) atomicAdd(&counts[j], (unsigned long long)s_cnt[j]);
+}
+
+int make_feistel(uint64_t seed, uint64_t n_total, Feistel* f) {
+  uint32_t bits = 2;
+  while (bits < 64 && (1ull << bits) < n_total) ++bits;
+  if (bits & 1) ++bits;
+  f->key = (uint32_t)seed;
+  f->tweak = (uint32_t)(seed >> 32);
+  f->half_bits = bits / 2;
+  f->half_mask = (1ull << (bits / 2)) - 1;
+  f->n = n_total;
+  return XCHG_OK;
+}
+
+int blocks_for(uint64_t n) {
+  return (int)std::max<uint64_t>(1, std::min<uint64_t>((n + 255) / 256, (uint64_t)xchg_sm_count() * 8));
+}
+
+}  // namespace
+
+extern "C" int xchg_shuffle_positions(uint64_t seed, uint64_t n_total, uint64_t first, uint64_t count,
+                                      int inverse, uint32_t* out, void* stream) {
+  if (count == 0) return XCHG_OK;
+  XCHG_REQUIRE(out != nullptr, "NULL out");
+  XCHG_REQUIRE(n_total >= 1 && first + count <= n_total, "range [first, first+count) exceeds n_total");
+  if (n_total > 0xFFFFFFFFull) {
+    xchg_set_error("xchg_shuffle_positions: n_total=%llu exceeds 2^32-1 (positions are uint32)",
+                   (unsigned long long)n_total);
+    return XCHG_ERR_LIMIT;
+  }
+  Feistel f;
+  make_feistel(seed, n_total, &f);
+  XCHG_LAUNCH(XK_SHUFFLE, (cudaStream_t)stream,
+              k_shuffle_positions<<<blocks_for(count), 256, 0, (cudaStream_t)stream>>>(f, first, count,
+                                                                                     inverse, out));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+extern "C" int xchg_invert_permutation(const uint32_t* pos, uint64_t n, uint64_t base, uint32_t* inv_out,
+                                       void* stream) {
+  if (n == 0) return XCHG_OK;
+  XCHG_REQUIRE(pos && inv_out, "NULL pos / inv_out");
+  XCHG_LAUNCH(XK_SHUFFLE, (cudaStream_t)stream,
+              k_invert_permutation<<<blocks_for(n), 256, 0, (cudaStream_t)stream>>>(pos, n, base, inv_out));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+extern "C" int xchg_even_split_dest(const uint32_t* pos, uint64_t n, uint64_t n_total, uint32_t parts,
+                                    uint32_t* dest_out, uint64_t* counts_out, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  XCHG_REQUIRE(parts >= 1 && parts <= 8192, "parts must be in [1, 8192]");
+  XCHG_REQUIRE(counts_out != nullptr, "NULL counts_out");
+  XCHG_CUDA_TRY(cudaMemsetAsync(counts_out, 0, (size_t)parts * 8, s));
+  if (n == 0) return XCHG_OK;
+  XCHG_REQUIRE(pos && dest_out, "NULL pos / dest_out");
+  XCHG_REQUIRE(n_total >= 1, "n_total must be >= 1");
+  XCHG_LAUNCH(XK_SHUFFLE, s,
+              k_even_split_dest<<<blocks_for(n), 256, (size_t)parts * 4, s>>>(
+                  pos, n, n_total, parts, dest_out, (unsigned long long*)counts_out));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}

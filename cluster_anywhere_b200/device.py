@@ -652,3 +652,34 @@ def sort_u32(rt: Runtime, keys: torch.Tensor, n: int) -> torch.Tensor:
     rt.call("xchg_sort_column", _vp(keys), _cabi.U32, 0, None, 0, None, n, _vp(perm), None, _vp(ws),
             ws_bytes, rt.stream, launches=6)
     return perm
+
+
+# ---------------------------------------------------------------------------
+# Random shuffle (K7)
+# ---------------------------------------------------------------------------
+
+def resolve_seed(seed: Optional[int]) -> int:
+    """``None`` -> fresh OS entropy (numpy's RandomState(None) does the same,
+    arrow_block.py:230); otherwise the seed folded to 64 bits."""
+    if seed is None:
+        return int.from_bytes(os.urandom(8), "little")
+    return int(seed) & 0xFFFFFFFFFFFFFFFF
+
+
+def shuffle_positions(rt: Runtime, seed: int, n_total: int, first: int, count: int,
+                      inverse: bool) -> torch.Tensor:
+    """K7: ``P(first..first+count)`` (or ``P^-1``) of the seeded permutation of
+    ``[0, n_total)`` as a uint32 array (int32 tensor)."""
+    out = rt.empty(count, torch.int32)
+    rt.call("xchg_shuffle_positions", int(seed), n_total, first, count, int(bool(inverse)),
+            _vp(out), rt.stream)
+    return out
+
+
+def shuffle_table(rt: Runtime, table: DeviceTable, seed: Optional[int]) -> DeviceTable:
+    """Device ``random_shuffle``: ``take(P^-1(0..n))``."""
+    n = table.num_rows
+    if n == 0:
+        return table
+    idx = shuffle_positions(rt, resolve_seed(seed), n, 0, n, inverse=True)
+    return take_table(rt, table, idx, n)

@@ -252,3 +252,92 @@ class DeviceExchange:
                                 group=None) -> List[pa.Table]:
         """This rank's host blocks in, this rank's run of the sorted output blocks out."""
         return self.export(self.sort_distributed(self.stage(blocks), sort_key, boundaries, seed, group))
+
+    # -- random shuffle --------------------------------------------------------------
+    def random_shuffle(self, ds: DeviceDataset, seed: Optional[int],
+                       num_outputs: Optional[int] = None, group=None,
+                       force_exchange: bool = False) -> DeviceDataset:
+        """``Dataset.random_shuffle(seed)`` on resident blocks (all ranks' blocks when a
+        process group is up).
+
+        The reference permutes every block, deals its rows into R equal slices, sends
+        slice j to reducer j and permutes again there (shuffle_task_spec.py:81-123):
+        a random, even spread of every block over the R outputs followed by a random
+        order inside each output.  Here ONE seeded permutation P of all N rows (K7)
+        gives row g (global id = rows of earlier ranks + local row) the output
+        position P(g); output block j is the even slice [j*N/R, (j+1)*N/R) of that
+        order, R = number of input blocks (random_shuffle.py:29-83).  Same seed ->
+        same output, whatever the number of GPUs.
+
+        One GPU: ``take(P^-1(0..N))``.  G GPUs: every rank evaluates P on its own rows,
+        orders them by destination block (stable one/two-digit radix pass), gathers
+        (K5), all-to-all-v over NVLink, and the receiver inverts the received
+        positions into its gather index."""
+        from . import collective as coll
+
+        rt = self.rt
+        rank, G = coll.world(group)
+        seed64 = dev.resolve_seed(seed)
+        if G > 1 and seed is None:  # every rank must use the same permutation
+            seed64 = coll.all_gather_object(seed64, group)[0]
+        schema = None if ds.table is None else ds.table.schema
+        if G == 1 and not force_exchange:
+            info = [(ds.num_blocks, ds.num_rows, schema)]
+        else:
+            info = coll.all_gather_object((ds.num_blocks, ds.num_rows, schema), group)
+        n_total = sum(i[1] for i in info)
+        r_total = max(1, num_outputs if num_outputs is not None else sum(i[0] for i in info))
+        schema = next((i[2] for i in info if i[2] is not None), None)
+        blocks_per_rank = [i[0] for i in info]
+        if num_outputs is None and all(b > 0 for b in blocks_per_rank):
+            out_per_rank = list(blocks_per_rank)
+        else:
+            out_per_rank = [r_total // G + (1 if g < r_total % G else 0) for g in range(G)]
+        ob = np.concatenate([[0], np.cumsum(out_per_rank)]).astype(int)
+        my_blocks = int(out_per_rank[rank])
+        if n_total == 0 or schema is None:
+            return DeviceDataset(None, [(0, 0)] * my_blocks)
+        starts = [(j * n_total) // r_total for j in range(r_total + 1)]  # block j = [starts[j], starts[j+1])
+        base = starts[int(ob[rank])]
+        my_ranges = [(starts[j] - base, starts[j + 1] - base) for j in range(int(ob[rank]), int(ob[rank + 1]))]
+
+        if G == 1 and not force_exchange:
+            idx = dev.shuffle_positions(rt, seed64, n_total, 0, n_total, inverse=True)
+            return DeviceDataset(dev.take_table(rt, ds.table, idx, n_total), my_ranges)
+
+        table = ds.table if ds.table is not None else coll.empty_device_table(rt, schema)
+        n = table.num_rows
+        first = int(sum(i[1] for i in info[:rank]))
+        send_counts = [0] * G
+        pos_col = dev.DeviceColumn(pa.uint32(), n, "fixed", 4, rt.empty(0))
+        send_table = table
+        if n > 0:
+            pos = dev.shuffle_positions(rt, seed64, n_total, first, n, inverse=False)
+            dest = rt.empty(n, torch.int32)
+            counts = rt.zeros(r_total, torch.int64)
+            rt.call("xchg_even_split_dest", dev._vp(pos), n, n_total, r_total, dev._vp(dest),
+                    dev._vp(counts), rt.stream)
+            perm = dev.sort_u32(rt, dest, n)
+            per_block = counts.tolist()
+            for g in range(G):
+                send_counts[g] = int(sum(per_block[int(ob[g]):int(ob[g + 1])]))
+            send_table = dev.take_table(rt, table, perm, n)
+            pos_sorted = rt.empty(n, torch.int32)
+            rt.call("xchg_gather_fixed", dev._vp(pos), 4, dev._vp(perm), n, dev._vp(pos_sorted), rt.stream)
+            pos_col = dev.DeviceColumn(pa.uint32(), n, "fixed", 4, pos_sorted.view(torch.uint8))
+        wire = dev.DeviceTable(list(send_table.names) + ["__xchg_pos"], list(send_table.columns) + [pos_col],
+                               n, send_table.schema.append(pa.field("__xchg_pos", pa.uint32())))
+        recv = coll.exchange_table(rt, wire, send_counts, group)
+        m = recv.num_rows
+        if my_blocks == 0 or m == 0:
+            assert m == 0
+            return DeviceDataset(None, [(0, 0)] * my_blocks)
+        inv = rt.empty(m, torch.int32)
+        rt.call("xchg_invert_permutation", dev._vp(recv.columns[-1].data), m, base, dev._vp(inv), rt.stream)
+        body = dev.DeviceTable(list(send_table.names), recv.columns[:-1], m, send_table.schema)
+        return DeviceDataset(dev.take_table(rt, body, inv, m), my_ranges)
+
+    def random_shuffle_blocks(self, blocks: Sequence[pa.Table], seed: Optional[int],
+                              num_outputs: Optional[int] = None, group=None) -> List[pa.Table]:
+        """Host blocks in, shuffled host blocks out (this rank's run when distributed)."""
+        return self.export(self.random_shuffle(self.stage(blocks), seed, num_outputs, group))

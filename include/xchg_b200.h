@@ -251,6 +251,33 @@ int xchg_offsets_uniform64(uint64_t count, uint64_t width, int64_t base, int64_t
 int xchg_offsets_check_uniform(const int64_t* off, uint64_t n_rows, uint64_t width,
                                uint32_t* flag_out, void* stream);
 
+/* ------------------------------------------------------------- shuffle ---- */
+
+/*
+ * Seeded random permutation of [0, n_total).  Replaces
+ * numpy.random.RandomState(seed).permutation(n) in ArrowBlockAccessor.random_shuffle
+ * (python/ray/data/_internal/arrow_block.py:225-231; called from
+ * ShuffleTaskSpec.map/reduce, planner/exchange/shuffle_task_spec.py:81-84, :120-123).
+ * The reference's MT19937 values are not pinned by its tests; this permutation is a
+ * Philox-2x32-10-keyed 4-round Feistel network with cycle walking: a bijection of
+ * [0, n_total) for every seed, evaluable per element and per sub-range.
+ *   inverse = 0:  out[i] = P(first + i)       output position of source row first+i
+ *   inverse = 1:  out[i] = P^-1(first + i)    source row of output position first+i
+ * so `take(P^-1(0..n))` is the shuffled table.  n_total <= 2^32 - 1.
+ */
+int xchg_shuffle_positions(uint64_t seed, uint64_t n_total, uint64_t first, uint64_t count,
+                           int inverse, uint32_t* out, void* stream);
+/* inv_out[pos[i] - base] = i  (pos holds n distinct values in [base, base+n)):
+ * turns "row i goes to position pos[i]" into the gather index of that range. */
+int xchg_invert_permutation(const uint32_t* pos, uint64_t n, uint64_t base, uint32_t* inv_out,
+                            void* stream);
+/* Owner of each position under an even split of [0, n_total) into `parts`
+ * contiguous ranges (range p = [floor(p*n_total/parts), floor((p+1)*n_total/parts)) ):
+ * dest_out[i] = p, counts_out[p] = rows (uint64[parts], zeroed here).  The shuffle's
+ * analogue of the reference's R equal slices per mapper (shuffle_task_spec.py:90-93). */
+int xchg_even_split_dest(const uint32_t* pos, uint64_t n, uint64_t n_total, uint32_t parts,
+                         uint32_t* dest_out, uint64_t* counts_out, void* stream);
+
 /*
  * Exchange-side utilities.  The reference moves map outputs between tasks as
  * Arrow IPC objects through the plasma store

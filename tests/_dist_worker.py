@@ -68,6 +68,18 @@ def main():
                 assert g.num_rows == e.num_rows
                 if e.num_rows:
                     assert tables_equal(g, e)
+    # random_shuffle: the G-rank result is the single-process result, take(P^-1(0..N))
+    for seed, nout in ((42, None), (7, 3)):
+        out = ex.random_shuffle_blocks(mine, seed, num_outputs=nout)
+        outs = [None] * w
+        dist.all_gather_object(outs, out)
+        got = [b for part in outs for b in part]
+        n = full.num_rows
+        idx = FakeLib()._feistel(seed, n, np.arange(n, dtype=np.uint64), True).astype(np.int64)
+        assert tables_equal(pa.concat_tables([g for g in got if g.num_rows]), full.take(idx)), seed
+        r_total = len(all_blocks) if nout is None else nout
+        assert [g.num_rows for g in got] == [(j + 1) * n // r_total - j * n // r_total
+                                             for j in range(r_total)]
     dist.barrier()
     if r == 0:
         print("DIST-OK", w)

@@ -362,3 +362,71 @@ class FakeLib:
         i = _arr(inp, np.int64, count)
         _arr(out, np.int64, count)[:] = i - i[0] + base
         return 0
+
+    # -- shuffle -----------------------------------------------------------------
+    @staticmethod
+    def _philox2x32_10(c0, c1, key):
+        c0 = c0.astype(np.uint64)
+        c1 = c1.astype(np.uint64)
+        key = np.uint64(key)
+        M = np.uint64(0xD256D193)
+        m32 = np.uint64(0xFFFFFFFF)
+        for _ in range(10):
+            p = M * c0
+            hi, lo = p >> np.uint64(32), p & m32
+            c0 = (hi ^ key ^ c1) & m32
+            c1 = lo
+            key = (key + np.uint64(0x9E3779B9)) & m32
+        return c0
+
+    def _feistel(self, seed, n_total, x, inverse):
+        bits = 2
+        while (1 << bits) < n_total:
+            bits += 1
+        bits += bits & 1
+        hb = bits // 2
+        mask = np.uint64((1 << hb) - 1)
+        key, tweak = seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF
+        x = x.astype(np.uint64).copy()
+        todo = np.ones(len(x), dtype=bool)
+        while todo.any():
+            v = x[todo]
+            L, R = v >> np.uint64(hb), v & mask
+            rounds = range(4) if not inverse else range(3, -1, -1)
+            for r in rounds:
+                tw = np.full(len(v), (tweak ^ ((0x9E3779B9 * (r + 1)) & 0xFFFFFFFF)), dtype=np.uint64)
+                if not inverse:
+                    t = L ^ (self._philox2x32_10(R, tw, key) & mask)
+                    L, R = R, t
+                else:
+                    t = R ^ (self._philox2x32_10(L, tw, key) & mask)
+                    R, L = L, t
+            v = (L << np.uint64(hb)) | R
+            x[todo] = v
+            todo[todo] = v >= np.uint64(n_total)
+        return x
+
+    def xchg_shuffle_positions(self, seed, n_total, first, count, inverse, out, stream):
+        if count == 0:
+            return 0
+        x = np.arange(first, first + count, dtype=np.uint64)
+        _arr(out, np.uint32, count)[:] = self._feistel(int(seed), int(n_total), x, bool(inverse)).astype(np.uint32)
+        return 0
+
+    def xchg_invert_permutation(self, pos, n, base, inv, stream):
+        if n == 0:
+            return 0
+        p = _arr(pos, np.uint32, n).astype(np.int64) - base
+        _arr(inv, np.uint32, n)[p] = np.arange(n, dtype=np.uint32)
+        return 0
+
+    def xchg_even_split_dest(self, pos, n, n_total, parts, dest, counts, stream):
+        _arr(counts, np.uint64, parts)[:] = 0
+        if n == 0:
+            return 0
+        p = _arr(pos, np.uint32, n).astype(np.int64)
+        starts = np.array([(k * n_total) // parts for k in range(parts)], dtype=np.int64)
+        d = np.searchsorted(starts, p, side="right") - 1
+        _arr(dest, np.uint32, n)[:] = d.astype(np.uint32)
+        _arr(counts, np.uint64, parts)[:] = np.bincount(d, minlength=parts).astype(np.uint64)
+        return 0
