@@ -29,6 +29,10 @@ import tempfile
 import threading
 import time
 
+# receive-side buffer sizes change from step to step (sampled splitters): let the
+# caching allocator grow segments instead of cudaMalloc-ing a new block per size
+os.environ.setdefault("PYTORCH_CUDA_ALLOC_CONF", "expandable_segments:True")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
@@ -353,7 +357,7 @@ def run_b200(args):
 
     lib = _cabi.load()
     rt = dev.Runtime()
-    ex = DeviceExchange(rt)
+    ex = DeviceExchange(rt, trace=args.trace)
     n = args.rows_per_gpu
     ds, keys, data = build_resident_dataset(rt, n, args.blocks_per_gpu, seed=2 + rank)
     sk = SortKey("c_0")
@@ -375,6 +379,7 @@ def run_b200(args):
         out = one_step(i)
         del out
     barrier()
+    ex.phase_ms = {}
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -498,6 +503,9 @@ def run_b200(args):
                "sample": sample, "gb_per_s": ref.total_rows / t_cpu * 2 * ROW_BYTES / 1e9,
                "primitives_only_value": ref.total_rows / t_prim}
 
+    if args.trace:
+        print(f"[trace rank {rank}] phase ms over the {args.steps} timed steps: "
+              + json.dumps({k: round(v, 2) for k, v in ex.phase_ms.items()}), file=sys.stderr, flush=True)
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -531,6 +539,9 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--trace", action="store_true",
+                    help="diagnostics: synchronise after every phase of the distributed sort and print "
+                         "per-phase wall-clock ms (serialises the pipeline; not a bench number)")
     ap.add_argument("--cpu-rows-per-block", type=int, default=2_000_000)
     ap.add_argument("--cpu-blocks", type=int, default=0, help="default: one block per host core")
     args = ap.parse_args()

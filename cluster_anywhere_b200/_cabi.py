@@ -38,6 +38,19 @@ _SIGNATURES = {
     "xchg_shuffle_positions": (c_int, [c_uint64, c_uint64, c_uint64, c_uint64, c_int, _P, _P]),
     "xchg_invert_permutation": (c_int, [_P, c_uint64, c_uint64, _P, _P]),
     "xchg_even_split_dest": (c_int, [_P, c_uint64, c_uint64, c_uint32, _P, _P, _P]),
+    "xchg_hash_table_bytes": (c_int, [c_uint64, ctypes.POINTER(c_uint64)]),
+    "xchg_hash_groups": (c_int, [_P, _P, c_int64, c_uint64, c_uint64, _P, c_uint64, _P, _P, _P,
+                                 ctypes.POINTER(c_uint64), _P]),
+    "xchg_group_ids": (c_int, [_P, _P, c_uint64, _P, c_uint64, c_uint64, _P, _P, _P]),
+    "xchg_agg_stats_init": (c_int, [_P, _P, c_uint64, _P]),
+    "xchg_agg_count_rows": (c_int, [_P, c_uint64, _P, _P]),
+    "xchg_agg_accumulate": (c_int, [_P, _P, c_int, _P, c_int64, c_uint64, c_uint64, _P, c_int, _P]),
+    "xchg_agg_accumulate_m2": (c_int, [_P, _P, c_int, _P, c_int64, c_uint64, c_uint64, _P, _P, _P]),
+    "xchg_agg_merge_rows": (c_int, [_P, _P, c_uint64, _P, _P]),
+    "xchg_agg_merge_states": (c_int, [_P, _P, c_uint64, c_int, c_uint64, _P, _P, _P]),
+    "xchg_agg_pack_states": (c_int, [c_uint64, _P, _P, _P, _P]),
+    "xchg_agg_finalize": (c_int, [c_int, c_int, c_int, c_int, c_uint64, _P, _P, _P, _P, _P, _P]),
+    "xchg_group_keys_out": (c_int, [_P, c_int, c_uint64, _P, _P]),
     "xchg_bitmap_unpack": (c_int, [_P, c_int64, c_uint64, _P, _P]),
     "xchg_bitmap_pack": (c_int, [_P, c_uint64, _P, _P, _P]),
     "xchg_offsets_rebase": (c_int, [_P, c_uint64, c_int64, _P, _P]),

@@ -199,3 +199,89 @@ class B200ArrowBlockAccessor:
             t = pa.concat_tables(blocks, promote_options="permissive")
             ret = B200ArrowBlockAccessor(t, runtime).sort(sort_key)
         return ret, B200ArrowBlockAccessor(ret, runtime).get_metadata(exec_stats=stats.build())
+
+    # -- aggregate -------------------------------------------------------------
+    def _reduce(self, kind: int, on: str, ignore_nulls: bool, ddof: int = 1):
+        """One global group over this block (the block reducers of arrow_block.py:346-423)."""
+        from . import aggregate as agg
+
+        cls = {agg.KIND_SUM: agg.Sum, agg.KIND_MIN: agg.Min, agg.KIND_MAX: agg.Max,
+               agg.KIND_MEAN: agg.Mean}[kind]
+        if self.num_rows() == 0:
+            return None
+        rt = self.rt
+        dt = dev.stage_table(rt, self._table.select([on]))
+        out = agg.aggregate_table(rt, dt, None, [cls(on, ignore_nulls=ignore_nulls)])
+        return dev.export_table(rt, out).column(0)[0].as_py()
+
+    def count(self, on: str) -> Optional[int]:
+        """arrow_block.py:346-360: number of non-null values of ``on``."""
+        if self.num_rows() == 0:
+            return None
+        col = self._table[on]
+        return len(col) - col.null_count
+
+    def sum(self, on: str, ignore_nulls: bool):
+        from . import aggregate as agg
+
+        return self._reduce(agg.KIND_SUM, on, ignore_nulls)
+
+    def min(self, on: str, ignore_nulls: bool):
+        from . import aggregate as agg
+
+        return self._reduce(agg.KIND_MIN, on, ignore_nulls)
+
+    def max(self, on: str, ignore_nulls: bool):
+        from . import aggregate as agg
+
+        return self._reduce(agg.KIND_MAX, on, ignore_nulls)
+
+    def mean(self, on: str, ignore_nulls: bool):
+        from . import aggregate as agg
+
+        return self._reduce(agg.KIND_MEAN, on, ignore_nulls)
+
+    @staticmethod
+    def _group_key(sort_key: SortKey) -> Optional[str]:
+        cols = sort_key.get_columns() if sort_key is not None else []
+        if len(cols) > 1:
+            raise NotImplementedError(
+                "group-by on several key columns is not offloaded to the B200 engine yet "
+                f"(got {cols}); use the reference path")
+        return cols[0] if cols else None
+
+    def combine(self, sort_key: SortKey, aggs) -> pa.Table:
+        """arrow_block.py:452-526: one row per group with the partially combined
+        accumulators (K8).  The reference requires the block to be sorted by key and
+        walks its runs; the hash aggregate does not need the order and emits the groups
+        sorted by key, as the reference does.  ``sort_key`` without columns = one global
+        group (arrow_block.py:473-476)."""
+        from . import aggregate as agg
+
+        key = self._group_key(sort_key)
+        if self.num_rows() == 0:
+            return self._empty_table()
+        rt = self.rt
+        dt = dev.stage_table(rt, agg.prune_columns(self._table, [key] if key else [], aggs))
+        out = agg.aggregate_table(rt, dt, key, aggs, finalize=False)
+        return dev.export_table(rt, out)
+
+    @staticmethod
+    def aggregate_combined_blocks(blocks: List[pa.Table], sort_key: SortKey, aggs, finalize: bool = True,
+                                  runtime: Optional[dev.Runtime] = None) -> Tuple[pa.Table, BlockMetadata]:
+        """arrow_block.py:544-663: merge the partial blocks of one key range (K9) and
+        finalize (``finalize=False`` keeps accumulators: the push-based merge stage,
+        push_based_shuffle_task_scheduler.py:715)."""
+        from . import aggregate as agg
+
+        stats = BlockExecStats.builder()
+        key = B200ArrowBlockAccessor._group_key(sort_key)
+        blocks = [b for b in blocks if b.num_rows > 0 and b.num_columns > 0]
+        if not blocks:
+            ret = empty_table()
+        else:
+            rt = runtime or dev.default_runtime()
+            t = pa.concat_tables(blocks, promote_options="default")
+            out = agg.aggregate_table(rt, dev.stage_table(rt, t), key, aggs, finalize=finalize)
+            ret = dev.export_table(rt, out)
+        return ret, B200ArrowBlockAccessor(ret, runtime).get_metadata(exec_stats=stats.build())

@@ -50,8 +50,24 @@ class DeviceDataset:
 
 
 class DeviceExchange:
-    def __init__(self, runtime: Optional[dev.Runtime] = None):
+    def __init__(self, runtime: Optional[dev.Runtime] = None, trace: bool = False):
         self.rt = runtime or dev.default_runtime()
+        # trace=True: synchronise after every phase and accumulate wall-clock ms per
+        # phase in ``phase_ms`` (diagnostics only -- it serialises the pipeline)
+        self.trace = trace
+        self.phase_ms = {}
+        self._t_last = None
+
+    def _phase(self, name: Optional[str]):
+        if not self.trace:
+            return
+        import time
+
+        self.rt.synchronize()
+        now = time.perf_counter()
+        if name is not None and self._t_last is not None:
+            self.phase_ms[name] = self.phase_ms.get(name, 0.0) + (now - self._t_last) * 1e3
+        self._t_last = now
 
     # -- staging ---------------------------------------------------------------
     def stage(self, blocks: Sequence[pa.Table]) -> DeviceDataset:
@@ -191,8 +207,10 @@ class DeviceExchange:
         if G == 1 and not force_exchange:  # force_exchange: run the map/exchange/reduce path anyway
             return self.sort(ds, sort_key, boundaries=boundaries, seed=seed)
         rt = self.rt
+        self._phase(None)
         schema = None if ds.table is None else ds.table.schema
         info = coll.all_gather_object((ds.num_blocks, ds.num_rows, schema), group)
+        self._phase("dist.gather_info")
         blocks_per_rank = [i[0] for i in info]
         total_rows = sum(i[1] for i in info)
         schema = next((i[2] for i in info if i[2] is not None), None)
@@ -218,6 +236,7 @@ class DeviceExchange:
             samples = [t for part in coll.all_gather_object(mine, group) for t in part]
             boundaries = (SortTaskSpec.boundaries_from_samples(samples, sort_key, r_total)
                           if r_total > 1 else [])
+        self._phase("dist.sample_boundaries")
         ncols = len(sort_key.get_columns())
         none_tuple = (None,) * ncols
         # splitters sit between consecutive ranks that own output blocks: the block
@@ -235,8 +254,11 @@ class DeviceExchange:
             perm = dev.sort_u32(rt, dest, n)
             for d, cnt in enumerate(counts.tolist()):
                 send_counts[owners[d]] = int(cnt)
+            self._phase("dist.assign_and_order")
             send_table = dev.take_table(rt, table, perm, n)
+            self._phase("dist.gather_send")
         recv = coll.exchange_table(rt, send_table, send_counts, group)
+        self._phase("dist.all_to_all")
 
         # ---- reduce: stable sort of the received runs, cut into this rank's blocks ----
         if my_blocks == 0:
@@ -244,8 +266,9 @@ class DeviceExchange:
             return DeviceDataset(None, [])
         lo_b, hi_b = int(ob[rank]), int(ob[rank + 1])
         local_bounds = list(boundaries[lo_b:hi_b - 1])
-        return self.sort(DeviceDataset(recv, [(0, recv.num_rows)]), sort_key,
-                         boundaries=local_bounds)
+        out = self.sort(DeviceDataset(recv, [(0, recv.num_rows)]), sort_key, boundaries=local_bounds)
+        self._phase("dist.reduce_sort")
+        return out
 
     def sort_blocks_distributed(self, blocks: Sequence[pa.Table], sort_key: SortKey,
                                 boundaries: Optional[list] = None, seed: int = 0,
@@ -341,3 +364,120 @@ class DeviceExchange:
                               num_outputs: Optional[int] = None, group=None) -> List[pa.Table]:
         """Host blocks in, shuffled host blocks out (this rank's run when distributed)."""
         return self.export(self.random_shuffle(self.stage(blocks), seed, num_outputs, group))
+
+    # -- group-by aggregate ------------------------------------------------------------
+    def aggregate(self, ds: DeviceDataset, key: Optional[str], aggs: Sequence,
+                  boundaries: Optional[list] = None, seed: int = 0, group=None,
+                  force_exchange: bool = False) -> DeviceDataset:
+        """``Dataset.groupby(key).aggregate(*aggs)`` on resident blocks (all ranks'
+        blocks when a process group is up).
+
+        Reference: generate_aggregate_fn (python/ray/data/_internal/planner/aggregate.py:
+        42-98): boundaries sampled on the key, R = number of input blocks (``key=None``:
+        one output block with one row, :61-63), then SortAggregateTaskSpec map / reduce
+        under the pull- or push-based schedule.  The result is fully determined: one row
+        per distinct key, sorted by key, cut into R range partitions by the boundaries.
+
+        One GPU: ONE hash aggregate over all resident rows (K8) and the boundary search
+        over the sorted groups (K4).  G GPUs: local hash aggregate -> partial rows (one
+        per local group) -> range split by the G-1 splitters (K4) -> all-to-all-v of the
+        partials over NVLink (a few bytes per GROUP, not per row) -> merge (K9) ->
+        finalize -> this rank's run of output blocks."""
+        from .. import aggregate as agg
+        from . import collective as coll
+
+        rt = self.rt
+        rank, G = coll.world(group)
+        dist_path = G > 1 or force_exchange
+        agg.check_aggs(aggs)
+        schema = None if ds.table is None else ds.table.schema
+        info = (coll.all_gather_object((ds.num_blocks, ds.num_rows, schema), group) if dist_path
+                else [(ds.num_blocks, ds.num_rows, schema)])
+        blocks_per_rank = [i[0] for i in info]
+        total_rows = sum(i[1] for i in info)
+        schema = next((i[2] for i in info if i[2] is not None), None)
+        if key is None:
+            r_total = 1
+        else:
+            r_total = max(1, sum(blocks_per_rank) if boundaries is None else len(boundaries) + 1)
+        if boundaries is None and key is not None and all(b > 0 for b in blocks_per_rank):
+            out_per_rank = list(blocks_per_rank)
+        else:
+            out_per_rank = [r_total // G + (1 if g < r_total % G else 0) for g in range(G)]
+        ob = np.concatenate([[0], np.cumsum(out_per_rank)]).astype(int)
+        my_blocks = int(out_per_rank[rank])
+        if total_rows == 0 or schema is None:
+            return DeviceDataset(None, [(0, 0)] * my_blocks)
+        for a in aggs:
+            a._validate(schema)
+        sk = SortKey(key) if key is not None else SortKey()
+        if key is not None:
+            sk.validate_schema(schema)
+            if boundaries is None:
+                first_block = int(sum(blocks_per_rank[:rank]))
+                m = max(1, sum(blocks_per_rank))
+                mine = self.sample_keys(ds, sk, int(r_total * 10 / m), seed, first_block)
+                samples = ([t for part in coll.all_gather_object(mine, group) for t in part]
+                           if dist_path else mine)
+                boundaries = (SortTaskSpec.boundaries_from_samples(samples, sk, r_total)
+                              if r_total > 1 else [])
+            boundaries = [(None,) if b is None else b for b in boundaries]
+        else:
+            boundaries = []
+
+        def cut_ranges(result, bounds, nblocks):
+            if result is None:
+                return [(0, 0)] * nblocks
+            cuts = agg.group_cut_points(rt, result, key, bounds) if (key is not None and bounds) else []
+            ranges, last = [], 0
+            for c in cuts:
+                ranges.append((last, c))
+                last = c
+            ranges.append((last, result.num_rows))
+            return ranges
+
+        if not dist_path:
+            out = agg.aggregate_table(rt, ds.table, key, aggs, finalize=True)
+            return DeviceDataset(out, cut_ranges(out, boundaries, r_total))
+
+        # ---- map: local partial aggregate, split by destination rank ----
+        owners = [g for g in range(G) if out_per_rank[g] > 0]
+        partial = (agg.aggregate_table(rt, ds.table, key, aggs, finalize=False)
+                   if ds.table is not None and ds.num_rows > 0 else None)
+        pschemas = coll.all_gather_object(None if partial is None else partial.schema, group)
+        pschema = next(s for s in pschemas if s is not None)
+        send_counts = [0] * G
+        if partial is None:
+            partial = coll.empty_device_table(rt, pschema)
+        elif key is None:
+            send_counts[owners[0]] = partial.num_rows
+        else:
+            splitters = [boundaries[int(ob[g + 1]) - 1] for g in owners[:-1]]
+            cuts = agg.group_cut_points(rt, partial, key, splitters) if splitters else []
+            edges = [0] + list(cuts) + [partial.num_rows]
+            for d, g in enumerate(owners):
+                send_counts[g] = max(0, edges[d + 1] - edges[d])
+        recv = coll.exchange_table(rt, partial, send_counts, group)
+        # ---- reduce: merge the partials of this rank's key range (K9), finalize ----
+        if my_blocks == 0:
+            return DeviceDataset(None, [])
+        out = agg.aggregate_table(rt, recv, key, aggs, finalize=True) if recv.num_rows else None
+        local_bounds = list(boundaries[int(ob[rank]):int(ob[rank + 1]) - 1])
+        return DeviceDataset(out, cut_ranges(out, local_bounds, my_blocks))
+
+    def aggregate_blocks(self, blocks: Sequence[pa.Table], key: Optional[str], aggs: Sequence,
+                         boundaries: Optional[list] = None, seed: int = 0, group=None) -> List[pa.Table]:
+        """Host blocks in, aggregated host blocks out (this rank's run when distributed).
+        Unused columns are pruned before staging (aggregate_task_spec.py:76-109)."""
+        from .. import aggregate as agg
+
+        agg.check_aggs(aggs)
+        for b in blocks:  # planner/aggregate.py:54-55: aggregates are validated against the schema
+            if b.num_columns > 0:
+                for a in aggs:
+                    a._validate(b.schema)
+                if key is not None:
+                    SortKey(key).validate_schema(b.schema)
+                break
+        pruned = [agg.prune_columns(b, [key] if key is not None else [], aggs) for b in blocks]
+        return self.export(self.aggregate(self.stage(pruned), key, aggs, boundaries, seed, group))

@@ -278,6 +278,84 @@ int xchg_invert_permutation(const uint32_t* pos, uint64_t n, uint64_t base, uint
 int xchg_even_split_dest(const uint32_t* pos, uint64_t n, uint64_t n_total, uint32_t parts,
                          uint32_t* dest_out, uint64_t* counts_out, void* stream);
 
+/* ----------------------------------------------------------- aggregate ---- */
+
+/*
+ * Hash group-by aggregate (one key column).  Replaces the arithmetic of
+ * ArrowBlockAccessor.combine (python/ray/data/_internal/arrow_block.py:452-526: a
+ * Python loop over groups, one pyarrow.compute call per group and aggregate,
+ * :346-423) and of aggregate_combined_blocks (:544-663: heapq.merge over rows), for
+ * Count / Sum / Min / Max / Mean / Std (python/ray/data/aggregate.py:97-326) with the
+ * null policy of _internal/null_aggregate.py:11-25.
+ *
+ * Call sequence
+ *   xchg_normalize_keys(key column)                      -> radix keys (row order)
+ *   xchg_hash_groups(...)                                -> slot per row, group list
+ *   xchg_sort_column(group keys as XCHG_U64)             -> groups in output order
+ *                                                           (numbers < NaN < null)
+ *   xchg_group_ids(...)                                  -> dense group id per row
+ *   xchg_agg_stats_init / xchg_agg_count_rows / xchg_agg_accumulate[_m2]   (raw rows)
+ *     or xchg_agg_merge_rows / xchg_agg_merge_states                      (partials)
+ *   xchg_agg_finalize (per aggregate)  or  xchg_agg_pack_states (emit partials)
+ *   xchg_group_keys_out                                  -> key column of the result
+ *
+ * Per value column the statistics live in `stats`: 5 arrays of num_groups 8-byte
+ * words [cnt | sum | min | max | nan] (sum is int64 for integer columns, double
+ * otherwise; min/max are order-preserving encodings) plus an optional double m2[]
+ * for Std.  A PARTIAL row (map-side output, the reference's accumulator columns
+ * _internal/null_aggregate.py:28-45) is 6 words: cnt, sum, min, max, nan, M2.
+ */
+/* Bytes of table workspace for `capacity` slots (a power of two, >= 2 x distinct keys). */
+int xchg_hash_table_bytes(uint64_t capacity, uint64_t* bytes_out);
+/*
+ * Build the table.  slot_out[i] = slot of row i; group_keys_out / group_slots_out
+ * (capacity + 2 entries each, caller-allocated) receive the num_groups distinct
+ * (radix key, slot) pairs in table order, null group last.  Null rows (validity)
+ * form their own group.  Synchronises the stream (reads the group count);
+ * XCHG_ERR_LIMIT if the table overflowed.
+ */
+int xchg_hash_groups(const uint64_t* norm_keys, const uint8_t* validity, int64_t validity_bit_offset,
+                     uint64_t n, uint64_t capacity, void* table_ws, uint64_t table_ws_bytes,
+                     uint32_t* slot_out, uint64_t* group_keys_out, uint32_t* group_slots_out,
+                     uint64_t* num_groups_out, void* stream);
+/* order = permutation that sorts the group list (from xchg_sort_column);
+ * row_gid_out[i] = position of row i's group in that order. */
+int xchg_group_ids(const uint32_t* order, const uint32_t* group_slots, uint64_t num_groups,
+                   const uint32_t* slot, uint64_t n, uint64_t capacity, void* table_ws,
+                   uint32_t* row_gid_out, void* stream);
+/* stats: 5 * num_groups words, m2 (may be NULL): num_groups doubles. */
+int xchg_agg_stats_init(uint64_t* stats, double* m2, uint64_t num_groups, void* stream);
+/* rows[g] += number of rows of group g (Count, and the ignore_nulls=False test);
+ * row_gid NULL = one global group (groupby key None, aggregate.py:61-63). */
+int xchg_agg_count_rows(const uint32_t* row_gid, uint64_t n, uint64_t* rows, void* stream);
+/* Accumulate one value column (value_type = xchg_key_type of its storage). */
+int xchg_agg_accumulate(const uint32_t* row_gid, const void* values, int value_type,
+                        const uint8_t* validity, int64_t validity_bit_offset, uint64_t n,
+                        uint64_t num_groups, uint64_t* stats, int want_minmax, void* stream);
+/* Second pass for Std: m2[g] += (x - sum[g]/cnt[g])^2 (after xchg_agg_accumulate). */
+int xchg_agg_accumulate_m2(const uint32_t* row_gid, const void* values, int value_type,
+                           const uint8_t* validity, int64_t validity_bit_offset, uint64_t n,
+                           uint64_t num_groups, const uint64_t* stats, double* m2, void* stream);
+/* K9: the same over partial rows (partial_states: n x 6 words). */
+int xchg_agg_merge_rows(const uint32_t* row_gid, const int64_t* partial_rows, uint64_t n,
+                        uint64_t* rows, void* stream);
+int xchg_agg_merge_states(const uint32_t* row_gid, const uint64_t* partial_states, uint64_t n,
+                          int sum_is_int, uint64_t num_groups, uint64_t* stats, double* m2,
+                          void* stream);
+int xchg_agg_pack_states(uint64_t num_groups, const uint64_t* stats, const double* m2,
+                         uint64_t* partial_states_out, void* stream);
+/* kind: 0 count, 1 sum, 2 min, 3 max, 4 mean, 5 std(ddof).  out: num_groups 8-byte
+ * values (int64 for count and for sum/min/max of integer columns, double otherwise);
+ * valid_out: one byte per group (0 = null result: no non-null value, or a null with
+ * ignore_nulls = 0). */
+int xchg_agg_finalize(int kind, int ddof, int ignore_nulls, int value_type, uint64_t num_groups,
+                      const uint64_t* rows, const uint64_t* stats, const double* m2, void* out,
+                      uint8_t* valid_out, void* stream);
+/* Sorted group radix keys -> key column of the result: int64 for integer keys, double
+ * for float keys (the reference rebuilds rows from Python scalars). */
+int xchg_group_keys_out(const uint64_t* sorted_norm_keys, int key_type, uint64_t num_groups,
+                        void* out, void* stream);
+
 /*
  * Exchange-side utilities.  The reference moves map outputs between tasks as
  * Arrow IPC objects through the plasma store

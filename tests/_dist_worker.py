@@ -80,6 +80,30 @@ def main():
         r_total = len(all_blocks) if nout is None else nout
         assert [g.num_rows for g in got] == [(j + 1) * n // r_total - j * n // r_total
                                              for j in range(r_total)]
+    # groupby().aggregate(): local hash aggregate, partials over the all-to-all, merge
+    from cluster_anywhere_b200 import Count, Max, Mean, Min, Std, Sum
+    from test_aggregate import assert_tables_close
+
+    aggs = [Count(), Sum("f"), Mean("f"), Min("k"), Max("f"), Std("f", ddof=1)]
+    exp = O.groupby_aggregate(all_blocks, "k", [("count",), ("sum", "f"), ("mean", "f"), ("min", "k"),
+                                                 ("max", "f"), ("std", "f", 1)])
+    i = exp.schema.get_field_index("min(k)")
+    exp = exp.set_column(i, "min(k)", exp["min(k)"].cast(pa.int64()))
+    for bounds in (None, [(-20,), (0,), (31,)]):
+        out = ex.aggregate_blocks(mine, "k", aggs, boundaries=bounds, seed=1)
+        outs = [None] * w
+        dist.all_gather_object(outs, out)
+        got = [b for part in outs for b in part]
+        assert len(got) == (len(all_blocks) if bounds is None else len(bounds) + 1)
+        assert_tables_close(pa.concat_tables([g for g in got if g.num_rows]), exp, exact=("k",))
+        if bounds is not None:
+            ks = [g["k"].to_pylist() for g in got]
+            assert all(k is None or k < -20 for k in ks[0]) and all(-20 <= k < 0 for k in ks[1])
+    out = ex.aggregate_blocks(mine, None, [Count(), Sum("k")])
+    outs = [None] * w
+    dist.all_gather_object(outs, out)
+    got = [b for part in outs for b in part]
+    assert len(got) == 1 and got[0]["count()"].to_pylist() == [full.num_rows]
     dist.barrier()
     if r == 0:
         print("DIST-OK", w)

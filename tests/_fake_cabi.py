@@ -430,3 +430,243 @@ class FakeLib:
         _arr(dest, np.uint32, n)[:] = d.astype(np.uint32)
         _arr(counts, np.uint64, parts)[:] = np.bincount(d, minlength=parts).astype(np.uint64)
         return 0
+
+    # -- aggregate ---------------------------------------------------------------
+    # Host-memory statement of the aggregate entry points' CONTRACT (numpy; no hashing:
+    # "slot" is simply the index of the key among the distinct keys, shuffled so that
+    # callers cannot rely on table order).
+    _EMPTY = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+    def xchg_hash_table_bytes(self, capacity, out):
+        out._obj.value = capacity * 8 + (capacity + 2) * 4 + 1024
+        return 0
+
+    def xchg_hash_groups(self, norm, validity, vbit, n, capacity, ws, ws_bytes, slot_out, gkeys, gslots,
+                         ngroups, stream):
+        keys = _arr(norm, np.uint64, n)
+        valid = _bits(validity, vbit, np.arange(n, dtype=np.int64)) if _addr(validity) and n else np.ones(n, bool)
+        regular = valid & (keys != self._EMPTY)
+        uniq = np.unique(keys[regular])
+        if len(uniq) > capacity:
+            self.err = b"hash table overflowed"
+            return -4
+        rng = np.random.default_rng(len(uniq))
+        slots_of_uniq = rng.permutation(capacity)[: len(uniq)].astype(np.uint32)
+        slot = np.empty(n, dtype=np.uint32)
+        slot[regular] = slots_of_uniq[np.searchsorted(uniq, keys[regular])]
+        slot[~valid] = capacity
+        is_max = valid & (keys == self._EMPTY)
+        slot[is_max] = capacity + 1
+        _arr(slot_out, np.uint32, n)[:] = slot
+        order = np.argsort(slots_of_uniq, kind="stable")  # table order
+        gk = list(uniq[order])
+        gs = list(slots_of_uniq[order])
+        if is_max.any():
+            gk.append(self._EMPTY)
+            gs.append(capacity + 1)
+        if (~valid).any():
+            gk.append(self._EMPTY)
+            gs.append(capacity)
+        g = len(gk)
+        _arr(gkeys, np.uint64, g)[:] = np.array(gk, dtype=np.uint64)
+        _arr(gslots, np.uint32, g)[:] = np.array(gs, dtype=np.uint32)
+        ngroups._obj.value = g
+        self._gid_of_slot = None
+        return 0
+
+    def xchg_group_ids(self, order, gslots, g, slot, n, capacity, ws, rgid, stream):
+        if g == 0 or n == 0:
+            return 0
+        o = _arr(order, np.uint32, g).astype(np.int64)
+        s = _arr(gslots, np.uint32, g).astype(np.int64)
+        gid_of_slot = np.full(capacity + 2, 0xFFFFFFFF, dtype=np.uint32)
+        gid_of_slot[s[o]] = np.arange(g, dtype=np.uint32)
+        _arr(rgid, np.uint32, n)[:] = gid_of_slot[_arr(slot, np.uint32, n)]
+        return 0
+
+    def xchg_agg_stats_init(self, stats, m2, g, stream):
+        if g == 0:
+            return 0
+        st = _arr(stats, np.uint64, 5 * g)
+        st[:] = 0
+        st[2 * g:3 * g] = self._EMPTY
+        if _addr(m2):
+            _arr(m2, np.float64, g)[:] = 0
+        return 0
+
+    @staticmethod
+    def _gids(rgid, n):
+        return _arr(rgid, np.uint32, n).astype(np.int64) if _addr(rgid) else np.zeros(n, np.int64)
+
+    def xchg_agg_count_rows(self, rgid, n, rows, stream):
+        if n == 0:
+            return 0
+        g = self._gids(rgid, n)
+        r = _arr(rows, np.uint64, int(g.max()) + 1)
+        r += np.bincount(g, minlength=len(r)).astype(np.uint64)
+        return 0
+
+    @staticmethod
+    def _enc(x, dt):
+        if dt.kind == "f":
+            b = x.astype(np.float64).view(np.uint64)
+            return np.where(b >> np.uint64(63), ~b, b | np.uint64(1 << 63))
+        if dt.kind == "i":
+            return x.astype(np.int64).view(np.uint64) ^ np.uint64(1 << 63)
+        return x.astype(np.uint64)
+
+    def xchg_agg_accumulate(self, rgid, values, vt, validity, vbit, n, g, stats, want_minmax, stream):
+        if n == 0:
+            return 0
+        dt = np.dtype(_KT[vt])
+        gid = self._gids(rgid, n)
+        x = _arr(values, dt, n)
+        valid = _bits(validity, vbit, np.arange(n, dtype=np.int64)) if _addr(validity) else np.ones(n, bool)
+        st = _arr(stats, np.uint64, 5 * g)
+        cnt, mn, mx, nan = st[0:g], st[2 * g:3 * g], st[3 * g:4 * g], st[4 * g:5 * g]
+        cnt += np.bincount(gid[valid], minlength=g).astype(np.uint64)
+        if dt.kind == "f":
+            s = st[g:2 * g].view(np.float64)
+            with np.errstate(invalid="ignore", over="ignore"):
+                np.add.at(s, gid[valid], x[valid].astype(np.float64))
+        else:
+            s = st[g:2 * g].view(np.int64)
+            np.add.at(s, gid[valid], x[valid].astype(np.int64) if dt != np.uint64 else x[valid].view(np.int64))
+        if want_minmax:
+            isnan = np.isnan(x) if dt.kind == "f" else np.zeros(n, bool)
+            nan += np.bincount(gid[valid & isnan], minlength=g).astype(np.uint64)
+            ok = valid & ~isnan
+            e = self._enc(x[ok], dt)
+            np.minimum.at(mn, gid[ok], e)
+            np.maximum.at(mx, gid[ok], e)
+        return 0
+
+    def xchg_agg_accumulate_m2(self, rgid, values, vt, validity, vbit, n, g, stats, m2, stream):
+        if n == 0:
+            return 0
+        dt = np.dtype(_KT[vt])
+        gid = self._gids(rgid, n)
+        x = _arr(values, dt, n).astype(np.float64)
+        valid = _bits(validity, vbit, np.arange(n, dtype=np.int64)) if _addr(validity) else np.ones(n, bool)
+        st = _arr(stats, np.uint64, 5 * g)
+        cnt = st[0:g].astype(np.float64)
+        s = st[g:2 * g].view(np.float64) if dt.kind == "f" else st[g:2 * g].view(np.int64).astype(np.float64)
+        with np.errstate(invalid="ignore", divide="ignore"):
+            mean = s / cnt
+            d = x[valid] - mean[gid[valid]]
+            np.add.at(_arr(m2, np.float64, g), gid[valid], d * d)
+        return 0
+
+    def xchg_agg_merge_rows(self, rgid, part_rows, n, rows, stream):
+        if n == 0:
+            return 0
+        g = self._gids(rgid, n)
+        r = _arr(rows, np.uint64, int(g.max()) + 1)
+        np.add.at(r, g, _arr(part_rows, np.int64, n).astype(np.uint64))
+        return 0
+
+    def xchg_agg_merge_states(self, rgid, pst, n, sum_is_int, g, stats, m2, stream):
+        if n == 0:
+            return 0
+        gid = self._gids(rgid, n)
+        p = _arr(pst, np.uint64, 6 * n).reshape(n, 6)
+        st = _arr(stats, np.uint64, 5 * g)
+        has = p[:, 0] > 0
+        np.add.at(st[0:g], gid[has], p[has, 0])
+        if sum_is_int:
+            np.add.at(st[g:2 * g].view(np.int64), gid[has], p[has, 1].view(np.int64))
+        else:
+            with np.errstate(invalid="ignore", over="ignore"):
+                np.add.at(st[g:2 * g].view(np.float64), gid[has], p[has, 1].view(np.float64))
+        np.minimum.at(st[2 * g:3 * g], gid[has], p[has, 2])
+        np.maximum.at(st[3 * g:4 * g], gid[has], p[has, 3])
+        np.add.at(st[4 * g:5 * g], gid[has], p[has, 4])
+        if _addr(m2):
+            cnt = st[0:g].astype(np.float64)
+            tot = st[g:2 * g].view(np.int64).astype(np.float64) if sum_is_int else st[g:2 * g].view(np.float64)
+            si = p[:, 1].view(np.int64).astype(np.float64) if sum_is_int else p[:, 1].view(np.float64)
+            with np.errstate(invalid="ignore", divide="ignore"):
+                d = si[has] / p[has, 0].astype(np.float64) - (tot / cnt)[gid[has]]
+                np.add.at(_arr(m2, np.float64, g), gid[has],
+                          p[has, 5].view(np.float64) + p[has, 0].astype(np.float64) * d * d)
+        return 0
+
+    def xchg_agg_pack_states(self, g, stats, m2, out, stream):
+        if g == 0:
+            return 0
+        st = _arr(stats, np.uint64, 5 * g).reshape(5, g)
+        o = _arr(out, np.uint64, 6 * g).reshape(g, 6)
+        o[:, :5] = st.T
+        o[:, 5] = _arr(m2, np.float64, g).view(np.uint64) if _addr(m2) else 0
+        return 0
+
+    def xchg_agg_finalize(self, kind, ddof, ignore_nulls, vt, g, rows, stats, m2, out, valid_out, stream):
+        if g == 0:
+            return 0
+        r = _arr(rows, np.uint64, g)
+        o = _arr(out, np.uint64, g)
+        v = _arr(valid_out, np.uint8, g)
+        if kind == 0:
+            o[:] = r
+            v[:] = 1
+            return 0
+        dt = np.dtype(_KT[vt])
+        is_int = dt.kind in "iu"
+        st = _arr(stats, np.uint64, 5 * g).reshape(5, g)
+        cnt = st[0]
+        ok = (cnt > 0) & (bool(ignore_nulls) | (cnt == r))
+        v[:] = ok.astype(np.uint8)
+        s = st[1].view(np.int64).astype(np.float64) if is_int else st[1].view(np.float64)
+        res = np.zeros(g, dtype=np.uint64)
+        with np.errstate(invalid="ignore", divide="ignore"):
+            if kind == 1:
+                res = st[1].copy()
+            elif kind in (2, 3):
+                e = st[2] if kind == 2 else st[3]
+                if is_int:
+                    res = e ^ np.uint64(1 << 63) if dt.kind == "i" else e.copy()
+                else:
+                    b = np.where(e >> np.uint64(63), e & np.uint64((1 << 63) - 1), ~e)
+                    f = b.view(np.float64).copy()
+                    f[st[4] >= cnt] = np.nan
+                    res = f.view(np.uint64)
+            elif kind == 4:
+                res = (s / cnt.astype(np.float64)).view(np.uint64)
+            else:
+                m = _arr(m2, np.float64, g)
+                c = cnt.astype(np.float64)
+                val = np.where(c >= 2, np.sqrt(m / (c - ddof)), 0.0)
+                res = val.view(np.uint64)
+        o[:] = np.where(ok, res, np.uint64(0))
+        return 0
+
+    def xchg_group_keys_out(self, norm, kt, g, out, stream):
+        if g == 0:
+            return 0
+        k = _arr(norm, np.uint64, g)
+        dt = np.dtype(_KT[kt])
+        o = _arr(out, np.uint64, g)
+        bits = dt.itemsize * 8
+        if dt.kind == "i":
+            u = k & np.uint64((1 << bits) - 1) if bits < 64 else k
+            x = (u ^ np.uint64(1 << (bits - 1))).astype(np.uint64)
+            if bits < 64:
+                x = x.astype(np.int64)
+                x = np.where(x >= (1 << (bits - 1)), x - (1 << bits), x)
+                o[:] = x.astype(np.int64).view(np.uint64)
+            else:
+                o[:] = x
+        elif dt.kind == "u":
+            o[:] = k
+        else:
+            nan_key = np.uint64((1 << bits) - 2) if bits < 64 else np.uint64(0xFFFFFFFFFFFFFFFE)
+            if bits == 32:
+                t = (k & np.uint64(0xFFFFFFFF)).astype(np.uint32)
+                b = np.where(t & np.uint32(0x80000000), t & np.uint32(0x7FFFFFFF), ~t)
+                f = b.view(np.float32).astype(np.float64)
+            else:
+                b = np.where(k >> np.uint64(63), k & np.uint64((1 << 63) - 1), ~k)
+                f = b.view(np.float64).copy()
+            f = np.where(k == nan_key, np.nan, f)
+            o[:] = f.view(np.uint64)
+        return 0
