@@ -380,6 +380,10 @@ def run_b200(args):
         del out
     barrier()
     ex.phase_ms = {}
+    if args.trace:
+        from cluster_anywhere_b200.exchange import collective as coll
+
+        coll.TRACE = ex.phase_ms
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()

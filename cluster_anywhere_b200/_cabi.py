@@ -51,6 +51,7 @@ _SIGNATURES = {
     "xchg_agg_pack_states": (c_int, [c_uint64, _P, _P, _P, _P]),
     "xchg_agg_finalize": (c_int, [c_int, c_int, c_int, c_int, c_uint64, _P, _P, _P, _P, _P, _P]),
     "xchg_group_keys_out": (c_int, [_P, c_int, c_uint64, _P, _P]),
+    "xchg_gather_bitmap_bytes": (c_int, [_P, c_int64, _P, c_uint64, _P, _P]),
     "xchg_bitmap_unpack": (c_int, [_P, c_int64, c_uint64, _P, _P]),
     "xchg_bitmap_pack": (c_int, [_P, c_uint64, _P, _P, _P]),
     "xchg_offsets_rebase": (c_int, [_P, c_uint64, c_int64, _P, _P]),

@@ -150,7 +150,7 @@ k_lookup_gid(const uint32_t* __restrict__ slot, const uint32_t* __restrict__ gid
              uint32_t* __restrict__ rgid) {
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
-    rgid[i] = gid_of_slot[slot[i]];
+    rgid[i] = ld_random(gid_of_slot + slot[i]);
 }
 
 // ---- order-preserving encodings for min / max -------------------------------------

@@ -55,6 +55,39 @@ __device__ __forceinline__ void st_stream_u4(uint4* p, const uint4& v) {
                : "memory");
 }
 
+// Random-access loads: ask the L2 for a 64-byte fill instead of the default whole
+// 128-byte line (measured on B200: a random 32-byte read costs 127 B of HBM traffic by
+// default, 64 B with .L2::64B -- profiles/r01_fetch_granularity.md).
+template <typename T>
+__device__ __forceinline__ T ld_random(const T* p) {
+  static_assert(sizeof(T) == 1 || sizeof(T) == 2 || sizeof(T) == 4 || sizeof(T) == 8 || sizeof(T) == 16,
+                "unsupported width");
+  if constexpr (sizeof(T) == 1) {
+    uint32_t v;
+    asm volatile("ld.global.L2::64B.u8 %0, [%1];" : "=r"(v) : "l"(p));
+    uint8_t b = (uint8_t)v;
+    return *reinterpret_cast<T*>(&b);
+  } else if constexpr (sizeof(T) == 2) {
+    uint16_t v;
+    asm volatile("ld.global.L2::64B.u16 %0, [%1];" : "=h"(v) : "l"(p));
+    return *reinterpret_cast<T*>(&v);
+  } else if constexpr (sizeof(T) == 4) {
+    uint32_t v;
+    asm volatile("ld.global.L2::64B.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return *reinterpret_cast<T*>(&v);
+  } else if constexpr (sizeof(T) == 8) {
+    uint64_t v;
+    asm volatile("ld.global.L2::64B.u64 %0, [%1];" : "=l"(v) : "l"(p));
+    return *reinterpret_cast<T*>(&v);
+  } else {
+    uint4 v;
+    asm volatile("ld.global.L2::64B.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(p));
+    return *reinterpret_cast<T*>(&v);
+  }
+}
+
 // ---- measurement hooks (api.cu) ----------------------------------------------
 // Every kernel launch is counted; when profiling is enabled a launch is bracketed
 // by CUDA events on its own stream so bench.py can report per-kernel device time.

@@ -26,7 +26,7 @@ k_gather_fixed(const T* __restrict__ in, const uint32_t* __restrict__ idx, uint6
                T* __restrict__ out) {
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
-    out[i] = in[idx[i]];
+    out[i] = ld_random(in + idx[i]);
 }
 
 __global__ void __launch_bounds__(256)
@@ -189,7 +189,7 @@ constexpr int GR_STAGE = 56 * 1024;          // staging bytes per CTA
 constexpr size_t GR_SMEM = GR_STAGE + 32 + (size_t)GR_MAX_ROWS * (8 + 8 + 4 + 4) + 64;
 
 __device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* g) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(g) : "memory");
+  asm volatile("cp.async.cg.shared.global.L2::64B [%0], [%1], 16;" ::"r"(smem_addr), "l"(g) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() {
   asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
@@ -659,6 +659,25 @@ __global__ void k_offsets_rebase(const int64_t* __restrict__ in, uint64_t count,
 }
 
 }  // namespace
+
+namespace {
+__global__ void __launch_bounds__(256)
+k_gather_bitmap_bytes(const uint8_t* __restrict__ in, int64_t in_bit, const uint32_t* __restrict__ idx,
+                      uint64_t n, uint8_t* __restrict__ out) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    out[i] = bit_is_set(in, (int64_t)idx[i] + in_bit) ? 1 : 0;
+}
+}  // namespace
+
+extern "C" int xchg_gather_bitmap_bytes(const uint8_t* in, int64_t in_bit_offset, const uint32_t* idx,
+                                        uint64_t n_out, uint8_t* out_bytes, void* stream) {
+  if (n_out == 0) return XCHG_OK;
+  XCHG_REQUIRE(in && idx && out_bytes, "NULL in / idx / out");
+  XCHG_LAUNCH(XK_GATHER_BITMAP, (cudaStream_t)stream, k_gather_bitmap_bytes<<<grid_for(n_out, 256, 8), 256, 0, (cudaStream_t)stream>>>(in, in_bit_offset, idx, n_out, out_bytes));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
 
 extern "C" int xchg_bitmap_unpack(const uint8_t* in, int64_t in_bit_offset, uint64_t n, uint8_t* out,
                                   void* stream) {

@@ -30,8 +30,13 @@ constexpr int GU_MAX_ROWS = 1024;
 // stage | pad | int64 src[GU_MAX_ROWS] | uint32 a0[GU_MAX_ROWS]
 constexpr size_t GU_SMEM = GU_STAGE + 32 + (size_t)GU_MAX_ROWS * (8 + 4);
 
+// .L2::64B: a miss fetches the 64 bytes around the access from HBM instead of the whole
+// 128-byte line (measured on B200, profiles/r01_fetch_granularity.md: 127 B of DRAM
+// reads per random 32-byte access by default, 64 B with this qualifier;
+// cudaLimitMaxL2FetchGranularity has no effect).  A 90-byte row then costs ~153 B of
+// reads instead of ~219 B.
 __device__ __forceinline__ void cp_async16_cg(uint32_t smem_addr, const void* g) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(g) : "memory");
+  asm volatile("cp.async.cg.shared.global.L2::64B [%0], [%1], 16;" ::"r"(smem_addr), "l"(g) : "memory");
 }
 __device__ __forceinline__ void cp_async_drain() {
   asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
@@ -88,6 +93,57 @@ k_gather_rows_uniform(const uint8_t* __restrict__ in, uint32_t w, const uint32_t
       const uint4* s4 = reinterpret_cast<const uint4*>(stage);
       uint4* o4 = reinterpret_cast<uint4*>(o);
       for (uint32_t q = tid; q < (nbytes >> 4); q += GU_THREADS) o4[q] = s4[q];
+    } else if (w >= 16) {
+      // 16 output bytes per thread.  Unit at tile byte t lies in row j = t / w from its
+      // byte r; if the row ends inside the unit (k = w - r < 16) the rest comes from the
+      // start of row j+1.  Both 16-byte windows are read unaligned from the stage (five
+      // aligned words + four funnel shifts each; the slots' slack keeps the over-reads in
+      // bounds) and merged bytewise with masks: no divergence, one 16-byte store.
+      const uint32_t head = min(nbytes, (uint32_t)((16 - ((uintptr_t)o & 15)) & 15));
+      const uint32_t nunits = (nbytes - head) >> 4;
+      const uint32_t tail0 = head + (nunits << 4);
+      uint4* ov = reinterpret_cast<uint4*>(o + head);
+      const uint32_t* sw = reinterpret_cast<const uint32_t*>(stage);
+      for (uint32_t q = tid; q < nunits; q += GU_THREADS) {
+        const uint32_t t = head + (q << 4);
+        const uint32_t j = udiv_magic(t, magic_w);
+        const uint32_t r = t - j * w;
+        const uint32_t k = w - r;  // bytes of row j available from r (>= 1)
+        const uint32_t a = m_a0[j] + r;
+        const uint32_t* pa = sw + (a >> 2);
+        const uint32_t sa = (a & 3) * 8;
+        const uint32_t a0w = pa[0], a1w = pa[1], a2w = pa[2], a3w = pa[3], a4w = pa[4];
+        uint4 v;
+        v.x = __funnelshift_r(a0w, a1w, sa);
+        v.y = __funnelshift_r(a1w, a2w, sa);
+        v.z = __funnelshift_r(a2w, a3w, sa);
+        v.w = __funnelshift_r(a3w, a4w, sa);
+        if (k < 16) {
+          // window that has row j+1's first bytes at unit offsets k..15
+          const uint32_t b = m_a0[j + 1] - k;
+          const uint32_t* pb = sw + (b >> 2);
+          const uint32_t sb = (b & 3) * 8;
+          const uint32_t b0w = pb[0], b1w = pb[1], b2w = pb[2], b3w = pb[3], b4w = pb[4];
+          uint32_t u[4] = {__funnelshift_r(b0w, b1w, sb), __funnelshift_r(b1w, b2w, sb),
+                           __funnelshift_r(b2w, b3w, sb), __funnelshift_r(b3w, b4w, sb)};
+          uint32_t x[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            // bytes of word i that still belong to row j: clamp(k - 4i, 0, 4)
+            const int keep = min(4, max(0, (int)k - 4 * i));
+            const uint32_t mask = keep >= 4 ? 0xFFFFFFFFu : ((1u << (8 * keep)) - 1u);
+            x[i] = (x[i] & mask) | (u[i] & ~mask);
+          }
+          v = make_uint4(x[0], x[1], x[2], x[3]);
+        }
+        ov[q] = v;
+      }
+      // head and tail bytes of the tile (at most 15 each)
+      if ((uint32_t)tid < head + (nbytes - tail0)) {
+        const uint32_t t = (uint32_t)tid < head ? (uint32_t)tid : tail0 + ((uint32_t)tid - head);
+        const uint32_t j = udiv_magic(t, magic_w);
+        o[t] = stage[m_a0[j] + (t - j * w)];
+      }
     } else {
       const uint32_t head = min(nbytes, (uint32_t)((4 - ((uintptr_t)o & 3)) & 3));
       const uint32_t nwords = (nbytes - head) >> 2;

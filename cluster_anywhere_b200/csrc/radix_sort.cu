@@ -13,6 +13,7 @@
 // the tile in shared memory in digit order and writes it out in coalesced runs.
 // Algorithmic bytes per pass: 24 B/row (12 read + 12 written).
 #include <algorithm>
+#include <cstdlib>
 #include <type_traits>
 
 #include "common.cuh"
@@ -22,11 +23,21 @@ namespace {
 constexpr int BINS = 256;
 constexpr int KEY_PLACES = 8;
 constexpr int NUM_PLACES = 9;  // 8 key digit places + the validity place
-constexpr int RS_THREADS = 512;
-constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_ITEMS = 16;
-constexpr int RS_TILE = RS_THREADS * RS_ITEMS;  // 8192 rows
-constexpr size_t RS_SMEM = (size_t)RS_TILE * 12 + (BINS + BINS + 32) * 4;
+// CTA shapes of the onesweep pass: 512 threads x 2 CTAs/SM (8192-row tiles) or 256
+// threads x 4 CTAs/SM (4096-row tiles).  Same registers and shared memory per SM; the
+// smaller CTA keeps every thread busy in the 256-wide scan / look-back phases and lets
+// four tiles per SM interleave their barrier-separated phases.
+constexpr int RS_MIN_TILE = 256 * 8;
+constexpr int RS_DEFAULT_THREADS = 256;
+constexpr int RS_DEFAULT_ITEMS = 16;
+constexpr int RS_BATCH = 4;  // items ranked together (independent match / atomic / shuffle chains)
+constexpr size_t rs_smem(int threads, int items) { return (size_t)threads * items * 12 + (BINS + BINS + 32) * 4; }
+// CTAs per SM by items per thread (register budget: 2 regs per key + rank + ~24)
+constexpr int rs_min_blocks(int threads, int items) {
+  return (items >= 16 ? 1024 : (items >= 12 ? 1280 : 1536)) / threads;
+}
+
+constexpr int LB_WINDOW = 8;  // predecessors fetched per look-back round trip
 
 constexpr uint32_t FLAG_MASK = 3u << 30;
 constexpr uint32_t FLAG_LOCAL = 1u << 30;
@@ -160,12 +171,14 @@ __device__ __forceinline__ uint32_t digit_of(uint64_t key, uint32_t val, int shi
   }
 }
 
-template <int MODE>
-__global__ void __launch_bounds__(RS_THREADS, 2)
+template <int MODE, int RS_THREADS, int RS_ITEMS>
+__global__ void __launch_bounds__(RS_THREADS, rs_min_blocks(RS_THREADS, RS_ITEMS))
 k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
            uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, uint32_t n,
            int shift, const uint32_t* __restrict__ gexcl, uint32_t* status,
            uint32_t* tile_counter, const uint8_t* __restrict__ validity, int64_t vbit) {
+  constexpr int RS_WARPS = RS_THREADS / 32;
+  constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
   extern __shared__ __align__(16) uint8_t smem[];
   uint64_t* skeys = reinterpret_cast<uint64_t*>(smem);
   uint32_t* svals = reinterpret_cast<uint32_t*>(smem + (size_t)RS_TILE * 8);
@@ -196,28 +209,30 @@ k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ va
   }
 
   // ---- rank inside the warp, in (i, lane) = memory order: stable ----
-  // Eight items at a time, three independent sweeps (match masks, leader atomics on
+  // RS_BATCH items at a time, three independent sweeps (match masks, leader atomics on
   // the warp's private counters, broadcasts) so that the ~30-cycle shared-memory
   // round trips of different items overlap instead of forming one serial chain per
   // item (the first version did: 52 % short-scoreboard stalls, profiles/r01_summary.md).
   // The atomics of successive items are issued in program order by one warp to its
   // own counter row, so equal digits receive increasing bases in item order.
   uint32_t* myhist = whist + warp * BINS;
-  uint32_t rank[RS_ITEMS];
+  uint32_t rank2[RS_ITEMS / 2];  // two 16-bit in-tile ranks per register (tile <= 8192 rows)
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS / 2; ++i) rank2[i] = 0;
   const unsigned lt_mask = lanemask_lt();
 #pragma unroll
-  for (int h = 0; h < RS_ITEMS; h += 8) {
-    uint32_t info[8];  // leader | lanes-before-me << 8 | group size << 16
+  for (int h = 0; h < RS_ITEMS; h += RS_BATCH) {
+    uint32_t info[RS_BATCH];  // leader | lanes-before-me << 8 | group size << 16
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
+    for (int u = 0; u < RS_BATCH; ++u) {
       const uint32_t d = digit_of<MODE>(key[h + u], val[h + u], shift, validity, vbit);
       const unsigned m = __match_any_sync(0xffffffffu, d);
       info[u] = (uint32_t)(__ffs(m) - 1) | ((uint32_t)__popc(m & lt_mask) << 8) |
                 ((uint32_t)__popc(m) << 16);
     }
-    uint32_t prev[8];
+    uint32_t prev[RS_BATCH];
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
+    for (int u = 0; u < RS_BATCH; ++u) {
       prev[u] = 0;
       if (lane == (int)(info[u] & 31u)) {
         const uint32_t d = digit_of<MODE>(key[h + u], val[h + u], shift, validity, vbit);
@@ -225,21 +240,25 @@ k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ va
       }
     }
 #pragma unroll
-    for (int u = 0; u < 8; ++u)
-      rank[h + u] = __shfl_sync(0xffffffffu, prev[u], (int)(info[u] & 31u)) + ((info[u] >> 8) & 63u);
+    for (int u = 0; u < RS_BATCH; ++u)
+      rank2[(h + u) >> 1] |= (__shfl_sync(0xffffffffu, prev[u], (int)(info[u] & 31u)) + ((info[u] >> 8) & 63u))
+                             << (16 * ((h + u) & 1));
   }
   __syncthreads();
 
   // ---- per digit: exclusive offsets across warps, tile totals, digit scan ----
   uint32_t total = 0, incl = 0;
   if (tid < BINS) {
-    uint32_t c[RS_WARPS];
 #pragma unroll
-    for (int w = 0; w < RS_WARPS; ++w) c[w] = whist[w * BINS + tid];
+    for (int w0 = 0; w0 < RS_WARPS; w0 += 4) {  // four loads in flight, few live registers
+      uint32_t c[4];
 #pragma unroll
-    for (int w = 0; w < RS_WARPS; ++w) {
-      whist[w * BINS + tid] = total;
-      total += c[w];
+      for (int w = 0; w < 4; ++w) c[w] = whist[(w0 + w) * BINS + tid];
+#pragma unroll
+      for (int w = 0; w < 4; ++w) {
+        whist[(w0 + w) * BINS + tid] = total;
+        total += c[w];
+      }
     }
     incl = total;
 #pragma unroll
@@ -264,16 +283,30 @@ k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ va
       *st = FLAG_INCL | cnt;
     } else {
       *st = FLAG_LOCAL | cnt;
+      // Windowed walk: the LB_WINDOW predecessors' words are fetched with independent
+      // loads (one L2 round trip for the window, not one per tile), then consumed in
+      // order up to the first word that is an inclusive prefix or not published yet.
+      // With ~300 tiles in flight a tile usually has to cross many LOCAL-only
+      // predecessors; the one-word-per-round-trip walk of the first version made that
+      // the longest phase of a tile.
       int64_t t = (int64_t)tile - 1;
-      while (true) {
-        volatile uint32_t* ps = status + (size_t)t * BINS + tid;
-        uint32_t s;
-        do {
-          s = *ps;
-        } while ((s & FLAG_MASK) == 0);
-        excl += s & VAL_MASK;
-        if (s & FLAG_INCL) break;
-        --t;
+      bool done = false;
+      while (!done) {
+        uint32_t w[LB_WINDOW];
+#pragma unroll
+        for (int j = 0; j < LB_WINDOW; ++j) {
+          const int64_t tj = t - j;
+          w[j] = tj >= 0 ? *(volatile uint32_t*)(status + (size_t)tj * BINS + tid) : (2u << 30);  // before tile 0: an inclusive prefix of zero
+        }
+#pragma unroll
+        for (int j = 0; j < LB_WINDOW; ++j) {
+          if (done) break;
+          const uint32_t sj = w[j];
+          if ((sj & FLAG_MASK) == 0) break;  // not published yet: re-read from here
+          excl += sj & VAL_MASK;
+          --t;
+          if (sj & FLAG_INCL) done = true;
+        }
       }
       *st = FLAG_INCL | (excl + cnt);
     }
@@ -285,13 +318,13 @@ k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ va
 #pragma unroll
   for (int i = 0; i < RS_ITEMS; ++i) {
     const uint32_t d = digit_of<MODE>(key[i], val[i], shift, validity, vbit);
-    rank[i] += myhist[d] + sstart[d];
+    rank2[i >> 1] += (myhist[d] + sstart[d]) << (16 * (i & 1));  // no carry: every rank < 65536
   }
   __syncthreads();  // whist is dead from here: skeys may overwrite it
 
   // ---- stage the tile in digit order ----
 #pragma unroll
-  for (int i = 0; i < RS_ITEMS; ++i) skeys[rank[i]] = key[i];
+  for (int i = 0; i < RS_ITEMS; ++i) skeys[(rank2[i >> 1] >> (16 * (i & 1))) & 0xFFFFu] = key[i];
 #pragma unroll
   for (int i = 0; i < RS_ITEMS; ++i) {
     uint32_t v;
@@ -301,7 +334,7 @@ k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ va
       const uint32_t idx = warp_base + 32 * i;
       v = idx < n ? (vals_in ? vals_in[idx] : idx) : 0xFFFFFFFFu;
     }
-    svals[rank[i]] = v;
+    svals[(rank2[i >> 1] >> (16 * (i & 1))) & 0xFFFFu] = v;
   }
   __syncthreads();
 
@@ -361,7 +394,7 @@ SortWorkspace carve(void* base, uint64_t n) {
     off = xchg_align_up(off + bytes, 256);
     return (uint8_t*)base + o;
   };
-  const uint64_t ntiles = (n + RS_TILE - 1) / RS_TILE;
+  const uint64_t ntiles = (n + RS_MIN_TILE - 1) / RS_MIN_TILE;
   w.norm = (uint64_t*)take(n * 8);
   w.keys_b = (uint64_t*)take(n * 8);
   w.keys_a = (uint64_t*)take(n * 8);
@@ -411,25 +444,39 @@ int xchg_internal_onesweep_pass(int mode, const uint64_t* kin, const uint32_t* v
                                 uint32_t* vout, uint32_t n, int shift, const uint32_t* gexcl,
                                 uint32_t* status, uint32_t* tile_counter, const uint8_t* validity,
                                 int64_t vbit, cudaStream_t s) {
-  static bool attr_done[2] = {false, false};
-  const uint32_t ntiles = (n + RS_TILE - 1) / RS_TILE;
-  if (mode == 0) {
-    if (!attr_done[0]) {
-      XCHG_CUDA_TRY(cudaFuncSetAttribute(k_onesweep<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)RS_SMEM));
-      attr_done[0] = true;
-    }
-    XCHG_LAUNCH(XK_ONESWEEP, s, k_onesweep<0><<<ntiles, RS_THREADS, RS_SMEM, s>>>(kin, vin, kout, vout, n, shift, gexcl, status,
-                                                      tile_counter, validity, vbit));
-  } else {
-    if (!attr_done[1]) {
-      XCHG_CUDA_TRY(cudaFuncSetAttribute(k_onesweep<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)RS_SMEM));
-      attr_done[1] = true;
-    }
-    XCHG_LAUNCH(XK_ONESWEEP, s, k_onesweep<1><<<ntiles, RS_THREADS, RS_SMEM, s>>>(kin, vin, kout, vout, n, shift, gexcl, status,
-                                                      tile_counter, validity, vbit));
+  // CTA shape: XCHG_ONESWEEP_THREADS=256|512 and XCHG_ONESWEEP_ITEMS=8|12|16 override the
+  // defaults (read once; tuning knobs for profiling runs)
+  static int threads = 0, items = 0;
+  if (threads == 0) {
+    const char* e = getenv("XCHG_ONESWEEP_THREADS");
+    threads = (e && atoi(e) == 512) ? 512 : ((e && atoi(e) == 256) ? 256 : RS_DEFAULT_THREADS);
+    const char* f = getenv("XCHG_ONESWEEP_ITEMS");
+    const int fi = f ? atoi(f) : 0;
+    items = (fi == 8 || fi == 12 || fi == 16) ? fi : RS_DEFAULT_ITEMS;
+    if (threads == 512) items = 16;
   }
+  static bool attr_done[2][4] = {{false, false, false, false}, {false, false, false, false}};
+#define XCHG_ONESWEEP_CASE(MODE, THREADS, ITEMS, SLOT)                                                  \
+  {                                                                                                    \
+    if (!attr_done[MODE][SLOT]) {                                                                      \
+      XCHG_CUDA_TRY(cudaFuncSetAttribute(k_onesweep<MODE, THREADS, ITEMS>,                             \
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize,                  \
+                                         (int)rs_smem(THREADS, ITEMS)));                               \
+      attr_done[MODE][SLOT] = true;                                                                    \
+    }                                                                                                  \
+    const uint32_t ntiles = (n + THREADS * ITEMS - 1) / (THREADS * ITEMS);                             \
+    XCHG_LAUNCH(XK_ONESWEEP, s,                                                                        \
+                k_onesweep<MODE, THREADS, ITEMS><<<ntiles, THREADS, rs_smem(THREADS, ITEMS), s>>>(      \
+                    kin, vin, kout, vout, n, shift, gexcl, status, tile_counter, validity, vbit));     \
+  }
+#define XCHG_ONESWEEP_MODE(MODE)                                          \
+  if (threads == 512) XCHG_ONESWEEP_CASE(MODE, 512, 16, 0)                \
+  else if (items == 16) XCHG_ONESWEEP_CASE(MODE, 256, 16, 1)              \
+  else if (items == 12) XCHG_ONESWEEP_CASE(MODE, 256, 12, 2)              \
+  else XCHG_ONESWEEP_CASE(MODE, 256, 8, 3)
+  if (mode == 0) { XCHG_ONESWEEP_MODE(0) } else { XCHG_ONESWEEP_MODE(1) }
+#undef XCHG_ONESWEEP_MODE
+#undef XCHG_ONESWEEP_CASE
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
 }
@@ -478,7 +525,7 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
     return XCHG_ERR_WORKSPACE;
   }
   const uint32_t n32 = (uint32_t)n;
-  const uint32_t ntiles = (n32 + RS_TILE - 1) / RS_TILE;
+  const uint32_t ntiles = (n32 + RS_MIN_TILE - 1) / RS_MIN_TILE;  // status rows cleared per pass
 
   XCHG_CUDA_TRY(cudaMemsetAsync(w.ghist, 0, NUM_PLACES * BINS * 4, s));
   int rc = dispatch_normalize(keys, key_type, perm_in, validity, validity_bit_offset, n32, descending,

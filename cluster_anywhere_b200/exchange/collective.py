@@ -26,6 +26,24 @@ from .. import device as dev
 from ..device import DeviceColumn, DeviceTable, _vp
 
 
+# diagnostics: set to a dict to accumulate synchronised wall-clock ms per sub-phase of
+# exchange_table (serialises the pipeline; bench.py --trace)
+TRACE = None
+_t_last = [None]
+
+
+def _trace(rt, name):
+    if TRACE is None:
+        return
+    import time
+
+    rt.synchronize()
+    now = time.perf_counter()
+    if name is not None and _t_last[0] is not None:
+        TRACE[name] = TRACE.get(name, 0.0) + (now - _t_last[0]) * 1e3
+    _t_last[0] = now
+
+
 def world(group=None):
     if dist.is_available() and dist.is_initialized():
         return dist.get_rank(group), dist.get_world_size(group)
@@ -71,6 +89,7 @@ def exchange_table(rt: dev.Runtime, table: DeviceTable, send_counts: Sequence[in
     assert sum(send_counts) == n_send
     cum = np.concatenate([[0], np.cumsum(np.asarray(send_counts, dtype=np.int64))])
     ncols = len(table.columns)
+    _trace(rt, None)
 
     # ---- metadata all-to-all: rows, per-column bytes, validity / uniform flags ----
     # row d of `meta` goes to rank d: [rows, (bytes, has_validity, uniform) per column]
@@ -96,11 +115,13 @@ def exchange_table(rt: dev.Runtime, table: DeviceTable, send_counts: Sequence[in
     recv_counts = got[:, 0].astype(np.int64)
     n_recv = int(recv_counts.sum())
     rcum = np.concatenate([[0], np.cumsum(recv_counts)])
+    _trace(rt, "a2a.meta")
 
     # a column is exchanged as uniform-width only if every rank sees the same width
     flags = all_gather_object(
         [(int(c.uniform) if (c.kind == "var" and c.uniform is not None) else -1,
           c.validity is not None) for c in table.columns], group)
+    _trace(rt, "a2a.flags_gather_object")
 
     out_cols: List[DeviceColumn] = []
     for j, c in enumerate(table.columns):
@@ -162,4 +183,5 @@ def exchange_table(rt: dev.Runtime, table: DeviceTable, send_counts: Sequence[in
             rt.call("xchg_offsets_uniform64", 1, 0, base, _vp(out_off[n_recv:]), rt.stream)
             out_cols.append(DeviceColumn(c.type, n_recv, "var", c.width, data, out_off, validity,
                                          null_count))
+        _trace(rt, f"a2a.col{j}.{c.kind}")
     return DeviceTable(list(table.names), out_cols, n_recv, table.schema)

@@ -58,6 +58,32 @@ class DeviceExchange:
         self.phase_ms = {}
         self._t_last = None
 
+    def _take_and_exchange(self, table, perm, send_counts, group):
+        """K5 + exchange.  On a GPU the gather kernels store straight into the
+        destination ranks' receive arenas over NVLink (exchange/peer.py); otherwise (host
+        double under gloo, XCHG_P2P=0, or no symmetric memory on this platform) the rows
+        are gathered locally and cross in one all-to-all-v per buffer."""
+        from . import collective as coll
+        from . import peer
+
+        rt = self.rt
+        if peer.enabled(rt) and not getattr(self, "_p2p_unavailable", False):
+            try:
+                recv = peer.gather_exchange(rt, self, table, perm, send_counts, group)
+                self._phase("dist.gather_exchange_p2p")
+                return recv
+            except (ImportError, AttributeError, NotImplementedError) as e:  # no symmetric memory here
+                import warnings
+
+                warnings.warn(f"NVLink peer-memory exchange unavailable ({e!r}); using NCCL all-to-all")
+                self._p2p_unavailable = True
+        n = table.num_rows
+        send_table = dev.take_table(rt, table, perm, n) if n > 0 else table
+        self._phase("dist.gather_send")
+        recv = coll.exchange_table(rt, send_table, send_counts, group)
+        self._phase("dist.all_to_all")
+        return recv
+
     def _phase(self, name: Optional[str]):
         if not self.trace:
             return
@@ -248,17 +274,14 @@ class DeviceExchange:
         # ---- map: destination of every row, stable order by destination ----
         n = table.num_rows
         send_counts = [0] * G
-        send_table = table
+        perm = None
         if n > 0:
             dest, counts = dev.assign_partitions(rt, table, splitters, sort_key)
             perm = dev.sort_u32(rt, dest, n)
             for d, cnt in enumerate(counts.tolist()):
                 send_counts[owners[d]] = int(cnt)
             self._phase("dist.assign_and_order")
-            send_table = dev.take_table(rt, table, perm, n)
-            self._phase("dist.gather_send")
-        recv = coll.exchange_table(rt, send_table, send_counts, group)
-        self._phase("dist.all_to_all")
+        recv = self._take_and_exchange(table, perm, send_counts, group)
 
         # ---- reduce: stable sort of the received runs, cut into this rank's blocks ----
         if my_blocks == 0:
@@ -333,7 +356,7 @@ class DeviceExchange:
         first = int(sum(i[1] for i in info[:rank]))
         send_counts = [0] * G
         pos_col = dev.DeviceColumn(pa.uint32(), n, "fixed", 4, rt.empty(0))
-        send_table = table
+        perm = None
         if n > 0:
             pos = dev.shuffle_positions(rt, seed64, n_total, first, n, inverse=False)
             dest = rt.empty(n, torch.int32)
@@ -344,20 +367,18 @@ class DeviceExchange:
             per_block = counts.tolist()
             for g in range(G):
                 send_counts[g] = int(sum(per_block[int(ob[g]):int(ob[g + 1])]))
-            send_table = dev.take_table(rt, table, perm, n)
-            pos_sorted = rt.empty(n, torch.int32)
-            rt.call("xchg_gather_fixed", dev._vp(pos), 4, dev._vp(perm), n, dev._vp(pos_sorted), rt.stream)
-            pos_col = dev.DeviceColumn(pa.uint32(), n, "fixed", 4, pos_sorted.view(torch.uint8))
-        wire = dev.DeviceTable(list(send_table.names) + ["__xchg_pos"], list(send_table.columns) + [pos_col],
-                               n, send_table.schema.append(pa.field("__xchg_pos", pa.uint32())))
-        recv = coll.exchange_table(rt, wire, send_counts, group)
+            pos_col = dev.DeviceColumn(pa.uint32(), n, "fixed", 4, pos.view(torch.uint8))
+        # the output position travels with its row as one more fixed-width column
+        wire = dev.DeviceTable(list(table.names) + ["__xchg_pos"], list(table.columns) + [pos_col],
+                               n, table.schema.append(pa.field("__xchg_pos", pa.uint32())))
+        recv = self._take_and_exchange(wire, perm, send_counts, group)
         m = recv.num_rows
         if my_blocks == 0 or m == 0:
             assert m == 0
             return DeviceDataset(None, [(0, 0)] * my_blocks)
         inv = rt.empty(m, torch.int32)
         rt.call("xchg_invert_permutation", dev._vp(recv.columns[-1].data), m, base, dev._vp(inv), rt.stream)
-        body = dev.DeviceTable(list(send_table.names), recv.columns[:-1], m, send_table.schema)
+        body = dev.DeviceTable(list(table.names), recv.columns[:-1], m, table.schema)
         return DeviceDataset(dev.take_table(rt, body, inv, m), my_ranges)
 
     def random_shuffle_blocks(self, blocks: Sequence[pa.Table], seed: Optional[int],

@@ -1,0 +1,228 @@
+"""Fused take + exchange over NVLink peer memory.
+
+The NCCL path (``collective.exchange_table``) first gathers every column into a
+send buffer ordered by destination (K5: read rows at random, write them densely),
+then ``ncclSend/ncclRecv`` read that buffer again and write the peer's receive
+buffer.  Here the gather kernels write their dense output stream DIRECTLY into the
+destination rank's receive buffer: every rank maps one symmetric arena of all its
+peers (CUDA VMM handles exchanged once through ``torch.distributed._symmetric_memory``;
+plumbing), and K5 is launched once per (column, destination) with the peer's pointer
+as its output.  The send buffer, its write and its re-read disappear, and the row
+gather runs at link speed with its random HBM reads overlapped tile by tile with the
+NVLink stores (a warp's stores are contiguous 128-byte lines, which is what NVLink
+moves efficiently).
+
+In the reference this step is M x R plasma objects pulled by the reducers
+(python/ray/data/_internal/planner/exchange/pull_based_shuffle_task_scheduler.py:
+84-120).
+
+Synchronisation: all arithmetic on where things go is derived from ONE all-gathered
+count matrix, identically on every rank; a stream-ordered collective before the
+stores orders them after every peer's previous use of its arena, and a second one
+after them makes the received rows visible.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import List, Optional, Sequence
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from .. import device as dev
+from ..device import DeviceColumn, DeviceTable, _vp
+from . import collective as coll
+
+_ALIGN = 256
+
+
+def _up(x: int) -> int:
+    return (int(x) + _ALIGN - 1) // _ALIGN * _ALIGN
+
+
+def enabled(rt: dev.Runtime) -> bool:
+    return rt.is_cuda and os.environ.get("XCHG_P2P", "1") != "0"
+
+
+class PeerArena:
+    """One symmetric byte buffer per rank, mapped by every rank."""
+
+    def __init__(self, rt: dev.Runtime, nbytes: int, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self.nbytes = int(nbytes)
+        self.buf = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=rt.device)
+        self.hdl = symm_mem.rendezvous(self.buf, group=group if group is not None else dist.group.WORLD)
+        self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+
+
+def _ptr(base: int, off: int = 0):
+    return ctypes.c_void_p(int(base) + int(off))
+
+
+def gather_exchange(rt: dev.Runtime, holder, table: DeviceTable, perm: Optional[torch.Tensor],
+                    send_counts: Sequence[int], group=None) -> DeviceTable:
+    """``take(table, perm)`` ordered by destination rank, written straight into the
+    destinations' arenas.  ``perm`` (uint32 row ids, may be None when there are no rows)
+    lists this rank's rows by destination; ``send_counts[d]`` of them go to rank ``d``.
+    ``holder.arena`` caches the symmetric arena between calls.  Returns the received
+    rows in (source rank, position at the source) order; the table aliases the arena and
+    is valid until the next exchange."""
+    rank, G = coll.world(group)
+    n = table.num_rows
+    ncols = len(table.columns)
+    cuts = np.concatenate([[0], np.cumsum(np.asarray(send_counts, dtype=np.int64))])
+    assert int(cuts[-1]) == n
+
+    # ---- ragged columns: output offsets of the whole take (needed for byte counts) ----
+    out_offs = {}
+    for j, c in enumerate(table.columns):
+        if c.kind == "var" and c.uniform is None and n:
+            oo = rt.empty(n + 1, torch.int64)
+            ws_bytes = ctypes.c_uint64()
+            dev._cabi.check(dev._cabi.load().xchg_gather_offsets_workspace_bytes(n, ctypes.byref(ws_bytes)))
+            ws = rt.empty(ws_bytes.value)
+            rt.call("xchg_gather_offsets", _vp(c.offsets), _vp(perm), n, _vp(oo), _vp(ws), ws_bytes.value,
+                    rt.stream, launches=3)
+            out_offs[j] = oo
+
+    # ---- one all-gathered matrix: [rows | per column: bytes, has_validity, uniform] per dest ----
+    meta = np.zeros((G, 1 + 3 * ncols), dtype=np.int64)
+    meta[:, 0] = send_counts
+    cum_d = None
+    for j, c in enumerate(table.columns):
+        meta[:, 2 + 3 * j] = 1 if c.validity is not None else 0
+        meta[:, 3 + 3 * j] = -1
+        if c.kind == "var":
+            if c.uniform is not None:
+                meta[:, 1 + 3 * j] = np.asarray(send_counts, dtype=np.int64) * c.uniform
+                meta[:, 3 + 3 * j] = c.uniform
+            elif n:
+                if cum_d is None:
+                    cum_d = torch.from_numpy(cuts).to(rt.device)
+                ends = out_offs[j][cum_d].tolist()  # sync: G+1 scalars
+                meta[:, 1 + 3 * j] = np.diff(np.asarray(ends, dtype=np.int64))
+    mine = torch.from_numpy(meta.reshape(-1)).to(rt.device)
+    allm = torch.empty(G * mine.numel(), dtype=torch.int64, device=rt.device)
+    dist.all_gather_into_tensor(allm, mine, group=group)  # also orders the stores below after
+    M = allm.cpu().numpy().reshape(G, G, 1 + 3 * ncols)   # every peer's previous use of its arena
+    rows_sd = M[:, :, 0]                                   # [source, dest]
+    recv_rows = rows_sd.sum(axis=0)                        # per dest
+    prefix_rows = np.cumsum(rows_sd, axis=0) - rows_sd     # rows of earlier sources, [source, dest]
+
+    # ---- arena layout of every rank (identical arithmetic everywhere) ----
+    col_plan = []
+    offsets_of = [dict() for _ in range(G)]  # dest -> {(col, region): byte offset}
+    totals = [0] * G
+    for j, c in enumerate(table.columns):
+        any_valid = bool(M[:, 0, 2 + 3 * j].max() > 0)
+        uni = set(int(x) for x in M[:, 0, 3 + 3 * j])
+        uniform = uni.pop() if (c.kind == "var" and len(uni) == 1 and -1 not in uni) else None
+        col_plan.append((any_valid, uniform))
+        for d in range(G):
+            r = int(recv_rows[d])
+            if any_valid:
+                offsets_of[d][(j, "valid")] = totals[d]
+                totals[d] += _up(r)
+            if c.kind == "fixed":
+                nb = r * c.width
+            elif c.kind == "bits":
+                nb = r
+            elif uniform is not None:
+                nb = r * uniform
+            else:
+                nb = int(M[:, d, 1 + 3 * j].sum())
+                offsets_of[d][(j, "offsets")] = totals[d]
+                totals[d] += _up((r + 1) * 8)
+            offsets_of[d][(j, "data")] = totals[d]
+            totals[d] += _up(nb + 64)
+    need = max(totals) + _ALIGN
+    arena = getattr(holder, "arena", None)
+    if arena is None or arena.nbytes < need:
+        if arena is not None:
+            holder.arena = None
+            del arena
+        arena = PeerArena(rt, int(need * 1.25) + (1 << 20), group)
+        holder.arena = arena
+
+    # ---- stores into the peers: K5 once per (column, destination) ----
+    perm_ptr = perm.data_ptr() if perm is not None else 0
+    for j, c in enumerate(table.columns):
+        any_valid, uniform = col_plan[j]
+        for d in range(G):
+            k = int(send_counts[d])
+            if k == 0:
+                continue
+            lo = int(cuts[d])
+            idx = _ptr(perm_ptr, lo * 4)
+            pre = int(prefix_rows[rank, d])
+            base = arena.ptrs[d]
+            if any_valid:
+                dst = _ptr(base, offsets_of[d][(j, "valid")] + pre)
+                if c.validity is not None:
+                    rt.call("xchg_gather_bitmap_bytes", _vp(c.validity), 0, idx, k, dst, rt.stream)
+                else:
+                    arena.hdl.get_buffer(d, (k,), torch.uint8, offsets_of[d][(j, "valid")] + pre).fill_(1)
+            data_off = offsets_of[d][(j, "data")]
+            if c.kind == "fixed":
+                rt.call("xchg_gather_fixed", _vp(c.data), c.width, idx, k, _ptr(base, data_off + pre * c.width),
+                        rt.stream)
+            elif c.kind == "bits":
+                rt.call("xchg_gather_bitmap_bytes", _vp(c.data), 0, idx, k, _ptr(base, data_off + pre), rt.stream)
+            elif uniform is not None:
+                rt.call("xchg_gather_rows", _vp(c.data), uniform, idx, k, _ptr(base, data_off + pre * uniform),
+                        rt.stream)
+            else:
+                pre_bytes = int(M[:rank, d, 1 + 3 * j].sum())
+                if c.uniform is not None:  # uniform here, ragged elsewhere
+                    w = c.uniform
+                    rt.call("xchg_gather_rows", _vp(c.data), w, idx, k, _ptr(base, data_off + pre_bytes), rt.stream)
+                    rt.call("xchg_offsets_uniform64", k, w, pre_bytes,
+                            _ptr(base, offsets_of[d][(j, "offsets")] + pre * 8), rt.stream)
+                else:
+                    oo = out_offs[j]
+                    first = int(M[rank, :d, 1 + 3 * j].sum())  # = oo[lo]: bytes of earlier destinations
+                    # row i of the segment lands at  data + pre_bytes + (oo[lo+i] - oo[lo])
+                    rt.call("xchg_gather_bytes", _vp(c.data), _vp(c.offsets), idx, k, _ptr(oo.data_ptr(), lo * 8),
+                            _ptr(base, data_off + pre_bytes - first), rt.stream)
+                    rt.call("xchg_offsets_rebase", _ptr(oo.data_ptr(), lo * 8), k, pre_bytes,
+                            _ptr(base, offsets_of[d][(j, "offsets")] + pre * 8), rt.stream)
+
+    # ---- every rank's stores are complete and visible after this collective ----
+    flag = torch.zeros(1, dtype=torch.int32, device=rt.device)
+    dist.all_reduce(flag, group=group)
+
+    # ---- received table: views of the local arena ----
+    m = int(recv_rows[rank])
+    my = offsets_of[rank]
+    out_cols: List[DeviceColumn] = []
+    for j, c in enumerate(table.columns):
+        any_valid, uniform = col_plan[j]
+        validity, nulls = None, 0
+        if any_valid and m:
+            vb = arena.buf[my[(j, "valid")]: my[(j, "valid")] + m]
+            validity = rt.zeros(((m + 31) // 32) * 4)
+            cnt = rt.zeros(1, torch.int64)
+            rt.call("xchg_bitmap_pack", _vp(vb), m, _vp(validity), _vp(cnt), rt.stream)
+            nulls = cnt
+        o = my[(j, "data")]
+        if c.kind == "fixed":
+            out_cols.append(DeviceColumn(c.type, m, "fixed", c.width, arena.buf[o: o + m * c.width], None,
+                                         validity, nulls))
+        elif c.kind == "bits":
+            data = rt.zeros(((m + 31) // 32) * 4)
+            if m:
+                rt.call("xchg_bitmap_pack", _vp(arena.buf[o: o + m]), m, _vp(data), None, rt.stream)
+            out_cols.append(DeviceColumn(c.type, m, "bits", 0, data, None, validity, nulls))
+        elif uniform is not None:
+            out_cols.append(DeviceColumn(c.type, m, "var", c.width, arena.buf[o: o + m * uniform], None,
+                                         validity, nulls, uniform=uniform))
+        else:
+            total = int(M[:, rank, 1 + 3 * j].sum())
+            oo_off = my[(j, "offsets")]
+            offs = arena.buf[oo_off: oo_off + (m + 1) * 8].view(torch.int64)
+            rt.call("xchg_offsets_uniform64", 1, 0, total, _ptr(offs.data_ptr(), m * 8), rt.stream)
+            out_cols.append(DeviceColumn(c.type, m, "var", c.width, arena.buf[o: o + total], offs, validity, nulls))
+    return DeviceTable(list(table.names), out_cols, m, table.schema)

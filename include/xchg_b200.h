@@ -370,6 +370,10 @@ int xchg_group_keys_out(const uint64_t* sorted_norm_keys, int key_type, uint64_t
  */
 int xchg_bitmap_unpack(const uint8_t* in, int64_t in_bit_offset, uint64_t n, uint8_t* out_bytes,
                        void* stream);
+/* out_bytes[i] = bit (idx[i] + in_bit_offset) of `in`: take of a validity / boolean
+ * buffer straight into the one-byte-per-row wire form (out_bytes may be peer memory). */
+int xchg_gather_bitmap_bytes(const uint8_t* in, int64_t in_bit_offset, const uint32_t* idx,
+                             uint64_t n_out, uint8_t* out_bytes, void* stream);
 int xchg_bitmap_pack(const uint8_t* in_bytes, uint64_t n, uint8_t* out, uint64_t* zero_count_out,
                      void* stream);
 int xchg_offsets_rebase(const int64_t* in, uint64_t count, int64_t base, int64_t* out, void* stream);

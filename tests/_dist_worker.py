@@ -34,8 +34,15 @@ def make_block(rng, n):
 
 
 def main():
-    _cabi._install_test_double(FakeLib())
-    dist.init_process_group("gloo")
+    if "--gpu" in sys.argv:  # real kernels + NCCL + NVLink peer stores, one rank per GPU
+        import torch
+
+        lr = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(lr)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
+    else:
+        _cabi._install_test_double(FakeLib())
+        dist.init_process_group("gloo")
     r, w = dist.get_rank(), dist.get_world_size()
     rng = np.random.default_rng(7)  # same stream on every rank: all ranks know all blocks
     sizes = (1000, 0, 300, 2000, 17) if w == 2 else (400, 0, 300, 0, 0, 900, 17)

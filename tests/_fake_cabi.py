@@ -670,3 +670,9 @@ class FakeLib:
             f = np.where(k == nan_key, np.nan, f)
             o[:] = f.view(np.uint64)
         return 0
+
+    def xchg_gather_bitmap_bytes(self, inp, bit_off, idx, n, out, stream):
+        if n == 0:
+            return 0
+        _arr(out, np.uint8, n)[:] = _bits(inp, bit_off, _arr(idx, np.uint32, n)).astype(np.uint8)
+        return 0
