@@ -508,7 +508,7 @@ def run_b200(args):
                "primitives_only_value": ref.total_rows / t_prim}
 
     if args.trace:
-        print(f"[trace rank {rank}] phase ms over the {args.steps} timed steps: "
+        print(f"[trace rank {rank}] phase ms over the {args.steps} timed steps (e2e.*: over warm-up + e2e steps): "
               + json.dumps({k: round(v, 2) for k, v in ex.phase_ms.items()}), file=sys.stderr, flush=True)
     if rank == 0:
         line = {

@@ -203,7 +203,14 @@ class DeviceExchange:
                     num_outputs: Optional[int] = None, boundaries: Optional[list] = None,
                     seed: int = 0) -> List[pa.Table]:
         """Host blocks in, sorted host blocks out (stage + sort + export)."""
-        return self.export(self.sort(self.stage(blocks), sort_key, num_outputs, boundaries, seed))
+        self._phase(None)
+        ds = self.stage(blocks)
+        self._phase("e2e.stage_h2d")
+        out = self.sort(ds, sort_key, num_outputs, boundaries, seed)
+        self._phase("e2e.sort")
+        res = self.export(out)
+        self._phase("e2e.export_d2h")
+        return res
 
     # -- multi-GPU sort ------------------------------------------------------------
     def sort_distributed(self, ds: DeviceDataset, sort_key: SortKey,
