@@ -171,6 +171,18 @@ __device__ __forceinline__ uint32_t digit_of(uint64_t key, uint32_t val, int shi
   }
 }
 
+// shared-memory add issued only by lanes whose predicate is set (stays a predicated
+// ATOMS in SASS: no divergent branch around every item's leader atomic)
+__device__ __forceinline__ uint32_t atoms_add_if(uint32_t saddr, uint32_t v, bool pred) {
+  uint32_t old = 0;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %3, 0;\n\t@p atom.shared.add.u32 %0, [%1], %2;\n\t}"
+      : "+r"(old)
+      : "r"(saddr), "r"(v), "r"((uint32_t)pred)
+      : "memory");
+  return old;
+}
+
 template <int MODE, int RS_THREADS, int RS_ITEMS>
 __global__ void __launch_bounds__(RS_THREADS, rs_min_blocks(RS_THREADS, RS_ITEMS))
 k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
@@ -195,15 +207,25 @@ k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ va
   const uint32_t tile = smisc[16];
   const uint32_t tile_base = tile * (uint32_t)RS_TILE;
   const uint32_t tile_items = min((uint32_t)RS_TILE, n - tile_base);
+  const bool full = tile_items == (uint32_t)RS_TILE;  // every tile but the last
   const uint32_t warp_base = tile_base + warp * (32 * RS_ITEMS) + lane;
 
   // ---- load (warp-striped: item i of lane l sits at warp_base + 32*i) ----
   uint64_t key[RS_ITEMS];
   uint32_t val[RS_ITEMS];  // only live in MODE 1 (the compiler drops it otherwise)
+  if (full) {
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; ++i) key[i] = keys_in[warp_base + 32 * i];
+  } else {
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; ++i) {
+      const uint32_t idx = warp_base + 32 * i;
+      key[i] = idx < n ? keys_in[idx] : 0xFFFFFFFFFFFFFFFFull;
+    }
+  }
 #pragma unroll
   for (int i = 0; i < RS_ITEMS; ++i) {
     const uint32_t idx = warp_base + 32 * i;
-    key[i] = idx < n ? keys_in[idx] : 0xFFFFFFFFFFFFFFFFull;
     if constexpr (MODE == 1) val[i] = idx < n ? (vals_in ? vals_in[idx] : idx) : 0xFFFFFFFFu;
     else val[i] = 0u;
   }
@@ -215,34 +237,29 @@ k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ va
   // item (the first version did: 52 % short-scoreboard stalls, profiles/r01_summary.md).
   // The atomics of successive items are issued in program order by one warp to its
   // own counter row, so equal digits receive increasing bases in item order.
+  const uint32_t myhist_s = (uint32_t)__cvta_generic_to_shared(whist + warp * BINS);
   uint32_t* myhist = whist + warp * BINS;
   uint32_t rank2[RS_ITEMS / 2];  // two 16-bit in-tile ranks per register (tile <= 8192 rows)
-#pragma unroll
-  for (int i = 0; i < RS_ITEMS / 2; ++i) rank2[i] = 0;
   const unsigned lt_mask = lanemask_lt();
 #pragma unroll
   for (int h = 0; h < RS_ITEMS; h += RS_BATCH) {
-    uint32_t info[RS_BATCH];  // leader | lanes-before-me << 8 | group size << 16
+    uint32_t d[RS_BATCH];
+    unsigned m[RS_BATCH];
 #pragma unroll
     for (int u = 0; u < RS_BATCH; ++u) {
-      const uint32_t d = digit_of<MODE>(key[h + u], val[h + u], shift, validity, vbit);
-      const unsigned m = __match_any_sync(0xffffffffu, d);
-      info[u] = (uint32_t)(__ffs(m) - 1) | ((uint32_t)__popc(m & lt_mask) << 8) |
-                ((uint32_t)__popc(m) << 16);
+      d[u] = digit_of<MODE>(key[h + u], val[h + u], shift, validity, vbit);
+      m[u] = __match_any_sync(0xffffffffu, d[u]);
     }
     uint32_t prev[RS_BATCH];
 #pragma unroll
-    for (int u = 0; u < RS_BATCH; ++u) {
-      prev[u] = 0;
-      if (lane == (int)(info[u] & 31u)) {
-        const uint32_t d = digit_of<MODE>(key[h + u], val[h + u], shift, validity, vbit);
-        prev[u] = atomicAdd(&myhist[d], info[u] >> 16);
-      }
-    }
+    for (int u = 0; u < RS_BATCH; ++u)  // the lowest lane of every same-digit set adds the set's size
+      prev[u] = atoms_add_if(myhist_s + d[u] * 4, (uint32_t)__popc(m[u]), (m[u] & lt_mask) == 0);
 #pragma unroll
-    for (int u = 0; u < RS_BATCH; ++u)
-      rank2[(h + u) >> 1] |= (__shfl_sync(0xffffffffu, prev[u], (int)(info[u] & 31u)) + ((info[u] >> 8) & 63u))
-                             << (16 * ((h + u) & 1));
+    for (int u = 0; u < RS_BATCH; ++u) {
+      const uint32_t r = __shfl_sync(0xffffffffu, prev[u], __ffs(m[u]) - 1) + (uint32_t)__popc(m[u] & lt_mask);
+      if (((h + u) & 1) == 0) rank2[(h + u) >> 1] = r;
+      else rank2[(h + u) >> 1] |= r << 16;
+    }
   }
   __syncthreads();
 
@@ -286,9 +303,6 @@ k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ va
       // Windowed walk: the LB_WINDOW predecessors' words are fetched with independent
       // loads (one L2 round trip for the window, not one per tile), then consumed in
       // order up to the first word that is an inclusive prefix or not published yet.
-      // With ~300 tiles in flight a tile usually has to cross many LOCAL-only
-      // predecessors; the one-word-per-round-trip walk of the first version made that
-      // the longest phase of a tile.
       int64_t t = (int64_t)tile - 1;
       bool done = false;
       while (!done) {
@@ -296,7 +310,8 @@ k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ va
 #pragma unroll
         for (int j = 0; j < LB_WINDOW; ++j) {
           const int64_t tj = t - j;
-          w[j] = tj >= 0 ? *(volatile uint32_t*)(status + (size_t)tj * BINS + tid) : (2u << 30);  // before tile 0: an inclusive prefix of zero
+          w[j] = tj >= 0 ? *(volatile uint32_t*)(status + (size_t)tj * BINS + tid)
+                         : (2u << 30);  // before tile 0: an inclusive prefix of zero
         }
 #pragma unroll
         for (int j = 0; j < LB_WINDOW; ++j) {
@@ -314,11 +329,12 @@ k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ va
   }
   __syncthreads();
 
-  // ---- final in-tile ranks ----
+  // ---- final in-tile ranks (both halves of a register at once: no carry, ranks < 65536) ----
 #pragma unroll
-  for (int i = 0; i < RS_ITEMS; ++i) {
-    const uint32_t d = digit_of<MODE>(key[i], val[i], shift, validity, vbit);
-    rank2[i >> 1] += (myhist[d] + sstart[d]) << (16 * (i & 1));  // no carry: every rank < 65536
+  for (int i = 0; i < RS_ITEMS; i += 2) {
+    const uint32_t d0 = digit_of<MODE>(key[i], val[i], shift, validity, vbit);
+    const uint32_t d1 = digit_of<MODE>(key[i + 1], val[i + 1], shift, validity, vbit);
+    rank2[i >> 1] += (myhist[d0] + sstart[d0]) + ((myhist[d1] + sstart[d1]) << 16);
   }
   __syncthreads();  // whist is dead from here: skeys may overwrite it
 
@@ -332,23 +348,34 @@ k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ va
       v = val[i];
     } else {
       const uint32_t idx = warp_base + 32 * i;
-      v = idx < n ? (vals_in ? vals_in[idx] : idx) : 0xFFFFFFFFu;
+      v = (full || idx < n) ? (vals_in ? vals_in[idx] : idx) : 0xFFFFFFFFu;
     }
     svals[(rank2[i >> 1] >> (16 * (i & 1))) & 0xFFFFu] = v;
   }
   __syncthreads();
 
   // ---- coalesced write-out: consecutive threads, consecutive ranks ----
+  if (full) {
 #pragma unroll
-  for (int i = 0; i < RS_ITEMS; ++i) {
-    const uint32_t pos = i * RS_THREADS + tid;
-    if (pos < tile_items) {
+    for (int i = 0; i < RS_ITEMS; ++i) {
+      const uint32_t pos = i * RS_THREADS + tid;
       const uint64_t k = skeys[pos];
       const uint32_t v = svals[pos];
-      const uint32_t d = digit_of<MODE>(k, v, shift, validity, vbit);
-      const uint32_t g = sbase[d] + pos;
+      const uint32_t g = sbase[digit_of<MODE>(k, v, shift, validity, vbit)] + pos;
       keys_out[g] = k;
       vals_out[g] = v;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; ++i) {
+      const uint32_t pos = i * RS_THREADS + tid;
+      if (pos < tile_items) {
+        const uint64_t k = skeys[pos];
+        const uint32_t v = svals[pos];
+        const uint32_t g = sbase[digit_of<MODE>(k, v, shift, validity, vbit)] + pos;
+        keys_out[g] = k;
+        vals_out[g] = v;
+      }
     }
   }
 }
