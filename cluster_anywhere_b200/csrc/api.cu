@@ -136,3 +136,15 @@ extern "C" int xchg_set_l2_fetch_granularity(int bytes) {
   XCHG_CUDA_TRY(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)bytes));
   return XCHG_OK;
 }
+
+// ---- gather grid cap -------------------------------------------------------------
+namespace {
+std::atomic<int> g_gather_ctas_per_sm{0};
+}
+int xchg_gather_ctas_per_sm() { return g_gather_ctas_per_sm.load(std::memory_order_relaxed); }
+
+extern "C" int xchg_set_gather_ctas_per_sm(int ctas_per_sm) {
+  XCHG_REQUIRE(ctas_per_sm >= 0 && ctas_per_sm <= 32, "ctas_per_sm must be in [0, 32]");
+  g_gather_ctas_per_sm.store(ctas_per_sm);
+  return XCHG_OK;
+}

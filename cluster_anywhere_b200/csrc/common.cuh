@@ -30,6 +30,9 @@ static inline uint64_t xchg_align_up(uint64_t x, uint64_t a) { return (x + a - 1
 
 // Number of SMs of the current device (cached per process; B200 = 148).
 int xchg_sm_count();
+// CTAs per SM the gather kernels may use (0 = each kernel's own default); see
+// xchg_set_gather_ctas_per_sm.
+int xchg_gather_ctas_per_sm();
 
 __device__ __forceinline__ bool bit_is_set(const uint8_t* bm, int64_t i) {
   return (bm[i >> 3] >> (i & 7)) & 1;

@@ -350,6 +350,8 @@ k_gather_rows(const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off
 }
 
 int grid_for(uint64_t n, int threads, int per_sm) {
+  const int cap = xchg_gather_ctas_per_sm();
+  if (cap) per_sm = std::min(per_sm, cap);
   return (int)std::max<uint64_t>(1, std::min<uint64_t>((n + threads - 1) / threads,
                                                        (uint64_t)xchg_sm_count() * per_sm));
 }
@@ -446,7 +448,8 @@ static int launch_gather_rows(bool uniform, const uint8_t* in, const int64_t* in
     attr_done = true;
   }
   const uint64_t ntiles = (n_out + rows_per_tile - 1) / rows_per_tile;
-  const int grid = (int)std::min<uint64_t>(ntiles, (uint64_t)xchg_sm_count() * 3 * 4);
+  const int cap = xchg_gather_ctas_per_sm();
+  const int grid = (int)std::min<uint64_t>(ntiles, (uint64_t)xchg_sm_count() * (cap ? cap : 3 * 4));
   if (uniform)
     XCHG_LAUNCH(XK_GATHER_ROWS, s, k_gather_rows<true><<<grid, GR_THREADS, GR_SMEM, s>>>(in, in_off, width, idx, n_out, out_off, out,
                                                           rows_per_tile));

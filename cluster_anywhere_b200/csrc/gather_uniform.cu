@@ -204,7 +204,10 @@ int xchg_internal_gather_rows_uniform(const uint8_t* in, uint32_t w, const uint3
   const uint32_t magic_w = w == 1 ? 0u : (uint32_t)((0x100000000ull + w - 1) / w);
   const uint32_t magic_cpr = cpr == 1 ? 0u : (uint32_t)((0x100000000ull + cpr - 1) / cpr);
   const uint64_t ntiles = (n_out + rpt - 1) / rpt;
-  const int grid = (int)std::min<uint64_t>(ntiles, (uint64_t)xchg_sm_count() * 3 * 8);
+  // persistent CTAs (3 resident per SM, 8 waves of tiles each by default); a cap leaves
+  // SMs' shared memory to kernels running beside a link-bound peer-store gather
+  const int cap = xchg_gather_ctas_per_sm();
+  const int grid = (int)std::min<uint64_t>(ntiles, (uint64_t)xchg_sm_count() * (cap ? cap : 3 * 8));
   if (vec16)
     XCHG_LAUNCH(XK_GATHER_ROWS, s, k_gather_rows_uniform<true><<<grid, GU_THREADS, GU_SMEM, s>>>(
         in, w, idx, n_out, out, rpt, slot, magic_w, magic_cpr));

@@ -503,6 +503,150 @@ def _export_buffers(rt: Runtime, col: DeviceColumn, lo: int, hi: int, pending: l
     return build
 
 
+def export_blocks(rt: Runtime, table: DeviceTable, ranges: Sequence[tuple]) -> List[pa.Table]:
+    """Copy a device table back as one Arrow table per row range with ONE device->host
+    copy per column buffer: every block is a zero-copy window (Arrow ``offset``) into the
+    column's pinned host buffer.  The buffers' sizes depend only on the table (not on
+    where the ranges cut it), so the pinned-memory cache serves them again on the next
+    call; a copy per block asked it for new sizes every time, and re-pinning host memory
+    was the largest part of the end-to-end step.  int32 offsets of ragged columns are
+    re-based per block (a block stays under 2 GiB per column even when the table does
+    not)."""
+    n = table.num_rows
+    ranges = [(lo, hi) if hi > lo else (0, 0) for lo, hi in ranges]
+
+    def d2h(t: torch.Tensor) -> torch.Tensor:
+        h = rt.host_empty(t.numel(), t.dtype)
+        h.copy_(t, non_blocking=True)
+        return h
+
+    staged = []
+    max_rows = max([hi - lo for lo, hi in ranges] + [0])
+    for col in table.columns:
+        st = _storage_type(col.type)
+        ent = {"col": col, "st": st}
+        if col.validity is not None and n:
+            ent["valid"] = d2h(col.validity[: (n + 7) // 8])
+        if col.kind == "fixed":
+            ent["data"] = d2h(col.data[: n * col.width])
+        elif col.kind == "bits":
+            ent["data"] = d2h(col.data[: (n + 7) // 8])
+        else:
+            obits = _var_offset_bits(col.type)
+            if col.uniform is not None:
+                w = col.uniform
+                ent["data"] = d2h(col.data[: n * w])
+                # every block's offsets are a prefix of 0, w, 2w, ...
+                offs_d = rt.empty(max_rows + 1, torch.int32 if obits == 32 else torch.int64)
+                elem_w = w // col.width
+                if obits == 32:
+                    rt.call("xchg_offsets_uniform32", max_rows + 1, elem_w, _vp(offs_d), rt.stream)
+                else:
+                    rt.call("xchg_offsets_uniform64", max_rows + 1, elem_w, 0, _vp(offs_d), rt.stream)
+                ent["offsets"] = d2h(offs_d)
+            else:
+                total = int(col.offsets[n].item()) if n else 0  # sync: byte count
+                ent["data"] = d2h(col.data[:total])
+                if obits == 64 and col.width == 1:
+                    ent["offsets"] = d2h(col.offsets[: n + 1])
+                    ent["abs"] = True
+                else:
+                    # per-block relative offsets, packed back to back: block b at sum(m_i + 1)
+                    odt = torch.int32 if obits == 32 else torch.int64
+                    tot_entries = sum(hi - lo + 1 for lo, hi in ranges)
+                    offs_d = rt.empty(tot_entries, odt)
+                    cut_idx = sorted({x for r in ranges for x in r})
+                    ends = dict(zip(cut_idx, col.offsets[torch.tensor(cut_idx, device=rt.device)].tolist())) \
+                        if cut_idx else {}
+                    pos = 0
+                    for lo, hi in ranges:
+                        m = hi - lo
+                        if col.width == 1 and obits == 32:
+                            if ends.get(hi, 0) - ends.get(lo, 0) > 0x7FFFFFFF:
+                                raise XchgError(
+                                    f"column of type {col.type}: {ends[hi]-ends[lo]} bytes do not fit int32 "
+                                    "offsets; export it in smaller row ranges")
+                            rt.call("xchg_offsets_narrow", _vp(col.offsets[lo:]), m + 1, _vp(offs_d[pos:]), rt.stream)
+                        else:
+                            seg = col.offsets[lo: hi + 1]
+                            offs_d[pos: pos + m + 1] = ((seg - seg[0]) // col.width).to(odt)
+                        pos += m + 1
+                    ent["offsets"] = d2h(offs_d)
+                    ent["ends"] = ends
+        staged.append(ent)
+    rt.synchronize()
+
+    def buf(t: Optional[torch.Tensor]):
+        return None if t is None else pa.py_buffer(t.numpy())
+
+    whole = []
+    for ent in staged:
+        ent["vbuf"] = buf(ent.get("valid"))
+        ent["dbuf"] = buf(ent.get("data"))
+        ent["obuf"] = buf(ent.get("offsets"))
+        whole.append(ent)
+
+    out = []
+    packed_pos = [0] * len(whole)
+    for lo, hi in ranges:
+        m = hi - lo
+        arrays = []
+        for ci, ent in enumerate(whole):
+            col, st = ent["col"], ent["st"]
+            vbuf = ent["vbuf"]
+            nc = -1 if vbuf is not None else 0
+            if col.kind == "fixed":
+                if pa.types.is_fixed_size_list(st):
+                    child = pa.Array.from_buffers(st.value_type, n * st.list_size, [None, ent["dbuf"]])
+                    arr = pa.Array.from_buffers(st, m, [vbuf], null_count=nc, offset=lo, children=[child])
+                else:
+                    arr = pa.Array.from_buffers(st, m, [vbuf, ent["dbuf"]], null_count=nc, offset=lo)
+            elif col.kind == "bits":
+                arr = pa.Array.from_buffers(st, m, [vbuf, ent["dbuf"]], null_count=nc, offset=lo)
+            else:
+                is_list = pa.types.is_list(st) or pa.types.is_large_list(st)
+                if col.uniform is not None:
+                    w = col.uniform
+                    dslice = ent["dbuf"].slice(lo * w, m * w)
+                    # offsets start at 0 for every block; validity still needs the row offset
+                    if vbuf is not None and lo:
+                        vb = _bitmap_window(ent["valid"], lo, m)
+                    else:
+                        vb = vbuf
+                    if is_list:
+                        child = pa.Array.from_buffers(st.value_type, m * (w // col.width), [None, dslice])
+                        arr = pa.Array.from_buffers(st, m, [vb, ent["obuf"]], null_count=nc, children=[child])
+                    else:
+                        arr = pa.Array.from_buffers(st, m, [vb, ent["obuf"], dslice], null_count=nc)
+                elif ent.get("abs"):
+                    arr = pa.Array.from_buffers(st, m, [vbuf, ent["obuf"], ent["dbuf"]], null_count=nc, offset=lo)
+                else:
+                    isz = 4 if _var_offset_bits(col.type) == 32 else 8
+                    obuf = ent["obuf"].slice(packed_pos[ci] * isz, (m + 1) * isz)
+                    packed_pos[ci] += m + 1
+                    b0, b1 = ent["ends"].get(lo, 0), ent["ends"].get(hi, 0)
+                    dslice = ent["dbuf"].slice(b0, b1 - b0)
+                    vb = _bitmap_window(ent["valid"], lo, m) if (vbuf is not None and lo) else vbuf
+                    if is_list:
+                        child = pa.Array.from_buffers(st.value_type, (b1 - b0) // col.width, [None, dslice])
+                        arr = pa.Array.from_buffers(st, m, [vb, obuf], null_count=nc, children=[child])
+                    else:
+                        arr = pa.Array.from_buffers(st, m, [vb, obuf, dslice], null_count=nc)
+            if isinstance(col.type, pa.ExtensionType):
+                arr = pa.ExtensionArray.from_storage(col.type, arr)
+            arrays.append(arr)
+        out.append(pa.Table.from_arrays(arrays, schema=table.schema))
+    return out
+
+
+def _bitmap_window(valid_host: torch.Tensor, lo: int, m: int):
+    """Bits [lo, lo+m) of a host bitmap re-aligned to bit 0 (for arrays whose other
+    buffers start at the block rather than at the column)."""
+    b0, b1 = lo // 8, (lo + m + 7) // 8
+    bits = np.unpackbits(valid_host.numpy()[b0:b1], bitorder="little")[lo - b0 * 8: lo - b0 * 8 + m]
+    return pa.py_buffer(np.packbits(bits, bitorder="little"))
+
+
 def export_table(rt: Runtime, table: DeviceTable, lo: int = 0, hi: Optional[int] = None) -> pa.Table:
     """Copy rows [lo, hi) back to (pinned) host memory as an Arrow table."""
     hi = table.num_rows if hi is None else hi

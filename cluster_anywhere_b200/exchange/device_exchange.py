@@ -16,6 +16,7 @@ locally, range-partitions by G-1 splitters and exchanges over NCCL (see
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 from typing import List, Optional, Sequence, Tuple
 
@@ -113,17 +114,8 @@ class DeviceExchange:
         """HBM -> host Arrow blocks (pinned host buffers, one per output block)."""
         if ds.table is None:
             return [empty_table() for _ in ds.block_ranges]
-        # every block gets its own Arrow buffers (own int32 offsets: a block stays
-        # under 2 GiB per column even when the device table does not); all copies
-        # are queued first, then one stream synchronisation
-        rt, t = self.rt, ds.table
-        builders = []
-        for lo, hi in ds.block_ranges:
-            if hi <= lo:
-                lo = hi = 0
-            builders.append([dev._export_buffers(rt, c, lo, hi, []) for c in t.columns])
-        rt.synchronize()
-        return [pa.Table.from_arrays([b() for b in bs], schema=t.schema) for bs in builders]
+        # one device->host copy per column buffer; blocks are windows into it
+        return dev.export_blocks(self.rt, ds.table, ds.block_ranges)
 
     # -- sort --------------------------------------------------------------------
     def sample_keys(self, ds: DeviceDataset, sort_key: SortKey, n_samples: int, seed: int = 0,
@@ -170,7 +162,7 @@ class DeviceExchange:
         return SortTaskSpec.boundaries_from_samples(tuples, sort_key, num_reducers)
 
     def sort(self, ds: DeviceDataset, sort_key: SortKey, num_outputs: Optional[int] = None,
-             boundaries: Optional[list] = None, seed: int = 0) -> DeviceDataset:
+             boundaries: Optional[list] = None, seed: int = 0, _complete=None) -> DeviceDataset:
         """``Dataset.sort`` on resident blocks -> resident, range-partitioned output.
 
         ``num_outputs`` defaults to the number of input blocks
@@ -191,7 +183,8 @@ class DeviceExchange:
         perm, norms = dev.sort_permutation(rt, ds.table, sort_key.get_columns(),
                                            sort_key.get_descending(), want_norm=len(boundaries) > 0)
         cuts = cuts_for(rt, ds.table, norms, boundaries, sort_key) if boundaries else []
-        out = dev.take_table(rt, ds.table, perm, n, _presorted(sort_key, norms))
+        table = ds.table if _complete is None else _complete()  # payload columns may arrive late
+        out = dev.take_table(rt, table, perm, n, _presorted(sort_key, norms))
         ranges, last = [], 0
         for c in cuts:
             ranges.append((last, c))
@@ -288,17 +281,82 @@ class DeviceExchange:
             for d, cnt in enumerate(counts.tolist()):
                 send_counts[owners[d]] = int(cnt)
             self._phase("dist.assign_and_order")
+        lo_b, hi_b = int(ob[rank]), int(ob[rank + 1])
+        local_bounds = list(boundaries[lo_b:max(lo_b, hi_b - 1)])
+        from . import peer
+
+        if (peer.enabled(rt) and not getattr(self, "_p2p_unavailable", False) and not self.trace
+                and os.environ.get("XCHG_OVERLAP", "1") != "0"):
+            try:
+                return self._exchange_and_reduce_overlapped(table, perm, send_counts, sort_key,
+                                                            local_bounds, my_blocks, group)
+            except (ImportError, AttributeError, NotImplementedError) as e:
+                import warnings
+
+                warnings.warn(f"NVLink peer-memory exchange unavailable ({e!r}); using NCCL all-to-all")
+                self._p2p_unavailable = True
         recv = self._take_and_exchange(table, perm, send_counts, group)
 
         # ---- reduce: stable sort of the received runs, cut into this rank's blocks ----
         if my_blocks == 0:
             assert recv.num_rows == 0
             return DeviceDataset(None, [])
-        lo_b, hi_b = int(ob[rank]), int(ob[rank + 1])
-        local_bounds = list(boundaries[lo_b:hi_b - 1])
         out = self.sort(DeviceDataset(recv, [(0, recv.num_rows)]), sort_key, boundaries=local_bounds)
         self._phase("dist.reduce_sort")
         return out
+
+    def _exchange_and_reduce_overlapped(self, table, perm, send_counts, sort_key, local_bounds,
+                                        my_blocks, group) -> DeviceDataset:
+        """Exchange + reduce with the payload crossing NVLink WHILE the received keys are
+        sorted (the push-based schedule's idea -- merge work pipelined with transfers,
+        push_based_shuffle_task_scheduler.py:548-561 -- at the granularity this machine
+        offers: two streams).
+
+          main stream   key columns -> peers | fence | K2 + K3 on the received keys, K4 cuts
+          side stream                 payload columns -> peers (few CTAs per SM: the
+                                      stores are link-bound) | fence
+          main stream   waits for the side stream, then the final K5 over all columns
+        """
+        from . import peer
+
+        rt = self.rt
+        pl = peer.plan_exchange(rt, self, table, perm, send_counts, group)
+        names = list(table.names)
+        key_idx = [names.index(c) for c in sort_key.get_columns()]
+        rest_idx = [j for j in range(len(names)) if j not in key_idx]
+        main = torch.cuda.current_stream(rt.device)
+        if getattr(self, "_side_stream", None) is None:
+            self._side_stream = torch.cuda.Stream(device=rt.device)
+        side = self._side_stream
+
+        peer.store_columns(rt, pl, key_idx)
+        peer.fence(rt, group)
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            rt.call("xchg_set_gather_ctas_per_sm", int(os.environ.get("XCHG_SIDE_CTAS_PER_SM", "2")), launches=0)
+            try:
+                peer.store_columns(rt, pl, rest_idx)
+            finally:
+                rt.call("xchg_set_gather_ctas_per_sm", 0, launches=0)
+            peer.fence(rt, group)
+
+        m = int(pl.recv_rows[pl.rank])
+        if my_blocks == 0 or m == 0:
+            main.wait_stream(side)
+            return DeviceDataset(None, [(0, 0)] * my_blocks)
+        key_cols = peer.received_columns(rt, pl, key_idx)
+        keys_table = dev.DeviceTable([names[j] for j in key_idx], key_cols, m,
+                                     pa.schema([table.schema.field(j) for j in key_idx]))
+
+        def complete():
+            main.wait_stream(side)
+            rest_cols = peer.received_columns(rt, pl, rest_idx)
+            by_idx = dict(zip(key_idx, key_cols))
+            by_idx.update(zip(rest_idx, rest_cols))
+            return dev.DeviceTable(names, [by_idx[j] for j in range(len(names))], m, table.schema)
+
+        return self.sort(DeviceDataset(keys_table, [(0, m)]), sort_key, boundaries=local_bounds,
+                         _complete=complete)
 
     def sort_blocks_distributed(self, blocks: Sequence[pa.Table], sort_key: SortKey,
                                 boundaries: Optional[list] = None, seed: int = 0,

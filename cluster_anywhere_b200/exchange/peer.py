@@ -62,22 +62,40 @@ def _ptr(base: int, off: int = 0):
     return ctypes.c_void_p(int(base) + int(off))
 
 
-def gather_exchange(rt: dev.Runtime, holder, table: DeviceTable, perm: Optional[torch.Tensor],
-                    send_counts: Sequence[int], group=None) -> DeviceTable:
-    """``take(table, perm)`` ordered by destination rank, written straight into the
-    destinations' arenas.  ``perm`` (uint32 row ids, may be None when there are no rows)
-    lists this rank's rows by destination; ``send_counts[d]`` of them go to rank ``d``.
-    ``holder.arena`` caches the symmetric arena between calls.  Returns the received
-    rows in (source rank, position at the source) order; the table aliases the arena and
-    is valid until the next exchange."""
+class ExchangePlan:
+    """Everything every rank derives from the all-gathered count matrix: who sends how
+    many rows / bytes to whom, where each column's region sits in every rank's arena."""
+
+    def __init__(self):
+        self.rank = 0
+        self.G = 1
+        self.table: Optional[DeviceTable] = None
+        self.perm: Optional[torch.Tensor] = None
+        self.send_counts: List[int] = []
+        self.cuts = None
+        self.M = None
+        self.recv_rows = None
+        self.prefix_rows = None
+        self.col_plan: list = []
+        self.offsets_of: list = []
+        self.out_offs: dict = {}
+        self.arena: Optional[PeerArena] = None
+        self.group = None
+
+
+def plan_exchange(rt: dev.Runtime, holder, table: DeviceTable, perm: Optional[torch.Tensor],
+                  send_counts: Sequence[int], group=None) -> ExchangePlan:
+    """Counts all-gather (a stream-ordered collective: it also orders the stores that
+    follow after every peer's previous use of its arena), arena layout, arena (re)allocation."""
     rank, G = coll.world(group)
     n = table.num_rows
     ncols = len(table.columns)
     cuts = np.concatenate([[0], np.cumsum(np.asarray(send_counts, dtype=np.int64))])
     assert int(cuts[-1]) == n
+    pl = ExchangePlan()
+    pl.rank, pl.G, pl.table, pl.perm, pl.send_counts, pl.cuts, pl.group = rank, G, table, perm, list(send_counts), cuts, group
 
     # ---- ragged columns: output offsets of the whole take (needed for byte counts) ----
-    out_offs = {}
     for j, c in enumerate(table.columns):
         if c.kind == "var" and c.uniform is None and n:
             oo = rt.empty(n + 1, torch.int64)
@@ -86,7 +104,7 @@ def gather_exchange(rt: dev.Runtime, holder, table: DeviceTable, perm: Optional[
             ws = rt.empty(ws_bytes.value)
             rt.call("xchg_gather_offsets", _vp(c.offsets), _vp(perm), n, _vp(oo), _vp(ws), ws_bytes.value,
                     rt.stream, launches=3)
-            out_offs[j] = oo
+            pl.out_offs[j] = oo
 
     # ---- one all-gathered matrix: [rows | per column: bytes, has_validity, uniform] per dest ----
     meta = np.zeros((G, 1 + 3 * ncols), dtype=np.int64)
@@ -102,29 +120,29 @@ def gather_exchange(rt: dev.Runtime, holder, table: DeviceTable, perm: Optional[
             elif n:
                 if cum_d is None:
                     cum_d = torch.from_numpy(cuts).to(rt.device)
-                ends = out_offs[j][cum_d].tolist()  # sync: G+1 scalars
+                ends = pl.out_offs[j][cum_d].tolist()  # sync: G+1 scalars
                 meta[:, 1 + 3 * j] = np.diff(np.asarray(ends, dtype=np.int64))
     mine = torch.from_numpy(meta.reshape(-1)).to(rt.device)
     allm = torch.empty(G * mine.numel(), dtype=torch.int64, device=rt.device)
-    dist.all_gather_into_tensor(allm, mine, group=group)  # also orders the stores below after
-    M = allm.cpu().numpy().reshape(G, G, 1 + 3 * ncols)   # every peer's previous use of its arena
+    dist.all_gather_into_tensor(allm, mine, group=group)
+    M = allm.cpu().numpy().reshape(G, G, 1 + 3 * ncols)
     rows_sd = M[:, :, 0]                                   # [source, dest]
-    recv_rows = rows_sd.sum(axis=0)                        # per dest
-    prefix_rows = np.cumsum(rows_sd, axis=0) - rows_sd     # rows of earlier sources, [source, dest]
+    pl.M = M
+    pl.recv_rows = rows_sd.sum(axis=0)                     # per dest
+    pl.prefix_rows = np.cumsum(rows_sd, axis=0) - rows_sd  # rows of earlier sources, [source, dest]
 
     # ---- arena layout of every rank (identical arithmetic everywhere) ----
-    col_plan = []
-    offsets_of = [dict() for _ in range(G)]  # dest -> {(col, region): byte offset}
+    pl.offsets_of = [dict() for _ in range(G)]  # dest -> {(col, region): byte offset}
     totals = [0] * G
     for j, c in enumerate(table.columns):
         any_valid = bool(M[:, 0, 2 + 3 * j].max() > 0)
         uni = set(int(x) for x in M[:, 0, 3 + 3 * j])
         uniform = uni.pop() if (c.kind == "var" and len(uni) == 1 and -1 not in uni) else None
-        col_plan.append((any_valid, uniform))
+        pl.col_plan.append((any_valid, uniform))
         for d in range(G):
-            r = int(recv_rows[d])
+            r = int(pl.recv_rows[d])
             if any_valid:
-                offsets_of[d][(j, "valid")] = totals[d]
+                pl.offsets_of[d][(j, "valid")] = totals[d]
                 totals[d] += _up(r)
             if c.kind == "fixed":
                 nb = r * c.width
@@ -134,9 +152,9 @@ def gather_exchange(rt: dev.Runtime, holder, table: DeviceTable, perm: Optional[
                 nb = r * uniform
             else:
                 nb = int(M[:, d, 1 + 3 * j].sum())
-                offsets_of[d][(j, "offsets")] = totals[d]
+                pl.offsets_of[d][(j, "offsets")] = totals[d]
                 totals[d] += _up((r + 1) * 8)
-            offsets_of[d][(j, "data")] = totals[d]
+            pl.offsets_of[d][(j, "data")] = totals[d]
             totals[d] += _up(nb + 64)
     need = max(totals) + _ALIGN
     arena = getattr(holder, "arena", None)
@@ -146,26 +164,33 @@ def gather_exchange(rt: dev.Runtime, holder, table: DeviceTable, perm: Optional[
             del arena
         arena = PeerArena(rt, int(need * 1.25) + (1 << 20), group)
         holder.arena = arena
+    pl.arena = arena
+    return pl
 
-    # ---- stores into the peers: K5 once per (column, destination) ----
+
+def store_columns(rt: dev.Runtime, pl: ExchangePlan, cols: Sequence[int]) -> None:
+    """K5 once per (column, destination), output = the destination's arena (current stream)."""
+    table, perm, arena, M, rank, G = pl.table, pl.perm, pl.arena, pl.M, pl.rank, pl.G
     perm_ptr = perm.data_ptr() if perm is not None else 0
-    for j, c in enumerate(table.columns):
-        any_valid, uniform = col_plan[j]
+    for j in cols:
+        c = table.columns[j]
+        any_valid, uniform = pl.col_plan[j]
         for d in range(G):
-            k = int(send_counts[d])
+            k = int(pl.send_counts[d])
             if k == 0:
                 continue
-            lo = int(cuts[d])
+            lo = int(pl.cuts[d])
             idx = _ptr(perm_ptr, lo * 4)
-            pre = int(prefix_rows[rank, d])
+            pre = int(pl.prefix_rows[rank, d])
             base = arena.ptrs[d]
+            off = pl.offsets_of[d]
             if any_valid:
-                dst = _ptr(base, offsets_of[d][(j, "valid")] + pre)
+                dst = _ptr(base, off[(j, "valid")] + pre)
                 if c.validity is not None:
                     rt.call("xchg_gather_bitmap_bytes", _vp(c.validity), 0, idx, k, dst, rt.stream)
                 else:
-                    arena.hdl.get_buffer(d, (k,), torch.uint8, offsets_of[d][(j, "valid")] + pre).fill_(1)
-            data_off = offsets_of[d][(j, "data")]
+                    arena.hdl.get_buffer(d, (k,), torch.uint8, off[(j, "valid")] + pre).fill_(1)
+            data_off = off[(j, "data")]
             if c.kind == "fixed":
                 rt.call("xchg_gather_fixed", _vp(c.data), c.width, idx, k, _ptr(base, data_off + pre * c.width),
                         rt.stream)
@@ -180,26 +205,33 @@ def gather_exchange(rt: dev.Runtime, holder, table: DeviceTable, perm: Optional[
                     w = c.uniform
                     rt.call("xchg_gather_rows", _vp(c.data), w, idx, k, _ptr(base, data_off + pre_bytes), rt.stream)
                     rt.call("xchg_offsets_uniform64", k, w, pre_bytes,
-                            _ptr(base, offsets_of[d][(j, "offsets")] + pre * 8), rt.stream)
+                            _ptr(base, off[(j, "offsets")] + pre * 8), rt.stream)
                 else:
-                    oo = out_offs[j]
+                    oo = pl.out_offs[j]
                     first = int(M[rank, :d, 1 + 3 * j].sum())  # = oo[lo]: bytes of earlier destinations
                     # row i of the segment lands at  data + pre_bytes + (oo[lo+i] - oo[lo])
                     rt.call("xchg_gather_bytes", _vp(c.data), _vp(c.offsets), idx, k, _ptr(oo.data_ptr(), lo * 8),
                             _ptr(base, data_off + pre_bytes - first), rt.stream)
                     rt.call("xchg_offsets_rebase", _ptr(oo.data_ptr(), lo * 8), k, pre_bytes,
-                            _ptr(base, offsets_of[d][(j, "offsets")] + pre * 8), rt.stream)
+                            _ptr(base, off[(j, "offsets")] + pre * 8), rt.stream)
 
-    # ---- every rank's stores are complete and visible after this collective ----
+
+def fence(rt: dev.Runtime, group=None) -> None:
+    """After this stream-ordered collective every rank's preceding stores (on the stream
+    the collective was issued from) are complete and visible."""
     flag = torch.zeros(1, dtype=torch.int32, device=rt.device)
     dist.all_reduce(flag, group=group)
 
-    # ---- received table: views of the local arena ----
-    m = int(recv_rows[rank])
-    my = offsets_of[rank]
+
+def received_columns(rt: dev.Runtime, pl: ExchangePlan, cols: Sequence[int]) -> List[DeviceColumn]:
+    """Views of the local arena for the given columns (valid until the next exchange)."""
+    table, arena, M, rank = pl.table, pl.arena, pl.M, pl.rank
+    m = int(pl.recv_rows[rank])
+    my = pl.offsets_of[rank]
     out_cols: List[DeviceColumn] = []
-    for j, c in enumerate(table.columns):
-        any_valid, uniform = col_plan[j]
+    for j in cols:
+        c = table.columns[j]
+        any_valid, uniform = pl.col_plan[j]
         validity, nulls = None, 0
         if any_valid and m:
             vb = arena.buf[my[(j, "valid")]: my[(j, "valid")] + m]
@@ -225,4 +257,20 @@ def gather_exchange(rt: dev.Runtime, holder, table: DeviceTable, perm: Optional[
             offs = arena.buf[oo_off: oo_off + (m + 1) * 8].view(torch.int64)
             rt.call("xchg_offsets_uniform64", 1, 0, total, _ptr(offs.data_ptr(), m * 8), rt.stream)
             out_cols.append(DeviceColumn(c.type, m, "var", c.width, arena.buf[o: o + total], offs, validity, nulls))
-    return DeviceTable(list(table.names), out_cols, m, table.schema)
+    return out_cols
+
+
+def gather_exchange(rt: dev.Runtime, holder, table: DeviceTable, perm: Optional[torch.Tensor],
+                    send_counts: Sequence[int], group=None) -> DeviceTable:
+    """``take(table, perm)`` ordered by destination rank, written straight into the
+    destinations' arenas.  ``perm`` (uint32 row ids, may be None when there are no rows)
+    lists this rank's rows by destination; ``send_counts[d]`` of them go to rank ``d``.
+    ``holder.arena`` caches the symmetric arena between calls.  Returns the received
+    rows in (source rank, position at the source) order; the table aliases the arena and
+    is valid until the next exchange."""
+    pl = plan_exchange(rt, holder, table, perm, send_counts, group)
+    every = list(range(len(table.columns)))
+    store_columns(rt, pl, every)
+    fence(rt, group)
+    cols = received_columns(rt, pl, every)
+    return DeviceTable(list(table.names), cols, int(pl.recv_rows[pl.rank]), table.schema)

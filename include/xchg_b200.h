@@ -77,6 +77,13 @@ int xchg_profile_read(int kernel_id, double* total_ms, uint64_t* launches);
  * counterpart in the reference.  bytes = 32, 64 or 128. */
 int xchg_set_l2_fetch_granularity(int bytes);
 
+/* Cap on the CTAs per SM the gather kernels launch (0 = each kernel's default).  The
+ * multi-GPU exchange sets a small cap while its peer-store gathers -- NVLink-bound, a
+ * few CTAs per SM saturate the links -- run on a side stream beside the receive-side
+ * key sort, so that they do not take the SMs' shared memory away from it.  Process
+ * wide; no counterpart in the reference. */
+int xchg_set_gather_ctas_per_sm(int ctas_per_sm);
+
 /* ---------------------------------------------------------------- sort ---- */
 
 /* Workspace bytes xchg_sort_column needs for n rows. */

@@ -676,3 +676,6 @@ class FakeLib:
             return 0
         _arr(out, np.uint8, n)[:] = _bits(inp, bit_off, _arr(idx, np.uint32, n)).astype(np.uint8)
         return 0
+
+    def xchg_set_gather_ctas_per_sm(self, n):
+        return 0
