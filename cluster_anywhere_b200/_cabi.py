@@ -56,6 +56,10 @@ _SIGNATURES = {
     "xchg_bitmap_unpack": (c_int, [_P, c_int64, c_uint64, _P, _P]),
     "xchg_bitmap_pack": (c_int, [_P, c_uint64, _P, _P, _P]),
     "xchg_offsets_rebase": (c_int, [_P, c_uint64, c_int64, _P, _P]),
+    "xchg_string_lengths": (c_int, [_P, c_uint64, _P, _P, _P]),
+    "xchg_string_chunk_keys": (c_int, [_P, _P, c_uint64, c_uint32, _P, _P]),
+    "xchg_partition_bounds_bytes": (c_int, [_P, _P, _P, c_uint64, _P, _P, _P, c_int, c_int, _P, _P]),
+    "xchg_assign_partitions_bytes": (c_int, [_P, _P, _P, c_uint64, _P, _P, _P, c_int, c_int, _P, _P, _P]),
     "xchg_gather_fixed": (c_int, [_P, c_uint32, _P, c_uint64, _P, _P]),
     "xchg_gather_bitmap": (c_int, [_P, c_int64, _P, c_uint64, _P, _P, _P]),
     "xchg_gather_offsets_workspace_bytes": (c_int, [c_uint64, ctypes.POINTER(c_uint64)]),

@@ -29,11 +29,21 @@ def _device_sort(rt: dev.Runtime, dt: dev.DeviceTable, sort_key: SortKey, want_n
 
 def _presorted(sort_key: SortKey, norms):
     """Primary key column -> its radix keys in output order (see dev.take_table)."""
+    if not norms or norms[0] is None:
+        return None
     return {sort_key.get_columns()[0]: (norms[0], sort_key.get_descending()[0])}
 
 
-def _cuts_for(rt: dev.Runtime, dt: dev.DeviceTable, norms, boundaries, sort_key: SortKey) -> List[int]:
+def _cuts_for(rt: dev.Runtime, dt: dev.DeviceTable, norms, boundaries, sort_key: SortKey,
+              sorted_dt: Optional[dev.DeviceTable] = None) -> List[int]:
+    """K4.  Numeric keys: search on the sorted radix keys.  A string key (single key
+    column only) is searched on the sorted column itself (``sorted_dt``)."""
     cols, desc = sort_key.get_columns(), sort_key.get_descending()
+    if any(dev.is_string_key(dt.column(c)) for c in cols):
+        if len(cols) != 1:
+            raise NotImplementedError("range partitioning with a string key supports a single key column")
+        assert sorted_dt is not None
+        return dev.string_partition_cuts(rt, sorted_dt.column(cols[0]), boundaries, desc[0])
     ktypes = [dev.key_type_of(dt.column(c).type) for c in cols]
     lower, upper, flags = keymod.normalize_boundaries(boundaries, ktypes, desc)
     thr = [keymod.last_class_threshold(k, dt.column(c).null_count) for k, c in zip(ktypes, cols)]
@@ -176,7 +186,7 @@ class B200ArrowBlockAccessor:
         sorted_dt = dev.take_table(rt, dt, perm, dt.num_rows, _presorted(sort_key, norms))
         if not want:
             return [dev.export_table(rt, sorted_dt)]
-        cuts = _cuts_for(rt, dt, norms, boundaries, sort_key)
+        cuts = _cuts_for(rt, dt, norms, boundaries, sort_key, sorted_dt)
         table = dev.export_table(rt, sorted_dt)
         out, last = [], 0
         for c in cuts:

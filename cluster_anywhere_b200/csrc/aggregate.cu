@@ -212,16 +212,21 @@ k_acc_values(const uint32_t* __restrict__ rgid, const T* __restrict__ vals,
     const T x = valid ? vals[i] : T(0);
     const unsigned m = __match_any_sync(act, g);
     const int leader = __ffs(m) - 1;
-    // the leader of every same-group lane set folds the set's values, then issues one
-    // atomic per statistic (members of a set run the loop in lock step)
+    // The leader of every same-group lane set folds the set's values, then issues one
+    // atomic per statistic.  All lanes walk the loop together with FULL-warp shuffles
+    // (trip count = the largest set in the warp: 1 when every lane has its own group);
+    // per-set shuffle masks would make the hardware converge and run the sets one after
+    // the other.
     S sum = 0;
     unsigned cnt = 0, nan = 0;
     uint64_t mn = EMPTY, mx = 0;
-    for (unsigned mm = m; mm; mm &= mm - 1) {
-      const int src = __ffs(mm) - 1;
-      const T xv = __shfl_sync(m, x, src);
-      const int vv = __shfl_sync(m, (int)valid, src);
-      if (lane == leader && vv) {
+    const int steps = (int)__reduce_max_sync(act, (unsigned)__popc(m));
+    unsigned rem = m;
+    for (int st = 0; st < steps; ++st) {
+      const int src = rem ? __ffs(rem) - 1 : lane;
+      const T xv = __shfl_sync(act, x, src);
+      const int vv = __shfl_sync(act, (int)valid, src);
+      if (lane == leader && rem && vv) {
         ++cnt;
         sum += (S)xv;
         if (want_minmax) {
@@ -236,6 +241,7 @@ k_acc_values(const uint32_t* __restrict__ rgid, const T* __restrict__ vals,
           }
         }
       }
+      rem &= rem - 1;
     }
     if (lane == leader && cnt) {
       atomicAdd(&a.cnt[g], (unsigned long long)cnt);
@@ -277,9 +283,12 @@ k_acc_m2(const uint32_t* __restrict__ rgid, const T* __restrict__ vals,
     const unsigned m = __match_any_sync(act, g);
     const int leader = __ffs(m) - 1;
     double tot = 0.0;
-    for (unsigned mm = m; mm; mm &= mm - 1) {
-      const double v = __shfl_sync(m, d2, __ffs(mm) - 1);
-      if (lane == leader) tot += v;
+    const int steps = (int)__reduce_max_sync(act, (unsigned)__popc(m));
+    unsigned rem = m;
+    for (int st = 0; st < steps; ++st) {
+      const double v = __shfl_sync(act, d2, rem ? __ffs(rem) - 1 : lane);
+      if (lane == leader && rem) tot += v;
+      rem &= rem - 1;
     }
     if (lane == leader && tot != 0.0) atomicAdd(&m2[g], tot);  // (NaN != 0: it propagates)
   }

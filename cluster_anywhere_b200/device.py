@@ -675,6 +675,83 @@ def sort_workspace_bytes(n: int) -> int:
 
 # launches per xchg_sort_column call: normalise+hist, scan, <=9 passes (bench counts the
 # exact number from the active-place flags; here we book the upper bound lazily)
+def is_string_key(col: DeviceColumn) -> bool:
+    """Arrow binary / string / large_* column (byte rows), usable as a bytewise sort key."""
+    t = _storage_type(col.type)
+    return col.kind == "var" and (pa.types.is_binary(t) or pa.types.is_string(t)
+                                  or pa.types.is_large_binary(t) or pa.types.is_large_string(t))
+
+
+def _string_offsets(rt: Runtime, col: DeviceColumn) -> torch.Tensor:
+    if col.offsets is not None:
+        return col.offsets
+    off = rt.empty(col.n + 1, torch.int64)  # uniform rows: offsets are arithmetic
+    rt.call("xchg_offsets_uniform64", col.n + 1, col.uniform, 0, _vp(off), rt.stream)
+    return off
+
+
+def _sort_string_column(rt: Runtime, col: DeviceColumn, desc: bool, perm, n: int, ws, ws_bytes):
+    """Stable sort by one string column: LSD over (length, last chunk, ..., chunk 0), every
+    step a stable K3 sort of a u32 / u64 key array (see csrc/strings.cu)."""
+    off = _string_offsets(rt, col)
+    lens = rt.empty(n, torch.int32)
+    mx = rt.zeros(1, torch.int64)
+    rt.call("xchg_string_lengths", _vp(off), n, _vp(lens), _vp(mx), rt.stream)
+    max_len = int(mx.item())  # sync: number of chunks
+    nchunks = (max_len + 7) // 8
+    out = rt.empty(n, torch.int32)
+    # validity goes with the most significant step (nulls last in both directions)
+    rt.call("xchg_sort_column", _vp(lens), _cabi.U32, int(desc), _vp(col.validity) if nchunks == 0 else None,
+            0, _vp(perm), n, _vp(out), None, _vp(ws), ws_bytes, rt.stream, launches=6)
+    perm = out
+    keys = rt.empty(n, torch.int64) if nchunks else None
+    for c in range(nchunks - 1, -1, -1):
+        rt.call("xchg_string_chunk_keys", _vp(off), _vp(col.data), n, c, _vp(keys), rt.stream)
+        out = rt.empty(n, torch.int32)
+        rt.call("xchg_sort_column", _vp(keys), _cabi.U64, int(desc), _vp(col.validity) if c == 0 else None, 0,
+                _vp(perm), n, _vp(out), None, _vp(ws), ws_bytes, rt.stream, launches=11)
+        perm = out
+    return perm
+
+
+def _pack_string_boundaries(rt: Runtime, boundaries: Sequence[tuple]):
+    """Boundary tuples of a single string key -> (offsets int64[nb+1], data, flags) on the device."""
+    vals, flags = [], []
+    for b in boundaries:
+        v = b[0] if isinstance(b, (tuple, list)) else b
+        if v is None:
+            vals.append(b"")
+            flags.append(4)
+        else:
+            vals.append(v.encode("utf-8") if isinstance(v, str) else bytes(v))
+            flags.append(0)
+    off = np.zeros(len(vals) + 1, dtype=np.int64)
+    off[1:] = np.cumsum([len(v) for v in vals])
+    blob = np.frombuffer(b"".join(vals), dtype=np.uint8) if off[-1] else np.zeros(0, np.uint8)
+    off_d = rt.empty(len(off), torch.int64)
+    _h2d(off_d.view(torch.uint8), off.view(np.uint8))
+    data_d = rt.empty(max(1, len(blob)))
+    if len(blob):
+        _h2d(data_d[: len(blob)], blob.copy())
+    fl_d = rt.empty(max(1, len(flags)), torch.uint8)
+    _h2d(fl_d[: len(flags)], np.asarray(flags, dtype=np.uint8))
+    return off_d, data_d, fl_d
+
+
+def string_partition_cuts(rt: Runtime, sorted_col: DeviceColumn, boundaries: Sequence[tuple],
+                          descending: bool) -> List[int]:
+    """K4 for one string key: cut indices on the SORTED column."""
+    nb = len(boundaries)
+    if nb == 0:
+        return []
+    off_d, data_d, fl_d = _pack_string_boundaries(rt, boundaries)
+    cuts = rt.empty(nb, torch.int64)
+    rt.call("xchg_partition_bounds_bytes", _vp(_string_offsets(rt, sorted_col)), _vp(sorted_col.data),
+            _vp(sorted_col.validity), sorted_col.n, _vp(off_d), _vp(data_d), _vp(fl_d), nb,
+            int(bool(descending)), _vp(cuts), rt.stream)
+    return [int(x) for x in cuts.tolist()]
+
+
 def sort_permutation(rt: Runtime, table: DeviceTable, columns: Sequence[str],
                      descending: Sequence[bool], want_norm: bool = False):
     """Stable multi-key sort -> (perm uint32[n] as int32 tensor, [norm key arrays]).
@@ -694,6 +771,9 @@ def sort_permutation(rt: Runtime, table: DeviceTable, columns: Sequence[str],
     for ci in range(len(order) - 1, -1, -1):
         name, desc = order[ci]
         col = table.column(name)
+        if is_string_key(col):
+            perm = _sort_string_column(rt, col, bool(desc), perm, n, ws, ws_bytes)
+            continue
         if col.kind != "fixed":
             raise NotImplementedError(f"sort key column {name!r} of type {col.type} is not supported")
         kt = key_type_of(col.type)
@@ -708,6 +788,10 @@ def sort_permutation(rt: Runtime, table: DeviceTable, columns: Sequence[str],
     if want_norm:
         for name, desc in order[1:]:
             col = table.column(name)
+            if is_string_key(col):
+                raise NotImplementedError(
+                    "range partitioning on several key columns is supported for numeric keys only; "
+                    f"{name!r} is {col.type}")
             nk = rt.empty(n, torch.int64)
             rt.call("xchg_normalize_keys", _vp(col.data), key_type_of(col.type), int(bool(desc)),
                     _vp(col.validity), 0, _vp(perm), n, _vp(nk), rt.stream)
@@ -765,6 +849,16 @@ def assign_partitions(rt: Runtime, table: DeviceTable, boundaries: Sequence[tupl
 
     cols, desc = sort_key.get_columns(), sort_key.get_descending()
     n, nb = table.num_rows, len(boundaries)
+    if any(is_string_key(table.column(c)) for c in cols):
+        if len(cols) != 1:
+            raise NotImplementedError("range partitioning with a string key supports a single key column")
+        col = table.column(cols[0])
+        off_d, data_d, fl_d = _pack_string_boundaries(rt, boundaries)
+        dest = rt.empty(n, torch.int32)
+        counts = rt.zeros(nb + 1, torch.int64)
+        rt.call("xchg_assign_partitions_bytes", _vp(_string_offsets(rt, col)), _vp(col.data), _vp(col.validity),
+                n, _vp(off_d), _vp(data_d), _vp(fl_d), nb, int(bool(desc[0])), _vp(dest), _vp(counts), rt.stream)
+        return dest, counts
     ktypes = [key_type_of(table.column(c).type) for c in cols]
     lower, upper, flags = keymod.normalize_boundaries(boundaries, ktypes, desc)
     norms = normalized_key_columns(rt, table, cols, desc)

@@ -182,9 +182,12 @@ class DeviceExchange:
         n = ds.num_rows
         perm, norms = dev.sort_permutation(rt, ds.table, sort_key.get_columns(),
                                            sort_key.get_descending(), want_norm=len(boundaries) > 0)
-        cuts = cuts_for(rt, ds.table, norms, boundaries, sort_key) if boundaries else []
+        string_key = any(dev.is_string_key(ds.table.column(c)) for c in sort_key.get_columns())
+        cuts = cuts_for(rt, ds.table, norms, boundaries, sort_key) if (boundaries and not string_key) else []
         table = ds.table if _complete is None else _complete()  # payload columns may arrive late
         out = dev.take_table(rt, table, perm, n, _presorted(sort_key, norms))
+        if boundaries and string_key:  # string keys are searched on the sorted column itself
+            cuts = cuts_for(rt, ds.table, norms, boundaries, sort_key, out)
         ranges, last = [], 0
         for c in cuts:
             ranges.append((last, c))

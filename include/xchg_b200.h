@@ -193,6 +193,44 @@ int xchg_assign_partitions(const uint64_t* const* norm_cols_host, const uint8_t*
                            int nb, int first_descending, uint32_t* dest_out,
                            uint64_t* counts_out, void* stream);
 
+/* ------------------------------------------------- string / binary keys ---- */
+/*
+ * Sort keys of variable-width columns (Arrow binary / string, int64 byte offsets as this
+ * engine stages them).  Arrow's order -- what pyarrow.compute.sort_indices gives the
+ * reference at python/ray/data/_internal/arrow_ops/transform_pyarrow.py:41 -- is bytewise
+ * (unsigned), a proper prefix before the longer string.  That order equals the
+ * lexicographic order of (chunk 0, chunk 1, ..., length) where chunk c = bytes
+ * [8c, 8c+8) as a big-endian u64, zero padded; callers sort LSD over those columns with
+ * xchg_sort_column (length as XCHG_U32 first, then the chunks as XCHG_U64 from the last
+ * to the first, the column's validity on the final call), chaining perm_out -> perm_in.
+ *
+ * xchg_string_lengths   len_out[i] = bytes of row i; *max_len_out (device uint64) = the
+ *                       longest row (tells the caller how many chunks exist)
+ * xchg_string_chunk_keys  keys_out[i] = chunk `chunk` of row i
+ */
+int xchg_string_lengths(const int64_t* offsets, uint64_t n, uint32_t* len_out, uint64_t* max_len_out,
+                        void* stream);
+int xchg_string_chunk_keys(const int64_t* offsets, const uint8_t* data, uint64_t n, uint32_t chunk,
+                           uint64_t* keys_out, void* stream);
+/*
+ * find_partition_index (python/ray/data/_internal/util.py:728-803) for ONE string key
+ * column: cut index of every boundary on the SORTED column (nulls last; the reference
+ * replaces nulls by NULL_SENTINEL, :765-772, so a None boundary equals the null rows).
+ * Boundaries are packed like an Arrow binary array (bound_offsets nb+1 entries,
+ * bound_data); bound_flags[b] bit2 = None boundary.  Descending reproduces
+ * numpy.searchsorted over the reversed view probe by probe, as xchg_partition_bounds does.
+ */
+int xchg_partition_bounds_bytes(const int64_t* sorted_offsets, const uint8_t* sorted_data,
+                                const uint8_t* sorted_validity, uint64_t n,
+                                const int64_t* bound_offsets, const uint8_t* bound_data,
+                                const uint8_t* bound_flags, int nb, int descending,
+                                uint64_t* cuts_out, void* stream);
+/* The same rule per row of an UNSORTED string column (see xchg_assign_partitions). */
+int xchg_assign_partitions_bytes(const int64_t* offsets, const uint8_t* data, const uint8_t* validity,
+                                 uint64_t n, const int64_t* bound_offsets, const uint8_t* bound_data,
+                                 const uint8_t* bound_flags, int nb, int descending,
+                                 uint32_t* dest_out, uint64_t* counts_out, void* stream);
+
 /* -------------------------------------------------------------- gather ---- */
 
 /*

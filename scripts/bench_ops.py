@@ -1,0 +1,118 @@
+#!/usr/bin/env python
+"""Secondary measurements: random_shuffle and groupby().aggregate() on the
+per-GPU shards of BASELINE.json configs[2] / configs[3], inputs resident in HBM, CUDA
+events, per-kernel device time from the library's profiling hooks.  One JSON line per op.
+
+  python scripts/bench_ops.py [--steps K] [--warmup W]
+"""
+import argparse
+import ctypes
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+KNAMES = {0: "k_normalize_hist", 1: "k_scan_hist", 2: "k_onesweep", 3: "k_gather_rows", 4: "k_gather_fixed",
+          5: "k_gather_bitmap", 6: "k_lengths_scan", 7: "k_partition", 8: "k_offsets_*", 9: "misc",
+          10: "k_merge", 11: "k_shuffle", 12: "k_aggregate"}
+
+
+def kernels(lib, steps):
+    from cluster_anywhere_b200 import _cabi
+
+    out = []
+    for kid, name in KNAMES.items():
+        tot, cnt = ctypes.c_double(), ctypes.c_uint64()
+        _cabi.check(lib.xchg_profile_read(kid, ctypes.byref(tot), ctypes.byref(cnt)))
+        if cnt.value:
+            out.append({"kernel": name, "launches_per_step": cnt.value / steps, "ms_per_step": tot.value / steps})
+    return sorted(out, key=lambda k: -k["ms_per_step"])
+
+
+def timed(fn, steps, warmup, lib):
+    import torch
+
+    for i in range(warmup):
+        fn(i)
+    torch.cuda.synchronize()
+    lib.xchg_profile_enable(1)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        out = fn(100 + i)
+        del out
+    e1.record()
+    torch.cuda.synchronize()
+    ks = kernels(lib, steps)
+    lib.xchg_profile_enable(0)
+    return e0.elapsed_time(e1) / steps, ks
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--shuffle-rows", type=int, default=25_000_000)
+    ap.add_argument("--agg-rows", type=int, default=250_000_000)
+    ap.add_argument("--agg-groups", type=int, default=10_000_000)
+    args = ap.parse_args()
+    import pyarrow as pa
+    import torch
+
+    import __graft_entry__ as ge
+
+    ge.build()
+    from cluster_anywhere_b200 import Count, Mean, Sum, _cabi
+    from cluster_anywhere_b200 import device as dev
+    from cluster_anywhere_b200.exchange import DeviceDataset, DeviceExchange
+
+    lib = _cabi.load()
+    rt = dev.Runtime()
+    ex = DeviceExchange(rt)
+    peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(
+        os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+
+    # ---- configs[2] shard: random_shuffle(seed=42) of 1 KiB tensor rows ----
+    n, w = args.shuffle_rows, 1024
+    data = torch.empty(n * w + 64, dtype=torch.uint8, device=rt.device)[: n * w]
+    data.view(torch.int64)[:] = torch.arange(n * w // 8, device=rt.device, dtype=torch.int64)  # row-id derived
+    typ = pa.large_list(pa.uint8())
+    col = dev.DeviceColumn(typ, n, "var", 1, data, None, None, 0, uniform=w)
+    table = dev.DeviceTable(["data"], [col], n, pa.schema([("data", typ)]))
+    blocks = 24
+    ds = DeviceDataset(table, [(i * n // blocks, (i + 1) * n // blocks) for i in range(blocks)])
+    ms, ks = timed(lambda i: ex.random_shuffle(ds, 42), args.steps, args.warmup, lib)
+    gbs = 2 * n * w / ms / 1e6
+    print(json.dumps({"op": "random_shuffle", "workload": f"{n} rows x 1 KiB tensor rows (25.6 GB), seed 42, "
+                      f"{blocks} blocks: the per-GPU shard of BASELINE configs[2] (200 M rows at 8 GPUs)",
+                      "ms_per_step": ms, "rows_per_s": n / ms * 1e3, "gb_per_s_algorithmic": gbs,
+                      "frac_of_measured_hbm": gbs / peak, "kernels": ks}), flush=True)
+    del ds, table, col, data
+    torch.cuda.empty_cache()
+
+    # ---- configs[3] shard: groupby(int32 key).aggregate(Sum, Mean, Count) over float32 rows ----
+    n, g = args.agg_rows, args.agg_groups
+    gen = torch.Generator(device=rt.device)
+    gen.manual_seed(4)
+    k = torch.randint(0, g, (n,), dtype=torch.int32, device=rt.device, generator=gen)
+    v = torch.randn(n, dtype=torch.float32, device=rt.device, generator=gen)
+    kc = dev.DeviceColumn(pa.int32(), n, "fixed", 4, k.view(torch.uint8))
+    vc = dev.DeviceColumn(pa.float32(), n, "fixed", 4, v.view(torch.uint8))
+    table = dev.DeviceTable(["k", "v"], [kc, vc], n, pa.schema([("k", pa.int32()), ("v", pa.float32())]))
+    blocks = 16
+    ds = DeviceDataset(table, [(i * n // blocks, (i + 1) * n // blocks) for i in range(blocks)])
+    aggs = [Sum("v"), Mean("v"), Count()]
+    ms, ks = timed(lambda i: ex.aggregate(ds, "k", aggs, seed=i), args.steps, args.warmup, lib)
+    out = ex.aggregate(ds, "k", aggs)
+    groups = out.num_rows
+    gbs = (8 * n + 32 * groups) / ms / 1e6
+    print(json.dumps({"op": "groupby.aggregate", "workload": f"{n} rows (int32 key, float32 value), {groups} groups, "
+                      f"Sum/Mean/Count, {blocks} blocks: the per-GPU shard of BASELINE configs[3] (2 B rows at 8 GPUs)",
+                      "ms_per_step": ms, "rows_per_s": n / ms * 1e3, "gb_per_s_algorithmic": gbs,
+                      "frac_of_measured_hbm": gbs / peak, "kernels": ks}), flush=True)
+
+
+if __name__ == "__main__":
+    main()

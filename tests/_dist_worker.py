@@ -54,7 +54,8 @@ def main():
     ex = DeviceExchange()
     full = pa.concat_tables([b for b in all_blocks if b.num_rows])
     cases = [(["k"], [False], None), (["k", "f"], [True, False], None), (["f"], [True], None),
-             (["f", "k"], [True, True], None),
+             (["f", "k"], [True, True], None), (["s"], [False], None), (["s"], [True], None),
+             (["s"], [False], [("s1",), ("s5",), (None,)]),
              (["k"], [False], [(-20,), (0,), (0,), (31,)]), (["k"], [True], [(10,), (-10,)])]
     for cols, desc, bounds in cases:
         sk = SortKey(cols, desc)

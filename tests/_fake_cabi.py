@@ -679,3 +679,84 @@ class FakeLib:
 
     def xchg_set_gather_ctas_per_sm(self, n):
         return 0
+
+    # -- string keys -------------------------------------------------------------
+    @staticmethod
+    def _rows_bytes(off, data, n):
+        o = _arr(off, np.int64, n + 1)
+        d = _arr(data, np.uint8, int(o[n])) if n and int(o[n]) else np.zeros(0, np.uint8)
+        return [bytes(d[o[i]:o[i + 1]]) for i in range(n)]
+
+    def xchg_string_lengths(self, off, n, len_out, max_len, stream):
+        _arr(max_len, np.uint64, 1)[0] = 0
+        if n == 0:
+            return 0
+        o = _arr(off, np.int64, n + 1)
+        l = np.diff(o)
+        _arr(len_out, np.uint32, n)[:] = np.minimum(l, 0xFFFFFFFF).astype(np.uint32)
+        _arr(max_len, np.uint64, 1)[0] = int(l.max())
+        return 0
+
+    def xchg_string_chunk_keys(self, off, data, n, chunk, out, stream):
+        if n == 0:
+            return 0
+        rows = self._rows_bytes(off, data, n)
+        _arr(out, np.uint64, n)[:] = np.array(
+            [int.from_bytes(r[8 * chunk: 8 * chunk + 8].ljust(8, b"\0"), "big") for r in rows], dtype=np.uint64)
+        return 0
+
+    def _str_inputs(self, off, data, validity, n, boff, bdata, bflags, nb):
+        rows = self._rows_bytes(off, data, n)
+        valid = _bits(validity, 0, np.arange(n, dtype=np.int64)) if _addr(validity) and n else np.ones(n, bool)
+        bounds = self._rows_bytes(boff, bdata, nb)
+        fl = _arr(bflags, np.uint8, nb) if _addr(bflags) else np.zeros(nb, np.uint8)
+        return rows, valid, bounds, fl
+
+    def xchg_partition_bounds_bytes(self, off, data, validity, n, boff, bdata, bflags, nb, desc, cuts, stream):
+        rows, valid, bounds, fl = self._str_inputs(off, data, validity, n, boff, bdata, bflags, nb)
+        out = _arr(cuts, np.uint64, nb)
+        for b in range(nb):
+            none = bool(fl[b] & 4)
+            if not desc:
+                lo, hi = 0, n
+                while lo < hi:
+                    mid = (lo + hi) // 2
+                    before = False if not valid[mid] else (True if none else rows[mid] < bounds[b])
+                    lo, hi = (mid + 1, hi) if before else (lo, mid)
+                out[b] = lo
+            else:
+                mn, mx = 0, n
+                while mn < mx:
+                    mid = mn + (mx - mn) // 2
+                    r = n - 1 - mid
+                    el = not valid[r]
+                    lt = (not el) if none else ((not el) and rows[r] < bounds[b])
+                    mn, mx = (mid + 1, mx) if lt else (mn, mid)
+                out[b] = n - mn
+        return 0
+
+    def xchg_assign_partitions_bytes(self, off, data, validity, n, boff, bdata, bflags, nb, desc, dest, counts,
+                                     stream):
+        if _addr(counts):
+            _arr(counts, np.uint64, nb + 1)[:] = 0
+        if n == 0:
+            return 0
+        rows, valid, bounds, fl = self._str_inputs(off, data, validity, n, boff, bdata, bflags, nb)
+        d = np.zeros(n, dtype=np.uint32)
+        for i in range(n):
+            cnt = 0
+            for b in range(nb):
+                none = bool(fl[b] & 4)
+                if not desc:
+                    right = True if not valid[i] else (False if none else rows[i] >= bounds[b])
+                else:
+                    right = True if (none or not valid[i]) else rows[i] < bounds[b]
+                if right:
+                    cnt += 1
+                else:
+                    break
+            d[i] = cnt
+        _arr(dest, np.uint32, n)[:] = d
+        if _addr(counts):
+            _arr(counts, np.uint64, nb + 1)[:] = np.bincount(d, minlength=nb + 1).astype(np.uint64)
+        return 0

@@ -104,8 +104,8 @@ def test_sort_key_errors(engine):
     t = pa.table({"a": [1]})
     with pytest.raises(ValueError):
         B200ArrowBlockAccessor.for_block(t).sort(SortKey("nope"))
-    with pytest.raises(NotImplementedError):
-        B200ArrowBlockAccessor.for_block(pa.table({"s": ["b", "a"]})).sort(SortKey("s"))
+    with pytest.raises(NotImplementedError):  # nested key types are not offloaded
+        B200ArrowBlockAccessor.for_block(pa.table({"s": [[2], [1]]})).sort(SortKey("s"))
 
 
 # ---- reference-generated golden fixtures ---------------------------------------
@@ -287,3 +287,74 @@ def test_take_and_sample(engine):
     assert s.num_rows == 50 and s.schema.names == ["k"]
     with pytest.raises(IndexError):
         B200ArrowBlockAccessor.for_block(t).take([n])
+
+
+# ---- string / binary sort keys (BASELINE configs[4]) ----------------------------------
+
+def _string_table(rng, n, kind="string", nulls=True, zipf=False):
+    if zipf:
+        vocab = ["w%d" % i + "x" * int(rng.integers(0, 24)) for i in range(200)]
+        vals = [vocab[min(int(z), len(vocab)) - 1] for z in rng.zipf(1.2, n)]
+    else:
+        alphabet = ["", "a", "b", "ab", "aa", "B", "\u00e9", "abc", "ab\x00", "ab\x00c", "zzzzzzzz", "zzzzzzzzz",
+                    "zzzzzzzz\x00", "0123456789abcdef", "0123456789abcdefg", "0123456789abcdeF"]
+        vals = [alphabet[int(i)] + ("" if rng.random() < 0.7 else str(rng.integers(0, 50)))
+                for i in rng.integers(0, len(alphabet), n)]
+    mask = (rng.random(n) < 0.1) if nulls else None
+    if kind == "string":
+        key = pa.array(vals, pa.string(), mask=mask)
+    elif kind == "large_string":
+        key = pa.array(vals, pa.large_string(), mask=mask)
+    else:
+        key = pa.array([v.encode() + bytes([int(rng.integers(0, 256))]) for v in vals], pa.binary(), mask=mask)
+    return pa.table({"s": key, "row": np.arange(n), "p": pa.array(["p%d" % i for i in range(n)])})
+
+
+@pytest.mark.parametrize("kind", ["string", "large_string", "binary"])
+@pytest.mark.parametrize("desc", [False, True])
+def test_string_key_sort(engine, kind, desc):
+    rng = np.random.default_rng(abs(hash((kind, desc))) % (2**32))
+    n = 20_011 if engine == "b200" else 1200
+    for zipf in (False, True):
+        t = _string_table(rng, n, kind, nulls=True, zipf=zipf)
+        got = B200ArrowBlockAccessor.for_block(t).sort(SortKey("s", desc))
+        assert G.tables_equal(got, O.sort_table(t, ["s"], [desc]))
+    # string as the SECOND key, numeric first
+    t = _string_table(rng, n, kind).append_column("k", pa.array(rng.integers(0, 5, n)))
+    got = B200ArrowBlockAccessor.for_block(t).sort(SortKey(["k", "s"], [desc, not desc]))
+    assert G.tables_equal(got, O.sort_table(t, ["k", "s"], [desc, not desc]))
+    # all-null / all-empty / empty-string-only columns
+    t = pa.table({"s": pa.array([None, None, None], pa.string()), "row": [0, 1, 2]})
+    assert G.tables_equal(B200ArrowBlockAccessor.for_block(t).sort(SortKey("s", desc)), O.sort_table(t, ["s"], [desc]))
+    t = pa.table({"s": pa.array(["", "", None, ""], pa.string()), "row": [0, 1, 2, 3]})
+    assert G.tables_equal(B200ArrowBlockAccessor.for_block(t).sort(SortKey("s", desc)), O.sort_table(t, ["s"], [desc]))
+
+
+@pytest.mark.parametrize("desc", [False, True])
+@pytest.mark.parametrize("nulls", [False, True])
+def test_string_key_partitions(engine, desc, nulls):
+    """sort_and_partition / the pull-based exchange with a string key vs the oracle
+    (find_partition_index on an object column: nulls are NULL_SENTINEL, util.py:765-772)."""
+    rng = np.random.default_rng(77 + int(desc) * 2 + int(nulls))
+    n = 9_001 if engine == "b200" else 700
+    t = _string_table(rng, n, "string", nulls=nulls)
+    bounds = [("B",), ("aa",), ("ab",), ("ab\x00c",), ("zzzzzzzz",)]
+    if desc:
+        bounds = bounds[::-1]
+    if not (desc and nulls):
+        bounds = bounds + [(None,)] if not desc else [(None,)] + bounds
+    got = B200ArrowBlockAccessor.for_block(t).sort_and_partition(bounds, SortKey("s", desc))
+    exp = O.sort_and_partition(t, bounds, ["s"], [desc])
+    _check_partitions(got, exp)
+    blocks = [t.slice(0, n // 3), t.slice(n // 3, 0), t.slice(n // 3)]
+    from cluster_anywhere_b200.exchange import DeviceExchange
+
+    out = DeviceExchange().sort_blocks(blocks, SortKey("s", desc), boundaries=bounds)
+    exp_x = O.sort_exchange(blocks, bounds, ["s"], [desc])
+    if not (desc and nulls):  # per-block vs global cuts agree wherever the rule is per-row consistent
+        _check_partitions(out, exp_x)
+    assert G.tables_equal(pa.concat_tables(out), O.sort_table(t, ["s"], [desc]))
+    # sampled boundaries: whole exchange
+    out = DeviceExchange().sort_blocks(blocks, SortKey("s", desc), seed=4)
+    assert len(out) == 3
+    assert G.tables_equal(pa.concat_tables([o for o in out if o.num_rows]), O.sort_table(t, ["s"], [desc]))
