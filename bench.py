@@ -44,7 +44,7 @@ PAYLOAD = 90
 
 KERNEL_NAMES = {0: "k_normalize_hist", 1: "k_scan_hist", 2: "k_onesweep", 3: "k_gather_rows",
                 4: "k_gather_fixed", 5: "k_gather_bitmap", 6: "k_lengths_scan", 7: "k_partition_bounds",
-                8: "k_offsets_*", 9: "misc", 10: "k_merge", 11: "k_shuffle", 12: "k_aggregate"}
+                8: "k_offsets_*", 9: "misc", 10: "k_merge", 11: "k_shuffle", 12: "k_aggregate", 13: "k_local_sort", 14: "k_msd_aux"}
 # algorithmic bytes per row per launch
 KERNEL_BYTES_PER_ROW = {0: 16, 2: 24, 3: 2 * PAYLOAD}
 

@@ -34,6 +34,7 @@ _SIGNATURES = {
     "xchg_denormalize_keys": (c_int, [_P, c_int, c_int, c_uint64, _P, _P]),
     "xchg_set_l2_fetch_granularity": (c_int, [c_int]),
     "xchg_set_gather_ctas_per_sm": (c_int, [c_int]),
+    "xchg_set_sort_algorithm": (c_int, [c_int]),
     "xchg_partition_bounds": (c_int, [ctypes.POINTER(c_void_p), _P, _P, _P, c_int, c_uint64, _P, _P, _P, c_int, c_int, _P, _P]),
     "xchg_assign_partitions": (c_int, [ctypes.POINTER(c_void_p), _P, c_int, c_uint64, _P, _P, _P, c_int, c_int, _P, _P, _P]),
     "xchg_shuffle_positions": (c_int, [c_uint64, c_uint64, c_uint64, c_uint64, c_int, _P, _P]),

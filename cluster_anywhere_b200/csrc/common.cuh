@@ -108,7 +108,9 @@ enum XchgKernelId {
   XK_MERGE = 10,
   XK_SHUFFLE = 11,
   XK_AGGREGATE = 12,
-  XK_COUNT = 13
+  XK_LOCAL_SORT = 13,
+  XK_MSD_AUX = 14,
+  XK_COUNT = 15
 };
 
 void xchg_prof_begin(int kernel_id, cudaStream_t s);

@@ -13,6 +13,7 @@
 // the tile in shared memory in digit order and writes it out in coalesced runs.
 // Algorithmic bytes per pass: 24 B/row (12 read + 12 written).
 #include <algorithm>
+#include <atomic>
 #include <cstdlib>
 #include <type_traits>
 
@@ -171,24 +172,58 @@ __device__ __forceinline__ uint32_t digit_of(uint64_t key, uint32_t val, int shi
   }
 }
 
-// shared-memory add issued only by lanes whose predicate is set (stays a predicated
-// ATOMS in SASS: no divergent branch around every item's leader atomic)
-__device__ __forceinline__ uint32_t atoms_add_if(uint32_t saddr, uint32_t v, bool pred) {
+// Lanes of the warp holding the same 8-bit digit.  Eight ballots and a select/and per
+// bit instead of one match.any: MATCH.ANY runs on the SM's single ADU pipe at ~2 cycles
+// per distinct value in the warp (~64 cycles per instruction on random digits; ncu showed
+// that pipe 70-74 % busy and bounding both the onesweep pass and the local sort at
+// ~1.2 ms per 125 M rows), whereas the votes and logic ops spread over the four
+// schedulers' ordinary pipes.
+__device__ __forceinline__ unsigned match_digit(uint32_t d) {
+  unsigned m = 0xffffffffu;
+#pragma unroll
+  for (int b = 0; b < 8; ++b) {
+    const bool p = (d >> b) & 1u;
+    const unsigned v = __ballot_sync(0xffffffffu, p);
+    m &= p ? v : ~v;
+  }
+  return m;
+}
+
+// Bump of a warp-PRIVATE shared-memory counter by the lanes whose predicate is set:
+// returns the old value.  Plain load + add + store, predicated (no divergent branch):
+// within one call the active lanes hold distinct digits, hence distinct addresses, and
+// no other warp touches this warp's counter row, so no atomic is needed -- a shared
+// atomic costs ~2 cycles per active lane on this part (ATOMS, 60 cycles per warp and
+// item with random digits: it bounded both the onesweep pass and the local sort), the
+// load/store pair a few cycles per warp.  Successive calls are ordered by the
+// __syncwarp() the caller issues between them.
+__device__ __forceinline__ uint32_t warp_counter_bump(uint32_t saddr, uint32_t v, bool pred) {
   uint32_t old = 0;
   asm volatile(
-      "{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %3, 0;\n\t@p atom.shared.add.u32 %0, [%1], %2;\n\t}"
+      "{\n\t.reg .pred p;\n\t.reg .u32 t;\n\tsetp.ne.u32 p, %3, 0;\n\t"
+      "@p ld.shared.u32 %0, [%1];\n\t@p add.u32 t, %0, %2;\n\t@p st.shared.u32 [%1], t;\n\t}"
       : "+r"(old)
       : "r"(saddr), "r"(v), "r"((uint32_t)pred)
       : "memory");
   return old;
 }
 
-template <int MODE, int RS_THREADS, int RS_ITEMS>
+// One segment of an MSD level: rows [start, start + count) share every digit above the
+// level's place; its tiles are tbase .. tbase + ceil(count / tile) - 1.
+struct Seg {
+  uint32_t start, count, tbase, pad;
+};
+
+// SEG = false: one LSD / top-level pass over the whole array.  SEG = true: the same pass
+// run independently inside every segment of an MSD level (tile -> segment through
+// tile_seg; digit offsets, look-back and output positions are relative to the segment).
+template <int MODE, int RS_THREADS, int RS_ITEMS, bool SEG>
 __global__ void __launch_bounds__(RS_THREADS, rs_min_blocks(RS_THREADS, RS_ITEMS))
-k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-           uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, uint32_t n,
-           int shift, const uint32_t* __restrict__ gexcl, uint32_t* status,
-           uint32_t* tile_counter, const uint8_t* __restrict__ validity, int64_t vbit) {
+k_onesweep(const uint64_t* __restrict__ keys_in_, const uint32_t* __restrict__ vals_in_,
+           uint64_t* __restrict__ keys_out_, uint32_t* __restrict__ vals_out_, uint32_t n_,
+           int shift, const uint32_t* __restrict__ gexcl_, uint32_t* status,
+           uint32_t* tile_counter, const uint8_t* __restrict__ validity, int64_t vbit,
+           const Seg* __restrict__ segs, const uint32_t* __restrict__ tile_seg) {
   constexpr int RS_WARPS = RS_THREADS / 32;
   constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
   extern __shared__ __align__(16) uint8_t smem[];
@@ -205,7 +240,24 @@ k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ va
   for (int j = tid; j < RS_WARPS * BINS; j += RS_THREADS) whist[j] = 0;
   __syncthreads();
   const uint32_t tile = smisc[16];
-  const uint32_t tile_base = tile * (uint32_t)RS_TILE;
+  const uint64_t* keys_in = keys_in_;
+  const uint32_t* vals_in = vals_in_;
+  uint64_t* keys_out = keys_out_;
+  uint32_t* vals_out = vals_out_;
+  const uint32_t* gexcl = gexcl_;
+  uint32_t n = n_, tile0 = 0;
+  if constexpr (SEG) {
+    const uint32_t sj = tile_seg[tile];
+    const Seg sg = segs[sj];
+    keys_in += sg.start;
+    vals_in += sg.start;
+    keys_out += sg.start;
+    vals_out += sg.start;
+    gexcl += (size_t)sj * BINS;
+    n = sg.count;
+    tile0 = sg.tbase;
+  }
+  const uint32_t tile_base = (tile - tile0) * (uint32_t)RS_TILE;
   const uint32_t tile_items = min((uint32_t)RS_TILE, n - tile_base);
   const bool full = tile_items == (uint32_t)RS_TILE;  // every tile but the last
   const uint32_t warp_base = tile_base + warp * (32 * RS_ITEMS) + lane;
@@ -231,12 +283,11 @@ k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ va
   }
 
   // ---- rank inside the warp, in (i, lane) = memory order: stable ----
-  // RS_BATCH items at a time, three independent sweeps (match masks, leader atomics on
-  // the warp's private counters, broadcasts) so that the ~30-cycle shared-memory
-  // round trips of different items overlap instead of forming one serial chain per
-  // item (the first version did: 52 % short-scoreboard stalls, profiles/r01_summary.md).
-  // The atomics of successive items are issued in program order by one warp to its
-  // own counter row, so equal digits receive increasing bases in item order.
+  // RS_BATCH items at a time: match masks first (independent), then the leaders' counter
+  // bumps on the warp's private counter row one item after the other (ordered by
+  // __syncwarp, so equal digits receive increasing bases in item order), then the
+  // broadcasts.  The bumps are plain shared-memory load/add/store, not atomics (see
+  // warp_counter_bump).
   const uint32_t myhist_s = (uint32_t)__cvta_generic_to_shared(whist + warp * BINS);
   uint32_t* myhist = whist + warp * BINS;
   uint32_t rank2[RS_ITEMS / 2];  // two 16-bit in-tile ranks per register (tile <= 8192 rows)
@@ -248,12 +299,14 @@ k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ va
 #pragma unroll
     for (int u = 0; u < RS_BATCH; ++u) {
       d[u] = digit_of<MODE>(key[h + u], val[h + u], shift, validity, vbit);
-      m[u] = __match_any_sync(0xffffffffu, d[u]);
+      m[u] = match_digit(d[u]);
     }
     uint32_t prev[RS_BATCH];
 #pragma unroll
-    for (int u = 0; u < RS_BATCH; ++u)  // the lowest lane of every same-digit set adds the set's size
-      prev[u] = atoms_add_if(myhist_s + d[u] * 4, (uint32_t)__popc(m[u]), (m[u] & lt_mask) == 0);
+    for (int u = 0; u < RS_BATCH; ++u) {  // the lowest lane of every same-digit set adds the set's size
+      prev[u] = warp_counter_bump(myhist_s + d[u] * 4, (uint32_t)__popc(m[u]), (m[u] & lt_mask) == 0);
+      __syncwarp();
+    }
 #pragma unroll
     for (int u = 0; u < RS_BATCH; ++u) {
       const uint32_t r = __shfl_sync(0xffffffffu, prev[u], __ffs(m[u]) - 1) + (uint32_t)__popc(m[u] & lt_mask);
@@ -296,7 +349,7 @@ k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ va
     if (tid == BINS - 1) cnt -= (uint32_t)RS_TILE - tile_items;  // padding sits in bin 255
     volatile uint32_t* st = status + (size_t)tile * BINS + tid;
     uint32_t excl = 0;
-    if (tile == 0) {
+    if (tile == tile0) {
       *st = FLAG_INCL | cnt;
     } else {
       *st = FLAG_LOCAL | cnt;
@@ -310,8 +363,8 @@ k_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ va
 #pragma unroll
         for (int j = 0; j < LB_WINDOW; ++j) {
           const int64_t tj = t - j;
-          w[j] = tj >= 0 ? *(volatile uint32_t*)(status + (size_t)tj * BINS + tid)
-                         : (2u << 30);  // before tile 0: an inclusive prefix of zero
+          w[j] = tj >= (int64_t)tile0 ? *(volatile uint32_t*)(status + (size_t)tj * BINS + tid)
+                                      : (2u << 30);  // before the first tile: an inclusive prefix of zero
         }
 #pragma unroll
         for (int j = 0; j < LB_WINDOW; ++j) {
@@ -400,6 +453,246 @@ __global__ void k_iota_or_copy(const uint32_t* __restrict__ in, uint32_t* __rest
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = in ? in[i] : i;
 }
 
+// ------------------------------------------------- MSD levels + local sort -----
+//
+// Sorting 125 M random 64-bit keys by eight LSD passes moves 8 x 24 B per row through
+// HBM.  The hybrid below runs the passes from the TOP place down instead, each level
+// splitting every segment (rows equal in all higher places) into 256 children with a
+// segmented onesweep pass, and stops moving a segment through HBM as soon as it fits in
+// shared memory: a CTA then loads it once, finishes all remaining places with a local
+// LSD sort and writes it to its final position.  Random 64-bit keys take two global
+// levels (65 536 segments of ~1 900 rows) and one local sort: 3 x 24 + 8 B per row.
+// Every pass is stable, so the result is identical to the LSD sort's.
+
+constexpr int LS_CLASSES = 4;
+constexpr uint32_t LS_CAP = 4096;  // largest segment a CTA sorts locally
+
+struct MsdCounters {
+  uint32_t nsmall[LS_CLASSES];
+  uint32_t nbig, ntiles, pad0, pad1;
+};
+
+__host__ __device__ constexpr uint32_t ls_class_cap(int c) { return 512u << c; }
+
+// Histogram of one digit place inside every segment of a level (8 B read per row).
+template <int TILE>
+__global__ void __launch_bounds__(256)
+k_seg_hist(const uint64_t* __restrict__ keys, int shift, const Seg* __restrict__ segs,
+           const uint32_t* __restrict__ tile_seg, uint32_t* __restrict__ seg_hist) {
+  __shared__ uint32_t sh[BINS];
+  const uint32_t tile = blockIdx.x;
+  const uint32_t sj = tile_seg[tile];
+  const Seg sg = segs[sj];
+  const uint32_t base = (tile - sg.tbase) * (uint32_t)TILE;
+  const uint32_t items = min((uint32_t)TILE, sg.count - base);
+  sh[threadIdx.x] = 0;
+  __syncthreads();
+  const uint64_t* k = keys + sg.start + base;
+  for (uint32_t i = threadIdx.x; i < items; i += 256) atomicAdd(&sh[(uint32_t)(k[i] >> shift) & 255u], 1u);
+  __syncthreads();
+  if (sh[threadIdx.x]) atomicAdd(&seg_hist[(size_t)sj * BINS + threadIdx.x], sh[threadIdx.x]);
+}
+
+// One CTA per segment: exclusive scan of its 256 counts.
+__global__ void __launch_bounds__(BINS)
+k_seg_scan(const uint32_t* __restrict__ seg_hist, uint32_t* __restrict__ seg_excl) {
+  __shared__ uint32_t wsum[BINS / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t c = seg_hist[(size_t)blockIdx.x * BINS + tid];
+  uint32_t x = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= o) x += y;
+  }
+  if (lane == 31) wsum[warp] = x;
+  __syncthreads();
+  uint32_t base = 0;
+  for (int w = 0; w < warp; ++w) base += wsum[w];
+  seg_excl[(size_t)blockIdx.x * BINS + tid] = base + x - c;
+}
+
+// Children of a level (one thread per parent segment and digit): small ones go to the
+// local-sort list of their size class, the others become the next level's segments and
+// claim their tiles.  parents == NULL: the single top-level segment [0, n).
+__global__ void __launch_bounds__(BINS)
+k_msd_classify(const Seg* __restrict__ parents, const uint32_t* __restrict__ hist,
+               const uint32_t* __restrict__ excl, uint32_t tile_rows, Seg* __restrict__ big_next,
+               uint64_t* __restrict__ small0, uint64_t* __restrict__ small1,
+               uint64_t* __restrict__ small2, uint64_t* __restrict__ small3,
+               MsdCounters* __restrict__ ctr) {
+  const size_t e = (size_t)blockIdx.x * BINS + threadIdx.x;
+  const uint32_t c = hist[e];
+  if (c == 0) return;
+  const uint32_t st = (parents ? parents[blockIdx.x].start : 0u) + excl[e];
+  if (c <= LS_CAP) {
+    const int cls = c <= ls_class_cap(0) ? 0 : (c <= ls_class_cap(1) ? 1 : (c <= ls_class_cap(2) ? 2 : 3));
+    uint64_t* list = cls == 0 ? small0 : (cls == 1 ? small1 : (cls == 2 ? small2 : small3));
+    const uint32_t idx = atomicAdd(&ctr->nsmall[cls], 1u);
+    list[idx] = (uint64_t)st | ((uint64_t)c << 32);
+  } else {
+    const uint32_t idx = atomicAdd(&ctr->nbig, 1u);
+    const uint32_t nt = (c + tile_rows - 1) / tile_rows;
+    const uint32_t tb = atomicAdd(&ctr->ntiles, nt);
+    big_next[idx] = Seg{st, c, tb, 0u};
+  }
+}
+
+__global__ void __launch_bounds__(128)
+k_fill_tile_map(const Seg* __restrict__ segs, uint32_t tile_rows, uint32_t* __restrict__ tile_seg) {
+  const Seg sg = segs[blockIdx.x];
+  const uint32_t nt = (sg.count + tile_rows - 1) / tile_rows;
+  for (uint32_t t = threadIdx.x; t < nt; t += blockDim.x) tile_seg[sg.tbase + t] = blockIdx.x;
+}
+
+struct LocalPlaces {
+  int n;
+  int shift[KEY_PLACES];
+};
+
+constexpr size_t ls_smem(int threads, int items) {
+  return (size_t)threads * items * 12 + (size_t)(2 * (threads / 32) * BINS + BINS + 32) * 4;
+}
+constexpr int ls_min_blocks(int threads, int items) {
+  // registers: 3 per item + ranks + ~28; shared memory: 12 B per row + counters
+  return items >= 16 ? (threads >= 256 ? 2 : 4) : (threads >= 256 ? 4 : 8);
+}
+
+// One CTA per small segment: load it, LSD-sort it by the remaining (lower) places in
+// shared memory, write it to its final position.  Rows past the segment's end are padded
+// with all-ones keys, which stay behind every real row through every stable pass.
+template <int LS_THREADS, int LS_ITEMS>
+__global__ void __launch_bounds__(LS_THREADS, ls_min_blocks(LS_THREADS, LS_ITEMS))
+k_local_sort(const uint64_t* __restrict__ src_keys, const uint32_t* __restrict__ src_vals,
+             uint64_t* __restrict__ dst_keys, uint32_t* __restrict__ dst_vals,
+             const uint64_t* __restrict__ small, LocalPlaces places) {
+  constexpr int WARPS = LS_THREADS / 32;
+  constexpr int ROWS = LS_THREADS * LS_ITEMS;
+  constexpr int BPT = BINS / LS_THREADS > 0 ? BINS / LS_THREADS : 1;  // bins per scanning thread
+  constexpr int SCAN_THREADS = BINS / BPT;
+  extern __shared__ __align__(16) uint8_t smem[];
+  uint64_t* skeys = reinterpret_cast<uint64_t*>(smem);
+  uint32_t* svals = reinterpret_cast<uint32_t*>(smem + (size_t)ROWS * 8);
+  uint32_t* whist = reinterpret_cast<uint32_t*>(smem + (size_t)ROWS * 12);  // [WARPS][BINS], zero between passes
+  uint32_t* woff = whist + WARPS * BINS;                                    // [WARPS][BINS]
+  uint32_t* sstart = woff + WARPS * BINS;                                   // [BINS]
+  uint32_t* smisc = sstart + BINS;
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint64_t ent = small[blockIdx.x];
+  const uint32_t st = (uint32_t)ent, cnt = (uint32_t)(ent >> 32);
+  const uint32_t wb = warp * (32 * LS_ITEMS) + lane;
+
+  for (int j = tid; j < WARPS * BINS; j += LS_THREADS) whist[j] = 0;
+
+  uint64_t key[LS_ITEMS];
+  uint32_t val[LS_ITEMS];
+#pragma unroll
+  for (int i = 0; i < LS_ITEMS; ++i) {
+    const uint32_t idx = wb + 32 * i;
+    key[i] = idx < cnt ? src_keys[st + idx] : 0xFFFFFFFFFFFFFFFFull;
+    val[i] = idx < cnt ? src_vals[st + idx] : 0xFFFFFFFFu;
+  }
+  __syncthreads();
+
+  const uint32_t myhist_s = (uint32_t)__cvta_generic_to_shared(whist + warp * BINS);
+  const uint32_t* myoff = woff + warp * BINS;
+  const unsigned lt_mask = lanemask_lt();
+  constexpr int BATCH = LS_ITEMS < RS_BATCH ? LS_ITEMS : RS_BATCH;
+
+  for (int p = 0; p < places.n; ++p) {
+    const int shift = places.shift[p];
+    uint32_t rank2[(LS_ITEMS + 1) / 2];
+#pragma unroll
+    for (int h = 0; h < LS_ITEMS; h += BATCH) {
+      uint32_t d[BATCH];
+      unsigned m[BATCH];
+#pragma unroll
+      for (int u = 0; u < BATCH; ++u) {
+        d[u] = (uint32_t)(key[h + u] >> shift) & 255u;
+        m[u] = match_digit(d[u]);
+      }
+      uint32_t prev[BATCH];
+#pragma unroll
+      for (int u = 0; u < BATCH; ++u) {
+        prev[u] = warp_counter_bump(myhist_s + d[u] * 4, (uint32_t)__popc(m[u]), (m[u] & lt_mask) == 0);
+        __syncwarp();
+      }
+#pragma unroll
+      for (int u = 0; u < BATCH; ++u) {
+        const uint32_t r = __shfl_sync(0xffffffffu, prev[u], __ffs(m[u]) - 1) + (uint32_t)__popc(m[u] & lt_mask);
+        if (((h + u) & 1) == 0) rank2[(h + u) >> 1] = r;
+        else rank2[(h + u) >> 1] |= r << 16;
+      }
+    }
+    __syncthreads();
+
+    // per digit: offsets of the warps' counts, digit totals, exclusive digit scan; the
+    // counters are left at zero for the next pass
+    uint32_t total = 0, incl = 0;
+    if (tid < SCAN_THREADS) {
+      uint32_t tb[BPT];
+#pragma unroll
+      for (int b = 0; b < BPT; ++b) {
+        const int bin = tid * BPT + b;
+        uint32_t t = 0;
+#pragma unroll
+        for (int w = 0; w < WARPS; ++w) {
+          const uint32_t c = whist[w * BINS + bin];
+          whist[w * BINS + bin] = 0;
+          woff[w * BINS + bin] = t;
+          t += c;
+        }
+        tb[b] = t;
+        total += t;
+      }
+      incl = total;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += y;
+      }
+      if (lane == 31) smisc[warp] = incl;
+      // stash the per-thread bin totals for the second half (registers survive the barrier)
+      uint32_t run = incl - total;
+#pragma unroll
+      for (int b = 0; b < BPT; ++b) {
+        sstart[tid * BPT + b] = run;  // still lacks the preceding warps' sums
+        run += tb[b];
+      }
+    }
+    __syncthreads();
+    if (tid < SCAN_THREADS && warp > 0) {
+      uint32_t add = 0;
+      for (int w = 0; w < warp; ++w) add += smisc[w];
+#pragma unroll
+      for (int b = 0; b < BPT; ++b) sstart[tid * BPT + b] += add;
+    }
+    __syncthreads();
+
+#pragma unroll
+    for (int i = 0; i < LS_ITEMS; ++i) {
+      const uint32_t d = (uint32_t)(key[i] >> shift) & 255u;
+      const uint32_t r = ((rank2[i >> 1] >> (16 * (i & 1))) & 0xFFFFu) + myoff[d] + sstart[d];
+      skeys[r] = key[i];
+      svals[r] = val[i];
+    }
+    __syncthreads();
+    if (p + 1 < places.n) {
+#pragma unroll
+      for (int i = 0; i < LS_ITEMS; ++i) {
+        key[i] = skeys[wb + 32 * i];
+        val[i] = svals[wb + 32 * i];
+      }
+      // the next scatter comes after two more barriers: no reader is overtaken
+    }
+  }
+  for (uint32_t pos = tid; pos < cnt; pos += LS_THREADS) {
+    dst_keys[st + pos] = skeys[pos];
+    dst_vals[st + pos] = svals[pos];
+  }
+}
+
 struct SortWorkspace {
   uint64_t* norm;    // N: normalised keys in input order
   uint64_t* keys_b;  // ping-pong side B
@@ -410,8 +703,26 @@ struct SortWorkspace {
   uint32_t* active;  // NUM_PLACES (+ padding)
   uint32_t* tile_counter;  // 16
   uint32_t* status;  // ntiles * BINS
+  // MSD levels
+  Seg* big[2];             // segments of the current / next level
+  uint32_t* seg_hist;      // nbig * BINS
+  uint32_t* seg_excl;      // nbig * BINS
+  uint32_t* tile_seg;      // tile -> segment
+  uint64_t* small[LS_CLASSES];  // local-sort lists by size class
+  MsdCounters* ctr;
   uint64_t total;
 };
+
+// Bounds that size the MSD scratch: a level has at most n / (LS_CAP + 1) segments too
+// large for a local sort, each with at most ceil(count / tile) <= count / tile + 1 tiles.
+uint64_t msd_max_big(uint64_t n) { return n / (LS_CAP + 1) + 1; }
+uint64_t msd_max_tiles(uint64_t n) { return n / RS_MIN_TILE + 1 + msd_max_big(n); }
+uint64_t msd_max_small(uint64_t n, int cls) {
+  // children of one level: 256 per parent; a class of sizes > lo also has < n / lo members
+  const uint64_t by_parent = BINS * msd_max_big(n);
+  const uint64_t by_size = cls == 0 ? n : n / ls_class_cap(cls - 1);
+  return std::min<uint64_t>(by_parent, by_size) + 1;
+}
 
 SortWorkspace carve(void* base, uint64_t n) {
   SortWorkspace w;
@@ -421,7 +732,7 @@ SortWorkspace carve(void* base, uint64_t n) {
     off = xchg_align_up(off + bytes, 256);
     return (uint8_t*)base + o;
   };
-  const uint64_t ntiles = (n + RS_MIN_TILE - 1) / RS_MIN_TILE;
+  const uint64_t ntiles = msd_max_tiles(n);
   w.norm = (uint64_t*)take(n * 8);
   w.keys_b = (uint64_t*)take(n * 8);
   w.keys_a = (uint64_t*)take(n * 8);
@@ -431,6 +742,13 @@ SortWorkspace carve(void* base, uint64_t n) {
   w.active = (uint32_t*)take(64);
   w.tile_counter = (uint32_t*)take(64);
   w.status = (uint32_t*)take(ntiles * BINS * 4);
+  w.big[0] = (Seg*)take(msd_max_big(n) * sizeof(Seg));
+  w.big[1] = (Seg*)take(msd_max_big(n) * sizeof(Seg));
+  w.seg_hist = (uint32_t*)take(msd_max_big(n) * BINS * 4);
+  w.seg_excl = (uint32_t*)take(msd_max_big(n) * BINS * 4);
+  w.tile_seg = (uint32_t*)take(ntiles * 4);
+  for (int c = 0; c < LS_CLASSES; ++c) w.small[c] = (uint64_t*)take(msd_max_small(n, c) * 8);
+  w.ctr = (MsdCounters*)take(sizeof(MsdCounters));
   w.total = off;
   return w;
 }
@@ -466,13 +784,10 @@ int dispatch_normalize(const void* keys, int key_type, const uint32_t* perm, con
 
 }  // namespace
 
-// Shared with the no-workspace variants: sorts already-normalised keys.
-int xchg_internal_onesweep_pass(int mode, const uint64_t* kin, const uint32_t* vin, uint64_t* kout,
-                                uint32_t* vout, uint32_t n, int shift, const uint32_t* gexcl,
-                                uint32_t* status, uint32_t* tile_counter, const uint8_t* validity,
-                                int64_t vbit, cudaStream_t s) {
-  // CTA shape: XCHG_ONESWEEP_THREADS=256|512 and XCHG_ONESWEEP_ITEMS=8|12|16 override the
-  // defaults (read once; tuning knobs for profiling runs)
+// CTA shape of the onesweep pass: XCHG_ONESWEEP_THREADS=256|512 and
+// XCHG_ONESWEEP_ITEMS=8|12|16 override the defaults (read once; tuning knobs for
+// profiling runs).
+static void onesweep_shape(int* threads_out, int* items_out) {
   static int threads = 0, items = 0;
   if (threads == 0) {
     const char* e = getenv("XCHG_ONESWEEP_THREADS");
@@ -482,29 +797,114 @@ int xchg_internal_onesweep_pass(int mode, const uint64_t* kin, const uint32_t* v
     items = (fi == 8 || fi == 12 || fi == 16) ? fi : RS_DEFAULT_ITEMS;
     if (threads == 512) items = 16;
   }
-  static bool attr_done[2][4] = {{false, false, false, false}, {false, false, false, false}};
-#define XCHG_ONESWEEP_CASE(MODE, THREADS, ITEMS, SLOT)                                                  \
+  *threads_out = threads;
+  *items_out = items;
+}
+
+// One onesweep pass.  segs == NULL: over the whole array of n rows (mode 1 = validity
+// place).  segs != NULL: inside every segment of an MSD level, ntiles_seg tiles in all.
+static int onesweep_pass(int mode, const uint64_t* kin, const uint32_t* vin, uint64_t* kout,
+                         uint32_t* vout, uint32_t n, int shift, const uint32_t* gexcl,
+                         uint32_t* status, uint32_t* tile_counter, const uint8_t* validity,
+                         int64_t vbit, const Seg* segs, const uint32_t* tile_seg,
+                         uint32_t ntiles_seg, cudaStream_t s) {
+  int threads, items;
+  onesweep_shape(&threads, &items);
+  static bool attr_done[3][4] = {{false}};
+#define XCHG_ONESWEEP_CASE(MODE, SEG, THREADS, ITEMS, SLOT)                                             \
   {                                                                                                    \
-    if (!attr_done[MODE][SLOT]) {                                                                      \
-      XCHG_CUDA_TRY(cudaFuncSetAttribute(k_onesweep<MODE, THREADS, ITEMS>,                             \
+    constexpr int ROW = (SEG) ? 2 : MODE;                                                              \
+    if (!attr_done[ROW][SLOT]) {                                                                       \
+      XCHG_CUDA_TRY(cudaFuncSetAttribute(k_onesweep<MODE, THREADS, ITEMS, SEG>,                        \
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,                  \
                                          (int)rs_smem(THREADS, ITEMS)));                               \
-      attr_done[MODE][SLOT] = true;                                                                    \
+      attr_done[ROW][SLOT] = true;                                                                     \
     }                                                                                                  \
-    const uint32_t ntiles = (n + THREADS * ITEMS - 1) / (THREADS * ITEMS);                             \
+    const uint32_t ntiles = (SEG) ? ntiles_seg : (n + THREADS * ITEMS - 1) / (THREADS * ITEMS);        \
     XCHG_LAUNCH(XK_ONESWEEP, s,                                                                        \
-                k_onesweep<MODE, THREADS, ITEMS><<<ntiles, THREADS, rs_smem(THREADS, ITEMS), s>>>(      \
-                    kin, vin, kout, vout, n, shift, gexcl, status, tile_counter, validity, vbit));     \
+                k_onesweep<MODE, THREADS, ITEMS, SEG><<<ntiles, THREADS, rs_smem(THREADS, ITEMS), s>>>( \
+                    kin, vin, kout, vout, n, shift, gexcl, status, tile_counter, validity, vbit, segs,  \
+                    tile_seg));                                                                        \
   }
-#define XCHG_ONESWEEP_MODE(MODE)                                          \
-  if (threads == 512) XCHG_ONESWEEP_CASE(MODE, 512, 16, 0)                \
-  else if (items == 16) XCHG_ONESWEEP_CASE(MODE, 256, 16, 1)              \
-  else if (items == 12) XCHG_ONESWEEP_CASE(MODE, 256, 12, 2)              \
-  else XCHG_ONESWEEP_CASE(MODE, 256, 8, 3)
-  if (mode == 0) { XCHG_ONESWEEP_MODE(0) } else { XCHG_ONESWEEP_MODE(1) }
+#define XCHG_ONESWEEP_MODE(MODE, SEG)                                          \
+  if (threads == 512) XCHG_ONESWEEP_CASE(MODE, SEG, 512, 16, 0)                \
+  else if (items == 16) XCHG_ONESWEEP_CASE(MODE, SEG, 256, 16, 1)              \
+  else if (items == 12) XCHG_ONESWEEP_CASE(MODE, SEG, 256, 12, 2)              \
+  else XCHG_ONESWEEP_CASE(MODE, SEG, 256, 8, 3)
+  if (segs) { XCHG_ONESWEEP_MODE(0, true) }
+  else if (mode == 0) { XCHG_ONESWEEP_MODE(0, false) }
+  else { XCHG_ONESWEEP_MODE(1, false) }
 #undef XCHG_ONESWEEP_MODE
 #undef XCHG_ONESWEEP_CASE
   XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+static int seg_hist_pass(const uint64_t* keys, int shift, const Seg* segs, const uint32_t* tile_seg,
+                         uint32_t ntiles, uint32_t* seg_hist, cudaStream_t s) {
+  int threads, items;
+  onesweep_shape(&threads, &items);
+  const int tile = threads * items;
+#define XCHG_SEG_HIST(TILE)                                                                          \
+  XCHG_LAUNCH(XK_MSD_AUX, s, k_seg_hist<TILE><<<ntiles, 256, 0, s>>>(keys, shift, segs, tile_seg, seg_hist))
+  if (tile == 8192) XCHG_SEG_HIST(8192);
+  else if (tile == 4096) XCHG_SEG_HIST(4096);
+  else if (tile == 3072) XCHG_SEG_HIST(3072);
+  else XCHG_SEG_HIST(2048);
+#undef XCHG_SEG_HIST
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+// Local sorts of one level's small segments, one launch per non-empty size class.
+static int local_sort_level(const uint64_t* src_k, const uint32_t* src_v, uint64_t* dst_k, uint32_t* dst_v,
+                            uint64_t* const* small, const uint32_t* nsmall, const LocalPlaces& lp,
+                            cudaStream_t s) {
+  static bool attr_done = false;
+  static int wide2 = -1;  // XCHG_LS_WIDE2=1: 256-thread CTAs for the 2048-row class
+  if (wide2 < 0) {
+    const char* e = getenv("XCHG_LS_WIDE2");
+    wide2 = (e && atoi(e) == 1) ? 1 : 0;
+  }
+  if (!attr_done) {
+    XCHG_CUDA_TRY(cudaFuncSetAttribute(k_local_sort<128, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)ls_smem(128, 16)));
+    XCHG_CUDA_TRY(cudaFuncSetAttribute(k_local_sort<256, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)ls_smem(256, 8)));
+    XCHG_CUDA_TRY(cudaFuncSetAttribute(k_local_sort<256, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)ls_smem(256, 16)));
+    attr_done = true;
+  }
+#define XCHG_LOCAL_SORT(CLS, THREADS, ITEMS)                                                         \
+  if (nsmall[CLS])                                                                                   \
+    XCHG_LAUNCH(XK_LOCAL_SORT, s,                                                                    \
+                k_local_sort<THREADS, ITEMS><<<nsmall[CLS], THREADS, ls_smem(THREADS, ITEMS), s>>>(   \
+                    src_k, src_v, dst_k, dst_v, small[CLS], lp))
+  XCHG_LOCAL_SORT(0, 128, 4);
+  XCHG_LOCAL_SORT(1, 128, 8);
+  if (wide2) { XCHG_LOCAL_SORT(2, 256, 8); } else { XCHG_LOCAL_SORT(2, 128, 16); }
+  XCHG_LOCAL_SORT(3, 256, 16);
+#undef XCHG_LOCAL_SORT
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+// 0 = hybrid (MSD levels + local sort), 1 = every pass global (LSD).  XCHG_SORT_ALGO=lsd
+// selects 1 at load; xchg_set_sort_algorithm overrides.
+static std::atomic<int> g_sort_algo{-1};
+static int sort_algorithm() {
+  int a = g_sort_algo.load(std::memory_order_relaxed);
+  if (a < 0) {
+    const char* e = getenv("XCHG_SORT_ALGO");
+    a = (e && e[0] == 'l') ? 1 : 0;
+    g_sort_algo.store(a);
+  }
+  return a;
+}
+
+extern "C" int xchg_set_sort_algorithm(int algorithm) {
+  XCHG_REQUIRE(algorithm == 0 || algorithm == 1, "algorithm must be 0 (hybrid) or 1 (LSD)");
+  g_sort_algo.store(algorithm);
   return XCHG_OK;
 }
 
@@ -581,21 +981,82 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
       XCHG_CUDA_TRY(cudaMemcpyAsync(norm_keys_out, w.norm, n * 8, cudaMemcpyDeviceToDevice, s));
     return XCHG_OK;
   }
-  const uint64_t* kin = w.norm;
-  const uint32_t* vin = perm_in;
-  for (int j = 0; j < np; ++j) {
-    const bool to_a = ((np - 1 - j) % 2) == 0;  // the last pass lands on side A
-    uint64_t* kout = to_a ? keys_a : w.keys_b;
-    uint32_t* vout = to_a ? perm_out : w.vals_b;
-    const int p = places[j];
+  // XCHG_SORT_ALGO=lsd keeps every pass global (A/B runs); the default finishes small
+  // segments in shared memory.  With one or two places the LSD passes are already minimal.
+  if (sort_algorithm() == 1 || np <= 2) {
+    const uint64_t* kin = w.norm;
+    const uint32_t* vin = perm_in;
+    for (int j = 0; j < np; ++j) {
+      const bool to_a = ((np - 1 - j) % 2) == 0;  // the last pass lands on side A
+      uint64_t* kout = to_a ? keys_a : w.keys_b;
+      uint32_t* vout = to_a ? perm_out : w.vals_b;
+      const int p = places[j];
+      XCHG_CUDA_TRY(cudaMemsetAsync(w.tile_counter, 0, 64, s));
+      XCHG_CUDA_TRY(cudaMemsetAsync(w.status, 0, (size_t)ntiles * BINS * 4, s));
+      rc = onesweep_pass(p == KEY_PLACES ? 1 : 0, kin, vin, kout, vout, n32, 8 * p, w.gexcl + p * BINS,
+                         w.status, w.tile_counter, validity, validity_bit_offset, nullptr, nullptr, 0, s);
+      if (rc) return rc;
+      kin = kout;
+      vin = vout;
+    }
+    return XCHG_OK;
+  }
+
+  // ---- MSD levels from the top place down; level l writes side X(l), X(np-1) = A ----
+  int os_threads, os_items;
+  onesweep_shape(&os_threads, &os_items);
+  const uint32_t tile_rows = (uint32_t)(os_threads * os_items);
+  auto side_keys = [&](int l) { return ((np - 1 - l) % 2) == 0 ? keys_a : w.keys_b; };
+  auto side_vals = [&](int l) { return ((np - 1 - l) % 2) == 0 ? perm_out : w.vals_b; };
+  MsdCounters h;
+  uint32_t nbig = 1, ntiles_l = 0;
+  for (int l = 0; l < np; ++l) {
+    const int p = places[np - 1 - l];
+    const bool last = l == np - 1;
+    Seg* cur = w.big[l & 1];
+    Seg* nxt = w.big[(l + 1) & 1];
+    const uint32_t* hist;
+    const uint32_t* excl;
     XCHG_CUDA_TRY(cudaMemsetAsync(w.tile_counter, 0, 64, s));
-    XCHG_CUDA_TRY(cudaMemsetAsync(w.status, 0, (size_t)ntiles * BINS * 4, s));
-    rc = xchg_internal_onesweep_pass(p == KEY_PLACES ? 1 : 0, kin, vin, kout, vout, n32, 8 * p,
-                                     w.gexcl + p * BINS, w.status, w.tile_counter, validity,
-                                     validity_bit_offset, s);
+    if (l == 0) {
+      XCHG_CUDA_TRY(cudaMemsetAsync(w.status, 0, (size_t)((n32 + tile_rows - 1) / tile_rows) * BINS * 4, s));
+      rc = onesweep_pass(p == KEY_PLACES ? 1 : 0, w.norm, perm_in, side_keys(0), side_vals(0), n32, 8 * p,
+                         w.gexcl + p * BINS, w.status, w.tile_counter, validity, validity_bit_offset,
+                         nullptr, nullptr, 0, s);
+      if (rc) return rc;
+      hist = w.ghist + p * BINS;
+      excl = w.gexcl + p * BINS;
+    } else {
+      XCHG_LAUNCH(XK_MSD_AUX, s, k_fill_tile_map<<<nbig, 128, 0, s>>>(cur, tile_rows, w.tile_seg));
+      XCHG_CUDA_TRY(cudaMemsetAsync(w.seg_hist, 0, (size_t)nbig * BINS * 4, s));
+      XCHG_CUDA_TRY(cudaMemsetAsync(w.status, 0, (size_t)ntiles_l * BINS * 4, s));
+      rc = seg_hist_pass(side_keys(l - 1), 8 * p, cur, w.tile_seg, ntiles_l, w.seg_hist, s);
+      if (rc) return rc;
+      XCHG_LAUNCH(XK_MSD_AUX, s, k_seg_scan<<<nbig, BINS, 0, s>>>(w.seg_hist, w.seg_excl));
+      XCHG_LAUNCH_CHECK();
+      rc = onesweep_pass(0, side_keys(l - 1), side_vals(l - 1), side_keys(l), side_vals(l), 0, 8 * p,
+                         w.seg_excl, w.status, w.tile_counter, nullptr, 0, cur, w.tile_seg, ntiles_l, s);
+      if (rc) return rc;
+      hist = w.seg_hist;
+      excl = w.seg_excl;
+    }
+    if (last) break;  // every row now sits at its final position on side A
+    XCHG_CUDA_TRY(cudaMemsetAsync(w.ctr, 0, sizeof(MsdCounters), s));
+    XCHG_LAUNCH(XK_MSD_AUX, s,
+                k_msd_classify<<<nbig, BINS, 0, s>>>(l == 0 ? nullptr : cur, hist, excl, tile_rows, nxt,
+                                                     w.small[0], w.small[1], w.small[2], w.small[3], w.ctr));
+    XCHG_LAUNCH_CHECK();
+    XCHG_CUDA_TRY(cudaMemcpyAsync(&h, w.ctr, sizeof(h), cudaMemcpyDeviceToHost, s));
+    XCHG_CUDA_TRY(cudaStreamSynchronize(s));
+    // small children of this level: finish them now, by the places below this one
+    LocalPlaces lp;
+    lp.n = np - 1 - l;
+    for (int j = 0; j < lp.n; ++j) lp.shift[j] = 8 * places[j];
+    rc = local_sort_level(side_keys(l), side_vals(l), keys_a, perm_out, w.small, h.nsmall, lp, s);
     if (rc) return rc;
-    kin = kout;
-    vin = vout;
+    nbig = h.nbig;
+    ntiles_l = h.ntiles;
+    if (nbig == 0) break;
   }
   return XCHG_OK;
 }

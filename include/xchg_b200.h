@@ -65,7 +65,8 @@ int xchg_device_count(void);
  * recorded events and returns the accumulated milliseconds / launch count of one
  * kernel class (ids: 0 normalize+hist, 1 scan_hist, 2 onesweep pass, 3 row
  * gather, 4 fixed gather, 5 bitmap gather, 6 offsets scan, 7 partition bounds,
- * 8 offsets utilities, 9 misc, 10 merge, 11 shuffle, 12 aggregate). */
+ * 8 offsets utilities, 9 misc, 10 merge, 11 shuffle, 12 aggregate, 13 local
+ * (shared-memory) sort, 14 MSD level bookkeeping: segment histograms, scans, lists). */
 uint64_t xchg_launch_count(void);
 int xchg_profile_enable(int on);
 int xchg_profile_read(int kernel_id, double* total_ms, uint64_t* launches);
@@ -85,6 +86,15 @@ int xchg_set_l2_fetch_granularity(int bytes);
 int xchg_set_gather_ctas_per_sm(int ctas_per_sm);
 
 /* ---------------------------------------------------------------- sort ---- */
+
+/* Which passes of xchg_sort_column go through HBM.  0 (default): the hybrid -- passes
+ * from the top digit place down, every segment of equal higher digits finished inside
+ * shared memory as soon as it has <= 4096 rows (random 64-bit keys: 2 global passes + 1
+ * local sort instead of 8 global passes).  1: every pass global (LSD), kept for A/B
+ * measurements; the environment variable XCHG_SORT_ALGO=lsd selects it at load.  Both
+ * are stable and produce identical output.  Process wide; no counterpart in the
+ * reference (pyarrow picks its own algorithm inside sort_indices). */
+int xchg_set_sort_algorithm(int algorithm);
 
 /* Workspace bytes xchg_sort_column needs for n rows. */
 int xchg_sort_workspace_bytes(uint64_t n, uint64_t* bytes_out);
@@ -107,7 +117,8 @@ int xchg_sort_workspace_bytes(uint64_t n, uint64_t* bytes_out);
  *  norm_keys_out  optional (may be NULL): n order-preserving 64-bit radix keys in
  *              sorted order (ascending as unsigned whatever the direction);
  *              input to xchg_partition_bounds
- *  Synchronises the stream once internally (reads 9 pass-activity flags).
+ *  Synchronises the stream internally: once for the 9 pass-activity flags, and in the
+ *  hybrid once per global level after the first (segment counts; two for random keys).
  */
 int xchg_sort_column(const void* keys, int key_type, int descending,
                      const uint8_t* validity, int64_t validity_bit_offset,

@@ -680,6 +680,9 @@ class FakeLib:
     def xchg_set_gather_ctas_per_sm(self, n):
         return 0
 
+    def xchg_set_sort_algorithm(self, a):
+        return 0 if a in (0, 1) else 1
+
     # -- string keys -------------------------------------------------------------
     @staticmethod
     def _rows_bytes(off, data, n):
