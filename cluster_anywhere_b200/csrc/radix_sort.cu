@@ -466,6 +466,7 @@ __global__ void k_iota_or_copy(const uint32_t* __restrict__ in, uint32_t* __rest
 
 constexpr int LS_CLASSES = 4;
 constexpr uint32_t LS_CAP = 4096;  // largest segment a CTA sorts locally
+constexpr uint32_t LS_RUN_LIMIT = 8;  // longest out-of-order run one thread fixes by insertion
 
 struct MsdCounters {
   uint32_t nsmall[LS_CLASSES];
@@ -600,8 +601,17 @@ k_local_sort(const uint64_t* __restrict__ src_keys, const uint32_t* __restrict__
   const unsigned lt_mask = lanemask_lt();
   constexpr int BATCH = LS_ITEMS < RS_BATCH ? LS_ITEMS : RS_BATCH;
 
-  for (int p = 0; p < places.n; ++p) {
-    const int shift = places.shift[p];
+  // With three or more places left, two passes on the TOP two of them nearly finish the
+  // job: a segment has at most 4096 rows, so few rows share those 16 bits.  The rows that
+  // do form short runs, which one thread each puts in order by insertion (stable:
+  // strictly-greater moves only).  A run longer than LS_RUN_LIMIT that is out of order
+  // sends the whole segment through the plain LSD passes over every place instead
+  // (correct from any stable arrangement of the rows).
+  bool quick = places.n >= 3;
+  int step = 0, nsteps = quick ? 2 : places.n;
+  while (true) {
+  for (; step < nsteps; ++step) {
+    const int shift = quick ? places.shift[places.n - 2 + step] : places.shift[step];
     uint32_t rank2[(LS_ITEMS + 1) / 2];
 #pragma unroll
     for (int h = 0; h < LS_ITEMS; h += BATCH) {
@@ -678,7 +688,7 @@ k_local_sort(const uint64_t* __restrict__ src_keys, const uint32_t* __restrict__
       svals[r] = val[i];
     }
     __syncthreads();
-    if (p + 1 < places.n) {
+    if (step + 1 < nsteps) {
 #pragma unroll
       for (int i = 0; i < LS_ITEMS; ++i) {
         key[i] = skeys[wb + 32 * i];
@@ -686,6 +696,68 @@ k_local_sort(const uint64_t* __restrict__ src_keys, const uint32_t* __restrict__
       }
       // the next scatter comes after two more barriers: no reader is overtaken
     }
+  }
+  if (!quick) break;
+
+  // ---- runs of rows equal in the top two places: find the ones out of order ----
+  const int s2 = places.shift[places.n - 2];
+  uint32_t* fixlist = woff;  // free between the scatter and the next pass's scan
+  if (tid == 0) smisc[24] = 0;
+  __syncthreads();
+  bool bad = false;
+  for (uint32_t i = tid + 1; i < cnt; i += LS_THREADS) {
+    const uint64_t k = skeys[i], kp = skeys[i - 1];
+    if ((kp >> s2) != (k >> s2) || k >= kp) continue;
+    // (i-1, i) is an inversion inside a run: the FIRST inversion of a run owns the run
+    uint32_t ra = i - 1;
+    uint64_t prev = kp;
+    bool first = true, ok = true;
+    while (ra > 0) {
+      const uint64_t q = skeys[ra - 1];
+      if ((q >> s2) != (k >> s2)) break;
+      if (prev < q) { first = false; break; }
+      prev = q;
+      --ra;
+      if (i - ra > LS_RUN_LIMIT) { ok = false; break; }
+    }
+    if (!ok) { bad = true; continue; }
+    if (!first) continue;
+    uint32_t rb = i + 1;
+    while (rb < cnt && (skeys[rb] >> s2) == (k >> s2)) {
+      ++rb;
+      if (rb - ra > LS_RUN_LIMIT) { ok = false; break; }
+    }
+    if (!ok) { bad = true; continue; }
+    fixlist[atomicAdd(&smisc[24], 1u)] = ra | (rb << 16);
+  }
+  if (!__syncthreads_or(bad)) {
+    const uint32_t nfix = smisc[24];
+    for (uint32_t e = tid; e < nfix; e += LS_THREADS) {
+      const uint32_t ra = fixlist[e] & 0xFFFFu, rb = fixlist[e] >> 16;
+      for (uint32_t x = ra + 1; x < rb; ++x) {
+        const uint64_t kx = skeys[x];
+        const uint32_t vx = svals[x];
+        uint32_t j = x;
+        while (j > ra && skeys[j - 1] > kx) {
+          skeys[j] = skeys[j - 1];
+          svals[j] = svals[j - 1];
+          --j;
+        }
+        skeys[j] = kx;
+        svals[j] = vx;
+      }
+    }
+    __syncthreads();
+    break;
+  }
+  quick = false;
+  step = 0;
+  nsteps = places.n;
+#pragma unroll
+  for (int i = 0; i < LS_ITEMS; ++i) {
+    key[i] = skeys[wb + 32 * i];
+    val[i] = svals[wb + 32 * i];
+  }
   }
   for (uint32_t pos = tid; pos < cnt; pos += LS_THREADS) {
     dst_keys[st + pos] = skeys[pos];

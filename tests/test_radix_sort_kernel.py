@@ -90,6 +90,18 @@ def test_every_size_class_and_deep_segments():
     parts.append(np.full(30_000, 0xCD00000000000011, dtype=np.uint64))
     # duplicates-heavy segment: 50 distinct values
     parts.append(np.uint64(0xEE00000000000000) | rng.integers(0, 50, 25_000, dtype=np.uint64))
+    # local-sort corner cases (segments of <= 4096 rows with >= 3 places left):
+    # one long out-of-order run (equal in the two top remaining places) -> plain LSD passes
+    parts.append(np.uint64(0x7700000000000000) | rng.integers(0, 2**40, 3000, dtype=np.uint64))
+    # many short runs (500 distinct values of the two top remaining places, ~4 rows each)
+    parts.append(np.uint64(0x7800000000000000) | (rng.integers(0, 500, 2000, dtype=np.uint64) << np.uint64(40))
+                 | rng.integers(0, 2**40, 2000, dtype=np.uint64))
+    # runs of exactly equal keys, longer than the insertion limit, need no fixing
+    parts.append(np.uint64(0x7900000000000000) | (rng.integers(0, 20, 1500, dtype=np.uint64) << np.uint64(44)))
+    # a run of 9 (just over the limit) in reverse order
+    parts.append(np.uint64(0x7A00000000000000) | np.arange(9, 0, -1, dtype=np.uint64))
+    # and of 8 (at the limit)
+    parts.append(np.uint64(0x7B00000000000000) | np.arange(8, 0, -1, dtype=np.uint64))
     keys = np.concatenate(parts)
     rng.shuffle(keys)
     _check_u64(rt, keys)
