@@ -464,13 +464,14 @@ __global__ void k_iota_or_copy(const uint32_t* __restrict__ in, uint32_t* __rest
 // levels (65 536 segments of ~1 900 rows) and one local sort: 3 x 24 + 8 B per row.
 // Every pass is stable, so the result is identical to the LSD sort's.
 
-constexpr int LS_CLASSES = 4;
-constexpr uint32_t LS_CAP = 4096;  // largest segment a CTA sorts locally
+constexpr int LS_CLASSES = 5;
+constexpr uint32_t LS_CAP = 8192;  // largest segment a CTA sorts locally
+constexpr uint32_t LS_GROUP_MEMBER_MAX = 512;  // children below this size are packed into shared jobs
 constexpr uint32_t LS_RUN_LIMIT = 8;  // longest out-of-order run one thread fixes by insertion
 
 struct MsdCounters {
   uint32_t nsmall[LS_CLASSES];
-  uint32_t nbig, ntiles, pad0, pad1;
+  uint32_t nbig, ntiles, pad0;
 };
 
 __host__ __device__ constexpr uint32_t ls_class_cap(int c) { return 512u << c; }
@@ -513,29 +514,97 @@ k_seg_scan(const uint32_t* __restrict__ seg_hist, uint32_t* __restrict__ seg_exc
   seg_excl[(size_t)blockIdx.x * BINS + tid] = base + x - c;
 }
 
-// Children of a level (one thread per parent segment and digit): small ones go to the
-// local-sort list of their size class, the others become the next level's segments and
-// claim their tiles.  parents == NULL: the single top-level segment [0, n).
-__global__ void __launch_bounds__(BINS)
-k_msd_classify(const Seg* __restrict__ parents, const uint32_t* __restrict__ hist,
-               const uint32_t* __restrict__ excl, uint32_t tile_rows, Seg* __restrict__ big_next,
-               uint64_t* __restrict__ small0, uint64_t* __restrict__ small1,
-               uint64_t* __restrict__ small2, uint64_t* __restrict__ small3,
-               MsdCounters* __restrict__ ctr) {
-  const size_t e = (size_t)blockIdx.x * BINS + threadIdx.x;
-  const uint32_t c = hist[e];
-  if (c == 0) return;
-  const uint32_t st = (parents ? parents[blockIdx.x].start : 0u) + excl[e];
-  if (c <= LS_CAP) {
-    const int cls = c <= ls_class_cap(0) ? 0 : (c <= ls_class_cap(1) ? 1 : (c <= ls_class_cap(2) ? 2 : 3));
-    uint64_t* list = cls == 0 ? small0 : (cls == 1 ? small1 : (cls == 2 ? small2 : small3));
-    const uint32_t idx = atomicAdd(&ctr->nsmall[cls], 1u);
-    list[idx] = (uint64_t)st | ((uint64_t)c << 32);
-  } else {
-    const uint32_t idx = atomicAdd(&ctr->nbig, 1u);
-    const uint32_t nt = (c + tile_rows - 1) / tile_rows;
-    const uint32_t tb = atomicAdd(&ctr->ntiles, nt);
-    big_next[idx] = Seg{st, c, tb, 0u};
+// Local-sort job: rows [start, start + count); GROUP set = the rows are several sibling
+// children (consecutive digits of this level's place), so the sort also covers that place.
+constexpr uint64_t LS_JOB_GROUP = 1ull << 48;
+__device__ __forceinline__ uint64_t ls_job(uint32_t start, uint32_t count, bool group) {
+  return (uint64_t)start | ((uint64_t)count << 32) | (group ? LS_JOB_GROUP : 0ull);
+}
+
+// Children of a level, one thread per parent segment walking its 256 digit counts:
+// a child too large for a local sort becomes a segment of the next level and claims its
+// tiles; consecutive children of fewer than LS_GROUP_MEMBER_MAX rows are packed greedily
+// into local-sort jobs of at most LS_CAP rows (so a parent just above LS_CAP does not
+// turn into 256 jobs of a few rows each); the others are jobs of their own.  can_group = 0 (validity place: no key digit tells the children apart)
+// keeps every child a job of its own.  parents == NULL: the top-level segment [0, n).
+struct SmallLists {
+  uint64_t* p[LS_CLASSES];
+};
+
+__global__ void __launch_bounds__(32)
+k_msd_classify(const Seg* __restrict__ parents, uint32_t nparents, const uint32_t* __restrict__ hist,
+               const uint32_t* __restrict__ excl, uint32_t tile_rows, int can_group,
+               Seg* __restrict__ big_next, SmallLists lists, MsdCounters* __restrict__ ctr) {
+  // one warp per parent: the lanes stage its counts and offsets in shared memory, lane 0
+  // walks them
+  __shared__ uint32_t h[BINS], x[BINS];
+  const uint32_t j = blockIdx.x;
+  for (int d = threadIdx.x; d < BINS; d += 32) {
+    h[d] = hist[(size_t)j * BINS + d];
+    x[d] = excl[(size_t)j * BINS + d];
+  }
+  __syncwarp();
+  if (threadIdx.x != 0) return;
+  const uint32_t base = parents ? parents[j].start : 0u;
+  auto cls_of = [](uint32_t c) {
+    int k = 0;
+    while (c > ls_class_cap(k)) ++k;
+    return k;
+  };
+  // two walks over the digit counts: count the jobs / segments / tiles this parent
+  // produces, reserve list space with one atomic per list, then write the entries
+  uint32_t njob[LS_CLASSES] = {0}, nb = 0, nt = 0;
+  uint32_t ojob[LS_CLASSES] = {0}, ob = 0, ot = 0;
+  for (int pass = 0; pass < 2; ++pass) {
+    uint32_t gstart = 0, gcount = 0, gmembers = 0;
+    auto emit = [&](uint32_t st, uint32_t c, bool group) {
+      const int cls = cls_of(c);
+      if (pass == 0) {
+        ++njob[cls];
+      } else {
+        lists.p[cls][ojob[cls]++] = ls_job(st, c, group);
+      }
+    };
+    for (int d = 0; d < BINS; ++d) {
+      const uint32_t c = h[d];
+      if (c == 0) continue;
+      const uint32_t st = base + x[d];
+      const bool big = c > LS_CAP;
+      const bool alone = !can_group || c >= LS_GROUP_MEMBER_MAX;  // large enough for a job of its own
+      if (gmembers && (big || alone || gcount + c > LS_CAP)) {
+        emit(gstart, gcount, gmembers > 1);
+        gmembers = 0;
+      }
+      if (big) {
+        const uint32_t tiles = (c + tile_rows - 1) / tile_rows;
+        if (pass == 0) {
+          ++nb;
+          nt += tiles;
+        } else {
+          big_next[ob++] = Seg{st, c, ot, 0u};
+          ot += tiles;
+        }
+      } else if (alone) {
+        emit(st, c, false);
+      } else if (gmembers == 0) {
+        gstart = st;
+        gcount = c;
+        gmembers = 1;
+      } else {
+        gcount += c;
+        ++gmembers;
+      }
+    }
+    if (gmembers) emit(gstart, gcount, gmembers > 1);
+    if (pass == 0) {
+#pragma unroll
+      for (int c = 0; c < LS_CLASSES; ++c)
+        if (njob[c]) ojob[c] = atomicAdd(&ctr->nsmall[c], njob[c]);
+      if (nb) {
+        ob = atomicAdd(&ctr->nbig, nb);
+        ot = atomicAdd(&ctr->ntiles, nt);
+      }
+    }
   }
 }
 
@@ -547,8 +616,8 @@ k_fill_tile_map(const Seg* __restrict__ segs, uint32_t tile_rows, uint32_t* __re
 }
 
 struct LocalPlaces {
-  int n;
-  int shift[KEY_PLACES];
+  int n;                      // places below the level that produced the jobs
+  int shift[KEY_PLACES + 1];  // their shifts, ascending; shift[n] = that level's own place
 };
 
 constexpr size_t ls_smem(int threads, int items) {
@@ -556,7 +625,7 @@ constexpr size_t ls_smem(int threads, int items) {
 }
 constexpr int ls_min_blocks(int threads, int items) {
   // registers: 3 per item + ranks + ~28; shared memory: 12 B per row + counters
-  return items >= 16 ? (threads >= 256 ? 2 : 4) : (threads >= 256 ? 4 : 8);
+  return items >= 16 ? (threads >= 512 ? 1 : (threads >= 256 ? 2 : 4)) : (threads >= 256 ? 4 : 8);
 }
 
 // One CTA per small segment: load it, LSD-sort it by the remaining (lower) places in
@@ -581,7 +650,8 @@ k_local_sort(const uint64_t* __restrict__ src_keys, const uint32_t* __restrict__
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint64_t ent = small[blockIdx.x];
-  const uint32_t st = (uint32_t)ent, cnt = (uint32_t)(ent >> 32);
+  const uint32_t st = (uint32_t)ent, cnt = (uint32_t)(ent >> 32) & 0xFFFFu;
+  const int nplaces = places.n + ((ent & LS_JOB_GROUP) ? 1 : 0);  // a group also sorts by shift[n]
   const uint32_t wb = warp * (32 * LS_ITEMS) + lane;
 
   for (int j = tid; j < WARPS * BINS; j += LS_THREADS) whist[j] = 0;
@@ -601,17 +671,19 @@ k_local_sort(const uint64_t* __restrict__ src_keys, const uint32_t* __restrict__
   const unsigned lt_mask = lanemask_lt();
   constexpr int BATCH = LS_ITEMS < RS_BATCH ? LS_ITEMS : RS_BATCH;
 
-  // With three or more places left, two passes on the TOP two of them nearly finish the
+  // With more than two places left, two passes on the TOP two of them nearly finish the
   // job: a segment has at most 4096 rows, so few rows share those 16 bits.  The rows that
   // do form short runs, which one thread each puts in order by insertion (stable:
   // strictly-greater moves only).  A run longer than LS_RUN_LIMIT that is out of order
   // sends the whole segment through the plain LSD passes over every place instead
   // (correct from any stable arrangement of the rows).
-  bool quick = places.n >= 3;
-  int step = 0, nsteps = quick ? 2 : places.n;
+  // (a group adds its own place as a third pass: its rows differ there by construction)
+  const int qsteps = (ent & LS_JOB_GROUP) ? 3 : 2;
+  bool quick = nplaces > qsteps;
+  int step = 0, nsteps = quick ? qsteps : nplaces;
   while (true) {
   for (; step < nsteps; ++step) {
-    const int shift = quick ? places.shift[places.n - 2 + step] : places.shift[step];
+    const int shift = quick ? places.shift[nplaces - qsteps + step] : places.shift[step];
     uint32_t rank2[(LS_ITEMS + 1) / 2];
 #pragma unroll
     for (int h = 0; h < LS_ITEMS; h += BATCH) {
@@ -700,7 +772,7 @@ k_local_sort(const uint64_t* __restrict__ src_keys, const uint32_t* __restrict__
   if (!quick) break;
 
   // ---- runs of rows equal in the top two places: find the ones out of order ----
-  const int s2 = places.shift[places.n - 2];
+  const int s2 = places.shift[nplaces - qsteps];
   uint32_t* fixlist = woff;  // free between the scatter and the next pass's scan
   if (tid == 0) smisc[24] = 0;
   __syncthreads();
@@ -752,7 +824,7 @@ k_local_sort(const uint64_t* __restrict__ src_keys, const uint32_t* __restrict__
   }
   quick = false;
   step = 0;
-  nsteps = places.n;
+  nsteps = nplaces;
 #pragma unroll
   for (int i = 0; i < LS_ITEMS; ++i) {
     key[i] = skeys[wb + 32 * i];
@@ -945,6 +1017,8 @@ static int local_sort_level(const uint64_t* src_k, const uint32_t* src_v, uint64
                                        (int)ls_smem(256, 8)));
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_local_sort<256, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)ls_smem(256, 16)));
+    XCHG_CUDA_TRY(cudaFuncSetAttribute(k_local_sort<512, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)ls_smem(512, 16)));
     attr_done = true;
   }
 #define XCHG_LOCAL_SORT(CLS, THREADS, ITEMS)                                                         \
@@ -956,6 +1030,7 @@ static int local_sort_level(const uint64_t* src_k, const uint32_t* src_v, uint64
   XCHG_LOCAL_SORT(1, 128, 8);
   if (wide2) { XCHG_LOCAL_SORT(2, 256, 8); } else { XCHG_LOCAL_SORT(2, 128, 16); }
   XCHG_LOCAL_SORT(3, 256, 16);
+  XCHG_LOCAL_SORT(4, 512, 16);
 #undef XCHG_LOCAL_SORT
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
@@ -1114,9 +1189,12 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
     }
     if (last) break;  // every row now sits at its final position on side A
     XCHG_CUDA_TRY(cudaMemsetAsync(w.ctr, 0, sizeof(MsdCounters), s));
+    const int can_group = p != KEY_PLACES;
+    SmallLists lists;
+    for (int c = 0; c < LS_CLASSES; ++c) lists.p[c] = w.small[c];
     XCHG_LAUNCH(XK_MSD_AUX, s,
-                k_msd_classify<<<nbig, BINS, 0, s>>>(l == 0 ? nullptr : cur, hist, excl, tile_rows, nxt,
-                                                     w.small[0], w.small[1], w.small[2], w.small[3], w.ctr));
+                k_msd_classify<<<nbig, 32, 0, s>>>(l == 0 ? nullptr : cur, nbig, hist, excl, tile_rows, can_group,
+                                                   nxt, lists, w.ctr));
     XCHG_LAUNCH_CHECK();
     XCHG_CUDA_TRY(cudaMemcpyAsync(&h, w.ctr, sizeof(h), cudaMemcpyDeviceToHost, s));
     XCHG_CUDA_TRY(cudaStreamSynchronize(s));
@@ -1124,6 +1202,7 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
     LocalPlaces lp;
     lp.n = np - 1 - l;
     for (int j = 0; j < lp.n; ++j) lp.shift[j] = 8 * places[j];
+    lp.shift[lp.n] = can_group ? 8 * p : 0;
     rc = local_sort_level(side_keys(l), side_vals(l), keys_a, perm_out, w.small, h.nsmall, lp, s);
     if (rc) return rc;
     nbig = h.nbig;

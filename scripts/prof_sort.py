@@ -23,7 +23,7 @@ def main():
     n = args.rows
     g = torch.Generator(device=rt.device)
     g.manual_seed(2)
-    keys = torch.randint(0, 2**args.bits - 1, (n,), dtype=torch.int64, device=rt.device, generator=g)
+    keys = torch.randint(0, min(2**args.bits, 2**63) - 1, (n,), dtype=torch.int64, device=rt.device, generator=g)
     ws_bytes = dev.sort_workspace_bytes(n)
     ws = rt.empty(ws_bytes)
     perm = rt.empty(n, torch.int32)
@@ -36,6 +36,21 @@ def main():
         e1.record()
         torch.cuda.synchronize()
         print(f"rep {r}: {e0.elapsed_time(e1):.3f} ms", flush=True)
+    import ctypes
+    lib = _cabi.load()
+    lib.xchg_profile_enable(1)
+    rt.call("xchg_sort_column", dev._vp(keys), _cabi.I64, 0, None, 0, None, n, dev._vp(perm), dev._vp(norm),
+            dev._vp(ws), ws_bytes, rt.stream, launches=0)
+    torch.cuda.synchronize()
+    names = {0: "normalize_hist", 1: "scan_hist", 2: "onesweep", 9: "misc", 13: "local_sort", 14: "msd_aux"}
+    out = []
+    for kid, name in names.items():
+        tot, cnt = ctypes.c_double(), ctypes.c_uint64()
+        lib.xchg_profile_read(kid, ctypes.byref(tot), ctypes.byref(cnt))
+        if cnt.value:
+            out.append(f"{name} x{cnt.value} {tot.value:.3f} ms")
+    lib.xchg_profile_enable(0)
+    print("  " + ", ".join(out), flush=True)
     s = norm[:: max(1, n // 1000)]
     assert bool((s[1:] >= s[:-1]).all())
 

@@ -62,6 +62,17 @@ def test_uniform_random_two_global_levels():
     _check_u64(rt, keys)
 
 
+def test_parents_just_above_the_local_capacity_group_their_children():
+    """256 segments of ~11 700 rows (just above the 8192-row local capacity): each splits
+    into 256 children of ~46 rows, which must be packed into a few local-sort jobs, not
+    sorted one CTA each."""
+    rt = dev.default_runtime()
+    rng = np.random.default_rng(3)
+    n = 3_000_000
+    keys = (rng.integers(0, 256, n, dtype=np.uint64) << np.uint64(56)) | rng.integers(0, 2**48, n, dtype=np.uint64)
+    _check_u64(rt, keys)
+
+
 @pytest.mark.parametrize("places", [3, 4, 5, 8])
 def test_active_places(places):
     rt = dev.default_runtime()
@@ -80,7 +91,7 @@ def test_every_size_class_and_deep_segments():
     parts = []
     # top byte t selects a child of the first level with a chosen size
     for t, size in enumerate([1, 37, 300, 512, 513, 800, 1024, 1025, 1500, 2048, 2049, 3000, 4096, 4097,
-                              5000, 9000, 70_000]):
+                              5000, 8192, 8193, 9000, 70_000]):
         low = rng.integers(0, 2**56, size, dtype=np.uint64)
         parts.append((np.uint64(t) << np.uint64(56)) | low)
     # a segment whose rows agree in the top FIVE places: stays large for five levels
