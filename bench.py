@@ -29,9 +29,9 @@ import tempfile
 import threading
 import time
 
-# receive-side buffer sizes change from step to step (sampled splitters): let the
-# caching allocator grow segments instead of cudaMalloc-ing a new block per size
-os.environ.setdefault("PYTORCH_CUDA_ALLOC_CONF", "expandable_segments:True")
+# (no expandable_segments: with it the allocator re-mapped the ~12 GB output buffer on some
+# ranks every step, ~1 ms per GB of host stall, and the 8-GPU step waited for those ranks;
+# Runtime.empty rounds large buffers to sticky size classes instead)
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
@@ -380,6 +380,10 @@ def run_b200(args):
         del out
     barrier()
     ex.phase_ms = {}
+    ex.timeline_ms = {}
+    ex.gpu_marks = []
+    import resource as _resource
+    ru0 = _resource.getrusage(_resource.RUSAGE_SELF)
     if args.trace:
         from cluster_anywhere_b200.exchange import collective as coll
 
@@ -392,10 +396,15 @@ def run_b200(args):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     ev0.record()
+    alloc_log = []
     for i in range(args.steps):
         out = one_step(100 + i)
         if i < args.steps - 1:
             del out
+        if getattr(ex, "timeline", False):
+            st = torch.cuda.memory_stats()
+            alloc_log.append((st.get("num_device_alloc", 0), st.get("num_device_free", 0),
+                              round(torch.cuda.memory_reserved() / 1e9, 2)))
     ev1.record()
     barrier()
     launches = lib.xchg_launch_count() - launches0
@@ -507,6 +516,19 @@ def run_b200(args):
                "sample": sample, "gb_per_s": ref.total_rows / t_cpu * 2 * ROW_BYTES / 1e9,
                "primitives_only_value": ref.total_rows / t_prim}
 
+    if getattr(ex, "timeline", False):
+        torch.cuda.synchronize()
+        ru1 = _resource.getrusage(_resource.RUSAGE_SELF)
+        print(f"[host rank {rank}] cpus={len(os.sched_getaffinity(0))} loadavg={os.getloadavg()} "
+              f"utime={ru1.ru_utime - ru0.ru_utime:.3f}s stime={ru1.ru_stime - ru0.ru_stime:.3f}s "
+              f"vol_cs={ru1.ru_nvcsw - ru0.ru_nvcsw} invol_cs={ru1.ru_nivcsw - ru0.ru_nivcsw}",
+              file=sys.stderr, flush=True)
+        print(f"[alloc rank {rank}] (device allocs, device frees, reserved GB) after each timed step: {alloc_log}",
+              file=sys.stderr, flush=True)
+        print(f"[gpu timeline rank {rank}] mean ms from step begin (timed steps + e2e steps): "
+              + json.dumps(ex.gpu_timeline()), file=sys.stderr, flush=True)
+        print(f"[timeline rank {rank}] host ms between stamps, summed over the timed steps (+ e2e steps if run): "
+              + json.dumps({k: round(v, 2) for k, v in ex.timeline_ms.items()}), file=sys.stderr, flush=True)
     if args.trace:
         print(f"[trace rank {rank}] phase ms over the {args.steps} timed steps (e2e.*: over warm-up + e2e steps): "
               + json.dumps({k: round(v, 2) for k, v in ex.phase_ms.items()}), file=sys.stderr, flush=True)

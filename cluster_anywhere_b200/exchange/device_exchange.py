@@ -58,6 +58,49 @@ class DeviceExchange:
         self.trace = trace
         self.phase_ms = {}
         self._t_last = None
+        # XCHG_TIMELINE=1: host wall-clock between stamps WITHOUT synchronising (shows
+        # where the host thread blocks: collectives, .tolist() / .cpu() read-backs)
+        self.timeline = os.environ.get("XCHG_TIMELINE", "0") == "1"
+        self.timeline_ms = {}
+        self._tl_last = None
+
+    def _gpu_mark(self, name: str):
+        """XCHG_TIMELINE=1: record a CUDA event on the current stream (no sync); bench.py
+        turns the events of a step into offsets from the step's first mark."""
+        if not self.timeline or not self.rt.is_cuda:
+            return
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record(torch.cuda.current_stream(self.rt.device))
+        if not hasattr(self, "gpu_marks"):
+            self.gpu_marks = []
+        self.gpu_marks.append((name, ev))
+
+    def gpu_timeline(self) -> dict:
+        """Mean offset (ms) of every mark from the preceding 'step_begin' mark."""
+        marks = getattr(self, "gpu_marks", [])
+        if not marks:
+            return {}
+        torch.cuda.synchronize()
+        acc, cnt, t0 = {}, {}, None
+        for name, ev in marks:
+            if name == "step_begin":
+                t0 = ev
+                continue
+            if t0 is None:
+                continue
+            acc[name] = acc.get(name, 0.0) + t0.elapsed_time(ev)
+            cnt[name] = cnt.get(name, 0) + 1
+        return {k: round(acc[k] / cnt[k], 2) for k in acc}
+
+    def _stamp(self, name: Optional[str]):
+        if not self.timeline:
+            return
+        import time
+
+        now = time.perf_counter()
+        if name is not None and self._tl_last is not None:
+            self.timeline_ms[name] = self.timeline_ms.get(name, 0.0) + (now - self._tl_last) * 1e3
+        self._tl_last = now
 
     def _take_and_exchange(self, table, perm, send_counts, group):
         """K5 + exchange.  On a GPU the gather kernels store straight into the
@@ -180,12 +223,19 @@ class DeviceExchange:
         if boundaries is None:
             boundaries = self.sample_boundaries(ds, sort_key, r, seed) if r > 1 else []
         n = ds.num_rows
+        self._stamp("tl.sort_prologue")
         perm, norms = dev.sort_permutation(rt, ds.table, sort_key.get_columns(),
                                            sort_key.get_descending(), want_norm=len(boundaries) > 0)
+        self._stamp("tl.sort_permutation")
+        self._gpu_mark("g.keys_sorted")
         string_key = any(dev.is_string_key(ds.table.column(c)) for c in sort_key.get_columns())
         cuts = cuts_for(rt, ds.table, norms, boundaries, sort_key) if (boundaries and not string_key) else []
+        self._stamp("tl.cuts")
         table = ds.table if _complete is None else _complete()  # payload columns may arrive late
+        self._stamp("tl.complete")
         out = dev.take_table(rt, table, perm, n, _presorted(sort_key, norms))
+        self._stamp("tl.take_launch")
+        self._gpu_mark("g.taken")
         if boundaries and string_key:  # string keys are searched on the sorted column itself
             cuts = cuts_for(rt, ds.table, norms, boundaries, sort_key, out)
         ranges, last = [], 0
@@ -237,9 +287,13 @@ class DeviceExchange:
             return self.sort(ds, sort_key, boundaries=boundaries, seed=seed)
         rt = self.rt
         self._phase(None)
+        self._stamp(None)
+        self._gpu_mark("step_begin")
         schema = None if ds.table is None else ds.table.schema
-        info = coll.all_gather_object((ds.num_blocks, ds.num_rows, schema), group)
+        info = coll.gather_dataset_info(rt, ds.num_blocks, ds.num_rows, schema, group)
+        self._gpu_mark("g.info_gathered")
         self._phase("dist.gather_info")
+        self._stamp("tl.gather_info")
         blocks_per_rank = [i[0] for i in info]
         total_rows = sum(i[1] for i in info)
         schema = next((i[2] for i in info if i[2] is not None), None)
@@ -262,7 +316,10 @@ class DeviceExchange:
             first_block = int(sum(blocks_per_rank[:rank]))
             m = max(1, sum(blocks_per_rank))
             mine = self.sample_keys(ds, sort_key, int(r_total * 10 / m), seed, first_block)
+            self._stamp("tl.sample_keys")
             samples = [t for part in coll.all_gather_object(mine, group) for t in part]
+            self._stamp("tl.gather_samples")
+            self._gpu_mark("g.samples_gathered")
             boundaries = (SortTaskSpec.boundaries_from_samples(samples, sort_key, r_total)
                           if r_total > 1 else [])
         self._phase("dist.sample_boundaries")
@@ -284,6 +341,8 @@ class DeviceExchange:
             for d, cnt in enumerate(counts.tolist()):
                 send_counts[owners[d]] = int(cnt)
             self._phase("dist.assign_and_order")
+            self._stamp("tl.assign_and_order")
+            self._gpu_mark("g.assigned")
         lo_b, hi_b = int(ob[rank]), int(ob[rank + 1])
         local_bounds = list(boundaries[lo_b:max(lo_b, hi_b - 1)])
         from . import peer
@@ -324,24 +383,53 @@ class DeviceExchange:
 
         rt = self.rt
         pl = peer.plan_exchange(rt, self, table, perm, send_counts, group)
+        self._stamp("tl.plan_exchange")
         names = list(table.names)
         key_idx = [names.index(c) for c in sort_key.get_columns()]
         rest_idx = [j for j in range(len(names)) if j not in key_idx]
         main = torch.cuda.current_stream(rt.device)
         if getattr(self, "_side_stream", None) is None:
-            self._side_stream = torch.cuda.Stream(device=rt.device)
+            # XCHG_SIDE_PRIORITY=1 gives the payload stores a high-priority stream; measured
+            # at 8 GPUs it only moves the wait from the stores to the key sort (42.4 vs
+            # 41.0 ms per step), so the default stays at equal priority
+            prio = -1 if os.environ.get("XCHG_SIDE_PRIORITY", "0") == "1" else 0
+            self._side_stream = torch.cuda.Stream(device=rt.device, priority=prio)
         side = self._side_stream
 
+        self._gpu_mark("g.planned")
+
+        def payload_stores():
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                rt.call("xchg_set_gather_ctas_per_sm", int(os.environ.get("XCHG_SIDE_CTAS_PER_SM", "2")), launches=0)
+                try:
+                    peer.store_columns(rt, pl, rest_idx)
+                finally:
+                    rt.call("xchg_set_gather_ctas_per_sm", 0, launches=0)
+                self._gpu_mark("g.side_payload_stored")
+
+        def payload_fence():
+            with torch.cuda.stream(side):
+                peer.fence(rt, group)
+                self._gpu_mark("g.side_payload_fenced")
+
+        # Keys first, then the payload (92 % of the bytes) on the side stream while the
+        # received keys are sorted.  XCHG_PAYLOAD_FIRST=1 queues the payload stores before
+        # the key columns instead (measured at 8 GPUs: 43.8 vs 41.0 ms per step -- the keys
+        # then share the links and the sort starts later).  The two fences are collectives
+        # of one communicator and complete in issue order, so the key fence is always issued
+        # BEFORE the payload fence (else the key sort would wait for the payload).
+        payload_first = os.environ.get("XCHG_PAYLOAD_FIRST", "0") == "1"
+        if payload_first:
+            payload_stores()
         peer.store_columns(rt, pl, key_idx)
+        self._gpu_mark("g.keys_stored")
         peer.fence(rt, group)
-        side.wait_stream(main)
-        with torch.cuda.stream(side):
-            rt.call("xchg_set_gather_ctas_per_sm", int(os.environ.get("XCHG_SIDE_CTAS_PER_SM", "2")), launches=0)
-            try:
-                peer.store_columns(rt, pl, rest_idx)
-            finally:
-                rt.call("xchg_set_gather_ctas_per_sm", 0, launches=0)
-            peer.fence(rt, group)
+        self._gpu_mark("g.keys_fenced")
+        if not payload_first:
+            payload_stores()
+        payload_fence()
+        self._stamp("tl.launch_stores")
 
         m = int(pl.recv_rows[pl.rank])
         if my_blocks == 0 or m == 0:
@@ -358,8 +446,10 @@ class DeviceExchange:
             by_idx.update(zip(rest_idx, rest_cols))
             return dev.DeviceTable(names, [by_idx[j] for j in range(len(names))], m, table.schema)
 
-        return self.sort(DeviceDataset(keys_table, [(0, m)]), sort_key, boundaries=local_bounds,
-                         _complete=complete)
+        out = self.sort(DeviceDataset(keys_table, [(0, m)]), sort_key, boundaries=local_bounds,
+                        _complete=complete)
+        self._stamp("tl.reduce_sort_launch")
+        return out
 
     def sort_blocks_distributed(self, blocks: Sequence[pa.Table], sort_key: SortKey,
                                 boundaries: Optional[list] = None, seed: int = 0,
@@ -398,7 +488,7 @@ class DeviceExchange:
         if G == 1 and not force_exchange:
             info = [(ds.num_blocks, ds.num_rows, schema)]
         else:
-            info = coll.all_gather_object((ds.num_blocks, ds.num_rows, schema), group)
+            info = coll.gather_dataset_info(rt, ds.num_blocks, ds.num_rows, schema, group)
         n_total = sum(i[1] for i in info)
         r_total = max(1, num_outputs if num_outputs is not None else sum(i[0] for i in info))
         schema = next((i[2] for i in info if i[2] is not None), None)
@@ -480,7 +570,7 @@ class DeviceExchange:
         dist_path = G > 1 or force_exchange
         agg.check_aggs(aggs)
         schema = None if ds.table is None else ds.table.schema
-        info = (coll.all_gather_object((ds.num_blocks, ds.num_rows, schema), group) if dist_path
+        info = (coll.gather_dataset_info(rt, ds.num_blocks, ds.num_rows, schema, group) if dist_path
                 else [(ds.num_blocks, ds.num_rows, schema)])
         blocks_per_rank = [i[0] for i in info]
         total_rows = sum(i[1] for i in info)
