@@ -45,8 +45,12 @@ _SIGNATURES = {
                                  ctypes.POINTER(c_uint64), _P]),
     "xchg_group_ids": (c_int, [_P, _P, c_uint64, _P, c_uint64, c_uint64, _P, _P, _P]),
     "xchg_agg_stats_init": (c_int, [_P, _P, c_uint64, _P]),
-    "xchg_agg_count_rows": (c_int, [_P, c_uint64, _P, _P]),
-    "xchg_agg_accumulate": (c_int, [_P, _P, c_int, _P, c_int64, c_uint64, c_uint64, _P, c_int, _P]),
+    "xchg_key_minmax": (c_int, [_P, _P, c_int64, c_uint64, _P, ctypes.POINTER(c_uint64), _P]),
+    "xchg_dense_groups_bytes": (c_int, [c_uint64, ctypes.POINTER(c_uint64)]),
+    "xchg_dense_groups": (c_int, [_P, _P, c_int64, c_uint64, c_uint64, c_uint64, _P, c_uint64, _P, _P,
+                                  ctypes.POINTER(c_uint64), _P]),
+    "xchg_agg_count_rows": (c_int, [_P, c_uint64, c_uint64, _P, _P]),
+    "xchg_agg_accumulate": (c_int, [_P, _P, c_int, _P, c_int64, c_uint64, c_uint64, _P, c_int, _P, _P]),
     "xchg_agg_accumulate_m2": (c_int, [_P, _P, c_int, _P, c_int64, c_uint64, c_uint64, _P, _P, _P]),
     "xchg_agg_merge_rows": (c_int, [_P, _P, c_uint64, _P, _P]),
     "xchg_agg_merge_states": (c_int, [_P, _P, c_uint64, c_int, c_uint64, _P, _P, _P]),

@@ -20,6 +20,7 @@ column's type travels in the field metadata.
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import numpy as np
@@ -172,6 +173,8 @@ def _next_pow2(x: int) -> int:
     return p
 
 
+DENSE_MAX_RANGE = 1 << 28  # XCHG_DENSE_MAX_RANGE
+
 _KEY_RANGE = {_cabi.I8: 1 << 8, _cabi.U8: 1 << 8, _cabi.I16: 1 << 16, _cabi.U16: 1 << 16}
 
 
@@ -189,6 +192,25 @@ def group_rows(rt: dev.Runtime, key_col: DeviceColumn, n: int):
     norm = rt.empty(n, torch.int64)
     rt.call("xchg_normalize_keys", _vp(key_col.data), kt, 0, _vp(key_col.validity), 0, None, n,
             _vp(norm), rt.stream)
+    if _is_int_type(kt) and os.environ.get("XCHG_DENSE_GROUPS", "1") != "0":
+        # integer keys over a small range: direct addressing instead of a hash table
+        scratch = rt.zeros(32)
+        mm = (ctypes.c_uint64 * 3)()
+        rt.call("xchg_key_minmax", _vp(norm), _vp(key_col.validity), 0, n, _vp(scratch), mm, rt.stream)
+        kmin, kmax, nvalid = int(mm[0]), int(mm[1]), int(mm[2])
+        rng = (kmax - kmin + 1) if nvalid else 1
+        if rng <= min(DENSE_MAX_RANGE, max(1 << 20, 4 * n)):
+            kmin = kmin if nvalid else 0
+            wsb = ctypes.c_uint64()
+            _cabi.check(_cabi.load().xchg_dense_groups_bytes(rng, ctypes.byref(wsb)))
+            ws = rt.empty(wsb.value)
+            rgid = rt.empty(n, torch.int32)
+            gkeys = rt.empty(min(rng, n) + 2, torch.int64)
+            g_out = ctypes.c_uint64()
+            rt.call("xchg_dense_groups", _vp(norm), _vp(key_col.validity), 0, n, kmin, rng, _vp(ws), wsb.value,
+                    _vp(rgid), _vp(gkeys), ctypes.byref(g_out), rt.stream, launches=5)
+            g = int(g_out.value)
+            return rgid, gkeys[:g], g, kt
     cap = max(64, _next_pow2(2 * min(n, _KEY_RANGE.get(kt, n))))
     ws_bytes = ctypes.c_uint64()
     _cabi.check(_cabi.load().xchg_hash_table_bytes(cap, ctypes.byref(ws_bytes)))
@@ -264,7 +286,7 @@ def aggregate_table(rt: dev.Runtime, table: DeviceTable, key: Optional[str],
     if partial_in:
         rt.call("xchg_agg_merge_rows", _vp(rgid), _vp(table.column(ROWS_COL).data), n, _vp(rows), rt.stream)
     else:
-        rt.call("xchg_agg_count_rows", _vp(rgid), n, _vp(rows), rt.stream)
+        rt.call("xchg_agg_count_rows", _vp(rgid), n, g, _vp(rows), rt.stream)
 
     # one statistics block per distinct value column
     value_cols = list(dict.fromkeys(a.on for a in aggs if a.kind != KIND_COUNT))
@@ -285,8 +307,11 @@ def aggregate_table(rt: dev.Runtime, table: DeviceTable, key: Optional[str],
             if vc.kind != "fixed":
                 raise NotImplementedError(f"aggregate on column {name!r} of type {vc.type} is not supported")
             vt = dev.key_type_of(vc.type)
+            # min / max / NaN counts only where something reads them: Min, Max, or a partial
+            # row (whose consumer is unknown here)
+            want_minmax = int((not finalize) or any(a.kind in (KIND_MIN, KIND_MAX) and a.on == name for a in aggs))
             rt.call("xchg_agg_accumulate", _vp(rgid), _vp(vc.data), vt, _vp(vc.validity), 0, n, g, _vp(st),
-                    1, rt.stream)
+                    want_minmax, _vp(rows), rt.stream, launches=2)
             if need_m2:
                 rt.call("xchg_agg_accumulate_m2", _vp(rgid), _vp(vc.data), vt, _vp(vc.validity), 0, n, g,
                         _vp(st), _vp(m2), rt.stream)

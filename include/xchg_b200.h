@@ -36,6 +36,8 @@ extern "C" {
 
 #define XCHG_ABI_VERSION 1
 #define XCHG_MAX_ROWS ((uint64_t)((1u << 30) - 1))
+/* widest key range xchg_dense_groups addresses directly */
+#define XCHG_DENSE_MAX_RANGE ((uint64_t)1 << 28)
 
 typedef enum {
   XCHG_OK = 0,
@@ -374,6 +376,29 @@ int xchg_hash_groups(const uint64_t* norm_keys, const uint8_t* validity, int64_t
                      uint64_t n, uint64_t capacity, void* table_ws, uint64_t table_ws_bytes,
                      uint32_t* slot_out, uint64_t* group_keys_out, uint32_t* group_slots_out,
                      uint64_t* num_groups_out, void* stream);
+/*
+ * Direct-address alternative to xchg_hash_groups + xchg_sort_column + xchg_group_ids for
+ * keys whose radix keys span a small range (integer keys such as ids, categories, dates:
+ * BASELINE config 4 groups 2 B rows by an int32 key with 10 M distinct values).  Same
+ * reference arithmetic as above (the grouping half of ArrowBlockAccessor.combine,
+ * arrow_block.py:452-526); the reference has no such special case -- it always sorts.
+ *
+ * xchg_key_minmax: out3_host = {min, max, number of valid rows} of the radix keys of the
+ *   valid rows ({UINT64_MAX, 0, 0} when there is none).  scratch32: 32 device bytes.
+ *   Synchronises the stream.
+ * xchg_dense_groups: presence byte per value in [key_min, key_min + range), scan, lookup:
+ *   row_gid_out[i] = group id of row i in OUTPUT order (key ascending, null group last);
+ *   group_keys_out (range + 1 entries at most; min(range, n) + 1 suffice) receives the
+ *   groups' radix keys in that order, UINT64_MAX for the null group.  range <=
+ *   XCHG_DENSE_MAX_RANGE.  Synchronises the stream (reads the group count).
+ */
+int xchg_key_minmax(const uint64_t* norm_keys, const uint8_t* validity, int64_t validity_bit_offset,
+                    uint64_t n, void* scratch32, uint64_t* out3_host, void* stream);
+int xchg_dense_groups_bytes(uint64_t range, uint64_t* bytes_out);
+int xchg_dense_groups(const uint64_t* norm_keys, const uint8_t* validity, int64_t validity_bit_offset,
+                      uint64_t n, uint64_t key_min, uint64_t range, void* workspace,
+                      uint64_t workspace_bytes, uint32_t* row_gid_out, uint64_t* group_keys_out,
+                      uint64_t* num_groups_out, void* stream);
 /* order = permutation that sorts the group list (from xchg_sort_column);
  * row_gid_out[i] = position of row i's group in that order. */
 int xchg_group_ids(const uint32_t* order, const uint32_t* group_slots, uint64_t num_groups,
@@ -382,12 +407,20 @@ int xchg_group_ids(const uint32_t* order, const uint32_t* group_slots, uint64_t 
 /* stats: 5 * num_groups words, m2 (may be NULL): num_groups doubles. */
 int xchg_agg_stats_init(uint64_t* stats, double* m2, uint64_t num_groups, void* stream);
 /* rows[g] += number of rows of group g (Count, and the ignore_nulls=False test);
- * row_gid NULL = one global group (groupby key None, aggregate.py:61-63). */
-int xchg_agg_count_rows(const uint32_t* row_gid, uint64_t n, uint64_t* rows, void* stream);
-/* Accumulate one value column (value_type = xchg_key_type of its storage). */
+ * row_gid NULL = one global group (groupby key None, aggregate.py:61-63).  With more
+ * than 65 536 groups the kernels issue one atomic per row; below that, lanes of a warp
+ * that share a group are folded first (contended addresses). */
+int xchg_agg_count_rows(const uint32_t* row_gid, uint64_t n, uint64_t num_groups, uint64_t* rows,
+                        void* stream);
+/* Accumulate one value column (value_type = xchg_key_type of its storage).
+ * want_minmax = 0 skips the min / max / NaN-count statistics (Sum, Mean, Std and Count
+ * need none of them).  rows (may be NULL): the per-group row counts of the SAME rows
+ * (xchg_agg_count_rows); for a column without validity they are its value counts and are
+ * added instead of being counted again. */
 int xchg_agg_accumulate(const uint32_t* row_gid, const void* values, int value_type,
                         const uint8_t* validity, int64_t validity_bit_offset, uint64_t n,
-                        uint64_t num_groups, uint64_t* stats, int want_minmax, void* stream);
+                        uint64_t num_groups, uint64_t* stats, int want_minmax,
+                        const uint64_t* rows, void* stream);
 /* Second pass for Std: m2[g] += (x - sum[g]/cnt[g])^2 (after xchg_agg_accumulate). */
 int xchg_agg_accumulate_m2(const uint32_t* row_gid, const void* values, int value_type,
                            const uint8_t* validity, int64_t validity_bit_offset, uint64_t n,

@@ -498,7 +498,43 @@ class FakeLib:
     def _gids(rgid, n):
         return _arr(rgid, np.uint32, n).astype(np.int64) if _addr(rgid) else np.zeros(n, np.int64)
 
-    def xchg_agg_count_rows(self, rgid, n, rows, stream):
+    def xchg_key_minmax(self, norm, validity, vbit, n, scratch, out3, stream):
+        out3[0], out3[1], out3[2] = int(self._EMPTY), 0, 0
+        if n == 0:
+            return 0
+        keys = _arr(norm, np.uint64, n)
+        valid = _bits(validity, vbit, np.arange(n, dtype=np.int64)) if _addr(validity) else np.ones(n, bool)
+        if valid.any():
+            out3[0], out3[1], out3[2] = int(keys[valid].min()), int(keys[valid].max()), int(valid.sum())
+        return 0
+
+    def xchg_dense_groups_bytes(self, rng, out):
+        if rng == 0 or rng > (1 << 28):
+            self.err = b"dense key range out of bounds"
+            return -3
+        out._obj.value = rng * 5 + 4096
+        return 0
+
+    def xchg_dense_groups(self, norm, validity, vbit, n, kmin, rng, ws, wsb, rgid, gkeys, ngroups, stream):
+        ngroups._obj.value = 0
+        if n == 0:
+            return 0
+        keys = _arr(norm, np.uint64, n)
+        valid = _bits(validity, vbit, np.arange(n, dtype=np.int64)) if _addr(validity) else np.ones(n, bool)
+        uniq = np.unique(keys[valid])
+        assert len(uniq) == 0 or (int(uniq[0]) >= kmin and int(uniq[-1]) < kmin + rng)
+        gid = np.full(n, len(uniq), dtype=np.uint32)
+        gid[valid] = np.searchsorted(uniq, keys[valid]).astype(np.uint32)
+        _arr(rgid, np.uint32, n)[:] = gid
+        g = len(uniq)
+        _arr(gkeys, np.uint64, g)[:] = uniq
+        if (~valid).any():
+            _arr(gkeys, np.uint64, g + 1)[g] = self._EMPTY
+            g += 1
+        ngroups._obj.value = g
+        return 0
+
+    def xchg_agg_count_rows(self, rgid, n, num_groups, rows, stream):
         if n == 0:
             return 0
         g = self._gids(rgid, n)
@@ -515,7 +551,7 @@ class FakeLib:
             return x.astype(np.int64).view(np.uint64) ^ np.uint64(1 << 63)
         return x.astype(np.uint64)
 
-    def xchg_agg_accumulate(self, rgid, values, vt, validity, vbit, n, g, stats, want_minmax, stream):
+    def xchg_agg_accumulate(self, rgid, values, vt, validity, vbit, n, g, stats, want_minmax, rows, stream):
         if n == 0:
             return 0
         dt = np.dtype(_KT[vt])
