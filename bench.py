@@ -46,7 +46,7 @@ KERNEL_NAMES = {0: "k_normalize_hist", 1: "k_scan_hist", 2: "k_onesweep", 3: "k_
                 4: "k_gather_fixed", 5: "k_gather_bitmap", 6: "k_lengths_scan", 7: "k_partition_bounds",
                 8: "k_offsets_*", 9: "misc", 10: "k_merge", 11: "k_shuffle", 12: "k_aggregate", 13: "k_local_sort", 14: "k_msd_aux"}
 # algorithmic bytes per row per launch
-KERNEL_BYTES_PER_ROW = {0: 16, 2: 24, 3: 2 * PAYLOAD}
+KERNEL_BYTES_PER_ROW = {0: 16, 2: 24, 3: 2 * PAYLOAD, 13: 24}
 
 
 def peaks():
@@ -438,8 +438,19 @@ def run_b200(args):
     roofline = None
     for k in kernels:
         if k["id"] in KERNEL_BYTES_PER_ROW:
-            rows_per_launch = n  # every launch of these kernels covers the rank's n rows
-            bpl = KERNEL_BYTES_PER_ROW[k["id"]] * rows_per_launch
+            # rows one step sends through this kernel class on this rank: every normalise /
+            # onesweep launch covers the n resident rows; the local sorts of a step cover
+            # them once in total (one launch per segment-size class); the row gather covers
+            # them once, or twice when distributed (into the peers' arenas, one launch per
+            # destination, then the final take)
+            if k["id"] == 13:
+                rows_per_step = n
+            elif k["id"] == 3:
+                rows_per_step = n * (2 if world > 1 else 1)
+            else:
+                rows_per_step = n * k["launches_per_step"]
+            bpl = KERNEL_BYTES_PER_ROW[k["id"]] * rows_per_step / k["launches_per_step"]
+            k["algorithmic_bytes_per_launch"] = bpl
             k["achieved_gbs"] = bpl / (k["avg_launch_ms"] * 1e-3) / 1e9
             k["frac_of_peak"] = k["achieved_gbs"] / peak
     dom = next((k for k in kernels if "achieved_gbs" in k), None)
@@ -447,10 +458,10 @@ def run_b200(args):
         roofline = {"bound": "hbm", "kernel": dom["kernel"], "achieved": dom["achieved_gbs"], "peak": peak,
                     "unit": "GB/s", "frac": dom["achieved_gbs"] / peak, "traffic": None,
                     "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": KERNEL_BYTES_PER_ROW[dom["id"]] * n,
+                    "algorithmic_bytes_per_launch": dom["algorithmic_bytes_per_launch"],
                     "share_of_step": dom["ms_per_step"] / ms_per_step}
         tr = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tr):
+        if os.path.exists(tr) and world == 1:  # captured per launch at one GPU (n rows per launch)
             try:
                 with open(tr) as f:
                     roofline["traffic"] = json.load(f).get(dom["kernel"])
