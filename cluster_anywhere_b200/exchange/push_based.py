@@ -29,7 +29,8 @@ from typing import Any, Dict, Iterator, List, Optional
 
 from ..block import BlockExecStats, BlockMetadata
 from ..block_accessor import B200ArrowBlockAccessor
-from .interfaces import ExchangeTaskScheduler
+from .interfaces import (ExchangeTaskScheduler, ExchangeTaskSpec, sub_progress_bar, unwrap_refs,
+                         wrap_outputs)
 
 
 class MergeSchedule:
@@ -139,7 +140,9 @@ class PushBasedShuffleTaskScheduler(ExchangeTaskScheduler):
         import os
 
         spec = self._exchange_spec
-        blocks = list(refs)
+        blocks, input_owned, wrapped = unwrap_refs(refs)
+        map_bar = sub_progress_bar(task_ctx, ExchangeTaskSpec.MAP_SUB_PROGRESS_BAR_NAME)
+        reduce_bar = sub_progress_bar(task_ctx, ExchangeTaskSpec.REDUCE_SUB_PROGRESS_BAR_NAME)
         if _debug_limit_execution_to_num_blocks is not None:
             blocks = blocks[:_debug_limit_execution_to_num_blocks]
         if num_cpus_per_node_map is None:
@@ -194,5 +197,10 @@ class PushBasedShuffleTaskScheduler(ExchangeTaskScheduler):
             blk, meta = spec.reduce(*spec._reduce_args, *inputs)
             results[j], reduce_meta[j] = blk, meta
         order = sorted(results)
-        stats = {"map": map_meta, "merge": merge_meta, "reduce": [reduce_meta[j] for j in order]}
-        return [results[j] for j in order], stats
+        if map_bar is not None:
+            map_bar.update(len(map_meta))
+        metas = [reduce_meta[j] for j in order]
+        if reduce_bar is not None:
+            metas = reduce_bar.fetch_until_complete(metas)
+        stats = {"map": map_meta, "merge": merge_meta, "reduce": metas}
+        return wrap_outputs([results[j] for j in order], metas, input_owned, wrapped), stats
