@@ -16,7 +16,7 @@ sys.path.insert(0, ROOT)
 
 KNAMES = {0: "k_normalize_hist", 1: "k_scan_hist", 2: "k_onesweep", 3: "k_gather_rows", 4: "k_gather_fixed",
           5: "k_gather_bitmap", 6: "k_lengths_scan", 7: "k_partition", 8: "k_offsets_*", 9: "misc",
-          10: "k_merge", 11: "k_shuffle", 12: "k_aggregate"}
+          10: "k_merge", 11: "k_shuffle", 12: "k_aggregate", 13: "k_local_sort", 14: "k_msd_aux"}
 
 
 def kernels(lib, steps):
@@ -50,6 +50,55 @@ def timed(fn, steps, warmup, lib):
     return e0.elapsed_time(e1) / steps, ks
 
 
+def string_sort(args, rt, ex, lib, peak):
+    """configs[4] at a stated sub-scale: Dataset.sort on a string key drawn Zipf(1.2) from a
+    vocabulary of 8..31-byte strings, with a 16..256-byte binary payload."""
+    import numpy as np
+    import pyarrow as pa
+    import torch
+
+    from cluster_anywhere_b200 import SortKey
+    from cluster_anywhere_b200 import device as dev
+    from cluster_anywhere_b200.exchange import DeviceDataset
+
+    n, V = args.string_rows, args.string_vocab
+    rng = np.random.default_rng(5)
+    gen = torch.Generator(device=rt.device)
+    gen.manual_seed(5)
+    vlen = torch.randint(8, 32, (V,), device=rt.device, generator=gen, dtype=torch.int64)
+    voff = torch.zeros(V + 1, dtype=torch.int64, device=rt.device)
+    voff[1:] = torch.cumsum(vlen, 0)
+    vbytes = int(voff[-1].item())
+    vdata = torch.randint(97, 123, (vbytes + 64,), device=rt.device, generator=gen, dtype=torch.uint8)[:vbytes]
+    vocab = dev.DeviceColumn(pa.string(), V, "var", 1, vdata, voff, None, 0)
+    z = np.minimum(rng.zipf(1.2, n), V) - 1
+    idx = torch.from_numpy(z.astype(np.int32)).to(rt.device)
+    keycol = dev.take_column(rt, vocab, idx, n)
+    plen = torch.randint(16, 257, (n,), device=rt.device, generator=gen, dtype=torch.int64)
+    poff = torch.zeros(n + 1, dtype=torch.int64, device=rt.device)
+    poff[1:] = torch.cumsum(plen, 0)
+    pbytes = int(poff[-1].item())
+    pdata = torch.empty(pbytes + 64, dtype=torch.uint8, device=rt.device)[:pbytes]
+    pdata[: pbytes // 8 * 8].view(torch.int64)[:] = torch.arange(pbytes // 8, device=rt.device, dtype=torch.int64)
+    del plen, idx
+    paycol = dev.DeviceColumn(pa.large_binary(), n, "var", 1, pdata, poff, None, 0)
+    table = dev.DeviceTable(["key", "payload"], [keycol, paycol], n,
+                            pa.schema([("key", pa.string()), ("payload", pa.large_binary())]))
+    blocks = 16
+    ds = DeviceDataset(table, [(i * n // blocks, (i + 1) * n // blocks) for i in range(blocks)])
+    sk = SortKey("key")
+    kbytes = int(keycol.data.numel())
+    ms, ks = timed(lambda i: ex.sort(ds, sk, seed=i), args.steps, args.warmup, lib)
+    gbs = 2 * (kbytes + pbytes + 16 * (n + 1)) / ms / 1e6
+    print(json.dumps({"op": "sort(string key)", "workload": f"{n} rows, string key Zipf(1.2) over {V} distinct strings of "
+                      f"8-31 bytes ({kbytes / 1e9:.2f} GB), binary payload 16-256 bytes ({pbytes / 1e9:.2f} GB), {blocks} "
+                      "blocks: BASELINE configs[4] (500 M rows, 10 M distinct) at a sub-scale that fits one run's time",
+                      "ms_per_step": ms, "rows_per_s": n / ms * 1e3, "gb_per_s_algorithmic": gbs,
+                      "frac_of_measured_hbm": gbs / peak, "kernels": ks}), flush=True)
+    del ds, table, keycol, paycol, pdata, poff, vocab
+    torch.cuda.empty_cache()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=5)
@@ -57,6 +106,9 @@ def main():
     ap.add_argument("--shuffle-rows", type=int, default=25_000_000)
     ap.add_argument("--agg-rows", type=int, default=250_000_000)
     ap.add_argument("--agg-groups", type=int, default=10_000_000)
+    ap.add_argument("--string-rows", type=int, default=40_000_000)
+    ap.add_argument("--string-vocab", type=int, default=800_000)
+    ap.add_argument("--only", default="", help="comma list of ops to run: shuffle,aggregate,strings")
     args = ap.parse_args()
     import pyarrow as pa
     import torch
@@ -73,6 +125,12 @@ def main():
     ex = DeviceExchange(rt)
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(
         os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+
+    only = set(x for x in args.only.split(",") if x)
+    if not only or "strings" in only:
+        string_sort(args, rt, ex, lib, peak)
+    if only and "shuffle" not in only and "aggregate" not in only:
+        return
 
     # ---- configs[2] shard: random_shuffle(seed=42) of 1 KiB tensor rows ----
     n, w = args.shuffle_rows, 1024
