@@ -49,6 +49,10 @@ _SIGNATURES = {
     "xchg_dense_groups_bytes": (c_int, [c_uint64, ctypes.POINTER(c_uint64)]),
     "xchg_dense_groups": (c_int, [_P, _P, c_int64, c_uint64, c_uint64, c_uint64, _P, c_uint64, _P, _P,
                                   ctypes.POINTER(c_uint64), _P]),
+    "xchg_group_flags_fixed": (c_int, [_P, _P, c_int64, _P, c_uint64, _P, _P]),
+    "xchg_group_flags_bytes": (c_int, [_P, _P, _P, c_int64, _P, c_uint64, _P, _P]),
+    "xchg_groups_from_flags_bytes": (c_int, [c_uint64, ctypes.POINTER(c_uint64)]),
+    "xchg_groups_from_flags": (c_int, [_P, _P, c_uint64, _P, c_uint64, _P, _P, ctypes.POINTER(c_uint64), _P]),
     "xchg_agg_count_rows": (c_int, [_P, c_uint64, c_uint64, _P, _P]),
     "xchg_agg_accumulate": (c_int, [_P, _P, c_int, _P, c_int64, c_uint64, c_uint64, _P, c_int, _P, _P]),
     "xchg_agg_accumulate_m2": (c_int, [_P, _P, c_int, _P, c_int64, c_uint64, c_uint64, _P, _P, _P]),

@@ -236,6 +236,92 @@ def group_rows(rt: dev.Runtime, key_col: DeviceColumn, n: int):
     return rgid, sorted_keys, g, kt
 
 
+def group_rows_sorted(rt: dev.Runtime, table: DeviceTable, key_names: Sequence[str]):
+    """General grouping (several key columns, string / binary keys): stable sort of the
+    rows by the keys, per-column change marks on the sorted order, scan of the marks.
+    -> (row group ids uint32[n] in OUTPUT order, G, original row id of every group's
+    first row uint32[G])."""
+    n = table.num_rows
+    perm, norms = dev.sort_permutation(rt, table, list(key_names), [False] * len(key_names))
+    flags = rt.zeros(n)
+    for ci, name in enumerate(key_names):
+        col = table.column(name)
+        if dev.is_string_key(col):
+            rt.call("xchg_group_flags_bytes", _vp(dev._string_offsets(rt, col)), _vp(col.data),
+                    _vp(col.validity), 0, _vp(perm), n, _vp(flags), rt.stream)
+            continue
+        if col.kind != "fixed":
+            raise NotImplementedError(f"group key of type {col.type} is not supported by the B200 engine")
+        nk = norms[0] if ci == 0 and norms and norms[0] is not None else None
+        if nk is None:
+            nk = rt.empty(n, torch.int64)
+            rt.call("xchg_normalize_keys", _vp(col.data), dev.key_type_of(col.type), 0, _vp(col.validity), 0,
+                    _vp(perm), n, _vp(nk), rt.stream)
+        rt.call("xchg_group_flags_fixed", _vp(nk), _vp(col.validity), 0, _vp(perm), n, _vp(flags), rt.stream)
+    wsb = ctypes.c_uint64()
+    _cabi.check(_cabi.load().xchg_groups_from_flags_bytes(n, ctypes.byref(wsb)))
+    ws = rt.empty(wsb.value)
+    rgid = rt.empty(n, torch.int32)
+    first = rt.empty(n, torch.int32)
+    g_out = ctypes.c_uint64()
+    rt.call("xchg_groups_from_flags", _vp(flags), _vp(perm), n, _vp(ws), wsb.value, _vp(rgid), _vp(first),
+            ctypes.byref(g_out), rt.stream, launches=3)
+    g = int(g_out.value)
+    return rgid, g, first[:g]
+
+
+def _key_columns_out(rt: dev.Runtime, table: DeviceTable, key_names: Sequence[str], first: torch.Tensor, g: int):
+    """Key columns of the result: the key values of every group's first row.  Integer
+    keys come out as int64 and float keys as double, as the reference rebuilds them from
+    Python scalars; string / binary keys keep their type."""
+    cols, fields = [], []
+    for name in key_names:
+        kc = table.column(name)
+        if dev.is_string_key(kc):
+            cols.append(dev.take_column(rt, kc, first, g))
+            fields.append(pa.field(name, kc.type))
+            continue
+        kt = dev.key_type_of(kc.type)
+        nk = rt.empty(g, torch.int64)
+        rt.call("xchg_normalize_keys", _vp(kc.data), kt, 0, _vp(kc.validity), 0, _vp(first), g, _vp(nk), rt.stream)
+        kvals = rt.empty(g, torch.int64)
+        rt.call("xchg_group_keys_out", _vp(nk), kt, g, _vp(kvals), rt.stream)
+        out_type = pa.int64() if _is_int_type(kt) else pa.float64()
+        kvalid, knulls = None, 0
+        if kc.validity is not None and _resolve_nulls(kc) > 0:
+            kvalid = rt.zeros(((g + 31) // 32) * 4)
+            cnt = rt.zeros(1, torch.int64)
+            rt.call("xchg_gather_bitmap", _vp(kc.validity), 0, _vp(first), g, _vp(kvalid), _vp(cnt), rt.stream)
+            knulls = cnt
+        cols.append(DeviceColumn(out_type, g, "fixed", 8, kvals.view(torch.uint8), None, kvalid, knulls))
+        fields.append(pa.field(name, out_type))
+    return cols, fields
+
+
+def null_typed_like_reference(t: pa.Table) -> pa.Table:
+    """A FINAL aggregate block is rebuilt by the reference row by row from Python scalars
+    (ArrowBlockBuilder over the rows of aggregate_combined_blocks, arrow_block.py:593-660),
+    so a column whose every value is None comes out with Arrow type ``null`` (e.g. the key
+    column of the block that holds only the null group), and a block without groups is the
+    schema-less empty table (arrow_block.py:316).  Same here, on the host copy."""
+    if t.num_rows == 0:
+        return pa.table({})
+    for i, name in enumerate(t.schema.names):
+        col = t.column(i)
+        if col.null_count == t.num_rows and not pa.types.is_null(col.type):
+            t = t.set_column(i, name, pa.nulls(t.num_rows))
+    return t
+
+
+def key_list(key) -> List[str]:
+    """``None`` / one column name / a list of names -> list of key columns."""
+    if key is None:
+        return []
+    if isinstance(key, str):
+        return [key]
+    return list(key)
+
+
 def _bytes_to_validity(rt: dev.Runtime, valid_bytes: torch.Tensor, g: int):
     bm = rt.zeros(((g + 31) // 32) * 4)
     cnt = rt.zeros(1, torch.int64)
@@ -267,7 +353,15 @@ def aggregate_table(rt: dev.Runtime, table: DeviceTable, key: Optional[str],
     g = 1
     key_col_out = None
     key_field = None
-    if key is not None:
+    keys = key_list(key)
+    key_cols_out: List[DeviceColumn] = []
+    key_fields: List[pa.Field] = []
+    general = len(keys) > 1 or (len(keys) == 1 and table.column(keys[0]).kind != "fixed")
+    if general:
+        rgid, g, first = group_rows_sorted(rt, table, keys)
+        key_cols_out, key_fields = _key_columns_out(rt, table, keys, first, g)
+    elif keys:
+        key = keys[0]
         kc = table.column(key)
         rgid, sorted_keys, g, kt = group_rows(rt, kc, n)
         kvals = rt.empty(g, torch.int64)
@@ -279,8 +373,8 @@ def aggregate_table(rt: dev.Runtime, table: DeviceTable, key: Optional[str],
             vb.fill_(1)
             vb[g - 1:g].fill_(0)  # the null group is the last one
             kvalid, knulls = _bytes_to_validity(rt, vb, g)
-        key_col_out = DeviceColumn(out_type, g, "fixed", 8, kvals.view(torch.uint8), None, kvalid, knulls)
-        key_field = pa.field(key, out_type)
+        key_cols_out = [DeviceColumn(out_type, g, "fixed", 8, kvals.view(torch.uint8), None, kvalid, knulls)]
+        key_fields = [pa.field(key, out_type)]
 
     rows = rt.zeros(g, torch.int64)
     if partial_in:
@@ -319,9 +413,8 @@ def aggregate_table(rt: dev.Runtime, table: DeviceTable, key: Optional[str],
 
     cols: List[DeviceColumn] = []
     fields: List[pa.Field] = []
-    if key_col_out is not None:
-        cols.append(key_col_out)
-        fields.append(key_field)
+    cols.extend(key_cols_out)
+    fields.extend(key_fields)
     if not finalize:
         cols.append(DeviceColumn(pa.int64(), g, "fixed", 8, rows.view(torch.uint8)))
         fields.append(pa.field(ROWS_COL, pa.int64()))
@@ -334,8 +427,7 @@ def aggregate_table(rt: dev.Runtime, table: DeviceTable, key: Optional[str],
             fields.append(_state_field(name, vt))
         return DeviceTable([f.name for f in fields], cols, g, pa.schema(fields))
 
-    names = munge_names(([key] if key is not None else []) + [a.name for a in aggs])
-    names = names[1:] if key is not None else names
+    names = munge_names(keys + [a.name for a in aggs])[len(keys):]
     for a, out_name in zip(aggs, names):
         out = rt.empty(g, torch.int64)
         vb = rt.empty(g)
@@ -355,20 +447,78 @@ def aggregate_table(rt: dev.Runtime, table: DeviceTable, key: Optional[str],
     return DeviceTable([f.name for f in fields], cols, g, pa.schema(fields))
 
 
-def group_cut_points(rt: dev.Runtime, result: DeviceTable, key: str, boundaries: Sequence[tuple]) -> List[int]:
+def _cuts_by_merged_sort(rt: dev.Runtime, result: DeviceTable, cols: List[str],
+                         boundaries: Sequence[tuple]) -> List[int]:
+    """Cut points for key tuples that mix string and numeric columns.  ``result`` holds one
+    row per DISTINCT key tuple, sorted ascending; the cut of a boundary is the number of
+    groups strictly before it (find_partition_index, _internal/util.py:728-803, all columns
+    ascending: the left end of the narrowing search; a None component sorts after every
+    value, as NULL_SENTINEL does).  The boundary tuples are appended to the group keys and
+    the whole is grouped once more (stable sort + run marks): the groups before a boundary
+    are the runs before its run that contain a data row."""
+    G, nb = result.num_rows, len(boundaries)
+    # A None component on a NUMERIC column ends the reference's search after every row that
+    # shares the components before it: pyarrow hands numpy a float array with NaN for the
+    # nulls, `col_vals == None` matches nothing, and NULL_SENTINEL compares above everything
+    # (util.py:761-770, 800-801), so left == right == end of the run and the loop returns.
+    # On a string column the nulls ARE replaced by the sentinel and the search goes on inside
+    # the null rows.  Hence: from the first numeric None on, the boundary is "after every row
+    # with this prefix": nulls in the remaining components and an UPPER bound.
+    is_str = [dev.is_string_key(result.column(c)) for c in cols]
+    tuples, upper = [], []
+    for bnd in boundaries:
+        bnd = tuple(bnd) + (None,) * (len(cols) - len(bnd))
+        cut_at = next((i for i, v in enumerate(bnd) if v is None and not is_str[i]), None)
+        if cut_at is not None:
+            bnd = bnd[:cut_at] + (None,) * (len(cols) - cut_at)
+        tuples.append(bnd)
+        upper.append(cut_at is not None)
+    try:
+        btab = pa.table({c: pa.array([t[i] for t in tuples], type=result.column(c).type)
+                         for i, c in enumerate(cols)})
+    except (pa.ArrowInvalid, pa.ArrowTypeError) as e:
+        raise NotImplementedError(f"boundaries {list(boundaries)!r} do not convert to the key types: {e}")
+    bdev = dev.stage_table(rt, btab)
+    merged_cols = [dev.concat_columns(rt, result.column(c), bdev.column(c)) for c in cols]
+    merged = DeviceTable(list(cols), merged_cols, G + nb, pa.schema([(c, result.column(c).type) for c in cols]))
+    rgid, g, first = group_rows_sorted(rt, merged, cols)
+    gid_b = rgid[G:G + nb].cpu().numpy().view(np.uint32).astype(np.int64)
+    first_h = first.cpu().numpy().view(np.uint32).astype(np.int64)
+    boundary_only = sorted(set(int(x) for x in gid_b if first_h[int(x)] >= G))
+    cuts = []
+    for x, up in zip(gid_b, upper):
+        x = int(x)
+        before = x - sum(1 for y in boundary_only if y < x)  # runs with a data row before this run
+        has_data_row = first_h[x] < G                         # data rows come first inside a run
+        cuts.append(before + (1 if (up and has_data_row) else 0))
+    return cuts
+
+
+def group_cut_points(rt: dev.Runtime, result: DeviceTable, key, boundaries: Sequence[tuple]) -> List[int]:
     """Range-partition cut points of an aggregate result / partial table (sorted by
     key ascending) under the reference's boundary rule (K4): partition i = groups
     ``[cut[i-1], cut[i])`` -- what ``sort_and_partition`` + per-partition ``combine``
-    produce in SortAggregateTaskSpec.map (aggregate_task_spec.py:38-59)."""
+    produce in SortAggregateTaskSpec.map (aggregate_task_spec.py:38-59).  ``key`` = one
+    column name or a list; a string key is searched on the (sorted) result column itself."""
     from . import keys as keymod
 
     if not boundaries:
         return []
-    kc = result.column(key)
+    cols = key_list(key)
     g = result.num_rows
-    kt = dev.key_type_of(kc.type)
-    norm = rt.empty(g, torch.int64)
-    rt.call("xchg_normalize_keys", _vp(kc.data), kt, 0, _vp(kc.validity), 0, None, g, _vp(norm), rt.stream)
-    lower, upper, flags = keymod.normalize_boundaries(boundaries, [kt], [False])
-    thr = keymod.last_class_threshold(kt, _resolve_nulls(kc))
-    return dev.partition_cuts(rt, [norm], g, lower, upper, flags, [False], [thr[0]], [thr[1]])
+    if any(dev.is_string_key(result.column(c)) for c in cols):
+        if len(cols) != 1:
+            return _cuts_by_merged_sort(rt, result, cols, boundaries)
+        return dev.string_partition_cuts(rt, result.column(cols[0]), boundaries, False)
+    norms, ktypes, thr = [], [], []
+    for c in cols:
+        kc = result.column(c)
+        kt = dev.key_type_of(kc.type)
+        norm = rt.empty(g, torch.int64)
+        rt.call("xchg_normalize_keys", _vp(kc.data), kt, 0, _vp(kc.validity), 0, None, g, _vp(norm), rt.stream)
+        norms.append(norm)
+        ktypes.append(kt)
+        thr.append(keymod.last_class_threshold(kt, _resolve_nulls(kc)))
+    desc = [False] * len(cols)
+    lower, upper, flags = keymod.normalize_boundaries(boundaries, ktypes, desc)
+    return dev.partition_cuts(rt, norms, g, lower, upper, flags, desc, [t[0] for t in thr], [t[1] for t in thr])

@@ -252,13 +252,12 @@ class B200ArrowBlockAccessor:
         return self._reduce(agg.KIND_MEAN, on, ignore_nulls)
 
     @staticmethod
-    def _group_key(sort_key: SortKey) -> Optional[str]:
-        cols = sort_key.get_columns() if sort_key is not None else []
-        if len(cols) > 1:
-            raise NotImplementedError(
-                "group-by on several key columns is not offloaded to the B200 engine yet "
-                f"(got {cols}); use the reference path")
-        return cols[0] if cols else None
+    def _group_key(sort_key: SortKey):
+        """None (one global group), a column name, or the list of key columns."""
+        cols = list(sort_key.get_columns()) if sort_key is not None else []
+        if not cols:
+            return None
+        return cols[0] if len(cols) == 1 else cols
 
     def combine(self, sort_key: SortKey, aggs) -> pa.Table:
         """arrow_block.py:452-526: one row per group with the partially combined
@@ -272,7 +271,7 @@ class B200ArrowBlockAccessor:
         if self.num_rows() == 0:
             return self._empty_table()
         rt = self.rt
-        dt = dev.stage_table(rt, agg.prune_columns(self._table, [key] if key else [], aggs))
+        dt = dev.stage_table(rt, agg.prune_columns(self._table, agg.key_list(key), aggs))
         out = agg.aggregate_table(rt, dt, key, aggs, finalize=False)
         return dev.export_table(rt, out)
 
@@ -294,4 +293,6 @@ class B200ArrowBlockAccessor:
             t = pa.concat_tables(blocks, promote_options="default")
             out = agg.aggregate_table(rt, dev.stage_table(rt, t), key, aggs, finalize=finalize)
             ret = dev.export_table(rt, out)
+            if finalize:
+                ret = agg.null_typed_like_reference(ret)
         return ret, B200ArrowBlockAccessor(ret, runtime).get_metadata(exec_stats=stats.build())

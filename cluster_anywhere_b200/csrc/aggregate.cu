@@ -694,6 +694,97 @@ k_dense_lookup(const uint64_t* __restrict__ norm, const uint8_t* __restrict__ va
   }
 }
 
+// ---- grouping of SORTED rows (any key: several columns, strings) ---------------------------
+// The general path: rows are sorted by the key columns (stable chained K2/K3 sorts, string
+// keys included), every key column marks the sorted positions where it changes, and a scan
+// of the marks numbers the groups -- the run detection of ArrowBlockAccessor.combine
+// (arrow_block.py:478-497, keys_equal: NaN == NaN, null its own group) and of
+// _get_block_boundaries (python/ray/data/block.py) as data-parallel kernels.
+
+// flags[i] |= sorted row i differs from sorted row i-1 in this column (flags[0] = 1).
+// norm: radix keys in SORTED order; validity is indexed by original row id through perm.
+__global__ void __launch_bounds__(AG_THREADS)
+k_group_flags_fixed(const uint64_t* __restrict__ norm, const uint8_t* __restrict__ validity, int64_t vbit,
+                    const uint32_t* __restrict__ perm, uint64_t n, uint8_t* __restrict__ flags) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    bool diff = i == 0;
+    if (!diff) {
+      diff = norm[i] != norm[i - 1];
+      if (!diff && validity)
+        diff = bit_is_set(validity, (int64_t)perm[i] + vbit) != bit_is_set(validity, (int64_t)perm[i - 1] + vbit);
+    }
+    if (diff) flags[i] = 1;
+  }
+}
+
+// The same for a variable-width column (int64 offsets + bytes): equal = same validity and,
+// when valid, same length and bytes.
+__global__ void __launch_bounds__(AG_THREADS)
+k_group_flags_bytes(const int64_t* __restrict__ offsets, const uint8_t* __restrict__ data,
+                    const uint8_t* __restrict__ validity, int64_t vbit,
+                    const uint32_t* __restrict__ perm, uint64_t n, uint8_t* __restrict__ flags) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    bool diff = i == 0;
+    if (!diff) {
+      const uint32_t a = perm[i - 1], b = perm[i];
+      const bool va = validity ? bit_is_set(validity, (int64_t)a + vbit) : true;
+      const bool vb = validity ? bit_is_set(validity, (int64_t)b + vbit) : true;
+      if (va != vb) {
+        diff = true;
+      } else if (va) {
+        const int64_t a0 = offsets[a], a1 = offsets[a + 1], b0 = offsets[b], b1 = offsets[b + 1];
+        if (a1 - a0 != b1 - b0) {
+          diff = true;
+        } else {
+          for (int64_t j = 0; j < a1 - a0; ++j)
+            if (data[a0 + j] != data[b0 + j]) {
+              diff = true;
+              break;
+            }
+        }
+      }
+    }
+    if (diff) flags[i] = 1;
+  }
+}
+
+// group id of every ORIGINAL row and the original row id of every group's first row
+__global__ void __launch_bounds__(256)
+k_groups_emit(const uint8_t* __restrict__ flags, uint64_t n, const uint32_t* __restrict__ tile_excl,
+              const uint32_t* __restrict__ perm, uint32_t* __restrict__ row_gid,
+              uint32_t* __restrict__ group_first) {
+  __shared__ uint32_t ws[8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint64_t base = (uint64_t)blockIdx.x * DG_TILE + (uint64_t)threadIdx.x * 16;
+  uint8_t b[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) b[j] = (base + j < n) ? flags[base + j] : 0;
+  uint32_t c = 0;
+#pragma unroll
+  for (int j = 0; j < 16; ++j) c += b[j];
+  uint32_t x = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= o) x += y;
+  }
+  if (lane == 31) ws[warp] = x;
+  __syncthreads();
+  uint32_t r = tile_excl[blockIdx.x] + x - c;  // marks before this thread's first position
+  for (int w = 0; w < warp; ++w) r += ws[w];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    if (base + j < n) {
+      r += b[j];
+      const uint32_t row = perm ? perm[base + j] : (uint32_t)(base + j);
+      row_gid[row] = r - 1;
+      if (b[j]) group_first[r - 1] = row;
+    }
+  }
+}
+
 bool key_type_is_int(int t) { return t >= XCHG_I8 && t <= XCHG_U64; }
 
 }  // namespace
@@ -861,6 +952,70 @@ extern "C" int xchg_dense_groups(const uint64_t* norm_keys, const uint8_t* valid
       norm_keys, validity, validity_bit_offset, n, key_min, w.rank, (uint32_t)total, row_gid_out));
   XCHG_LAUNCH_CHECK();
   *num_groups_out = total + (has_null ? 1 : 0);
+  return XCHG_OK;
+}
+
+extern "C" int xchg_group_flags_fixed(const uint64_t* norm_sorted, const uint8_t* validity,
+                                      int64_t validity_bit_offset, const uint32_t* perm, uint64_t n,
+                                      uint8_t* flags, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  if (n == 0) return XCHG_OK;
+  XCHG_REQUIRE(norm_sorted && flags, "NULL keys / flags");
+  XCHG_REQUIRE(!validity || perm, "validity needs the permutation");
+  XCHG_LAUNCH(XK_AGGREGATE, s, k_group_flags_fixed<<<ag_grid(n), AG_THREADS, 0, s>>>(
+      norm_sorted, validity, validity_bit_offset, perm, n, flags));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+extern "C" int xchg_group_flags_bytes(const int64_t* offsets, const uint8_t* data, const uint8_t* validity,
+                                      int64_t validity_bit_offset, const uint32_t* perm, uint64_t n,
+                                      uint8_t* flags, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  if (n == 0) return XCHG_OK;
+  XCHG_REQUIRE(offsets && perm && flags, "NULL offsets / perm / flags");
+  XCHG_LAUNCH(XK_AGGREGATE, s, k_group_flags_bytes<<<ag_grid(n), AG_THREADS, 0, s>>>(
+      offsets, data, validity, validity_bit_offset, perm, n, flags));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+extern "C" int xchg_groups_from_flags_bytes(uint64_t n, uint64_t* bytes_out) {
+  XCHG_REQUIRE(bytes_out != nullptr, "bytes_out is NULL");
+  XCHG_REQUIRE(n <= XCHG_MAX_ROWS, "n exceeds XCHG_MAX_ROWS");
+  *bytes_out = xchg_align_up(((n + DG_TILE - 1) / DG_TILE + 1) * 4, 256) + 512;
+  return XCHG_OK;
+}
+
+extern "C" int xchg_groups_from_flags(const uint8_t* flags, const uint32_t* perm, uint64_t n,
+                                      void* workspace, uint64_t workspace_bytes, uint32_t* row_gid_out,
+                                      uint32_t* group_first_out, uint64_t* num_groups_out, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  XCHG_REQUIRE(num_groups_out != nullptr, "NULL num_groups_out");
+  *num_groups_out = 0;
+  if (n == 0) return XCHG_OK;
+  XCHG_REQUIRE(flags && workspace && row_gid_out && group_first_out, "NULL argument");
+  uint64_t need = 0;
+  int rc = xchg_groups_from_flags_bytes(n, &need);
+  if (rc) return rc;
+  if (workspace_bytes < need) {
+    xchg_set_error("group scan workspace too small: have %llu, need %llu",
+                   (unsigned long long)workspace_bytes, (unsigned long long)need);
+    return XCHG_ERR_WORKSPACE;
+  }
+  uint8_t* base = (uint8_t*)xchg_align_up((uint64_t)(uintptr_t)workspace, 256);
+  const uint32_t ntiles = (uint32_t)((n + DG_TILE - 1) / DG_TILE);
+  uint32_t* tile_sums = (uint32_t*)base;
+  unsigned long long* total = (unsigned long long*)(base + xchg_align_up((uint64_t)(ntiles + 1) * 4, 256));
+  XCHG_LAUNCH(XK_AGGREGATE, s, k_dense_tile_sums<<<ntiles, 256, 0, s>>>(flags, n, tile_sums));
+  XCHG_LAUNCH(XK_AGGREGATE, s, k_dense_scan_sums<<<1, 1024, 0, s>>>(tile_sums, ntiles, total));
+  XCHG_LAUNCH(XK_AGGREGATE, s, k_groups_emit<<<ntiles, 256, 0, s>>>(flags, n, tile_sums, perm, row_gid_out,
+                                                                group_first_out));
+  XCHG_LAUNCH_CHECK();
+  unsigned long long g = 0;
+  XCHG_CUDA_TRY(cudaMemcpyAsync(&g, total, 8, cudaMemcpyDeviceToHost, s));
+  XCHG_CUDA_TRY(cudaStreamSynchronize(s));
+  *num_groups_out = g;
   return XCHG_OK;
 }
 

@@ -403,6 +403,47 @@ def take_column(rt: Runtime, col: DeviceColumn, idx: torch.Tensor, n_out: int) -
     return DeviceColumn(col.type, n_out, "var", col.width, out, out_off, validity, null_count)
 
 
+def concat_columns(rt: Runtime, a: DeviceColumn, b: DeviceColumn) -> DeviceColumn:
+    """Rows of ``a`` followed by rows of ``b`` (same Arrow type) as one device column."""
+    assert a.type == b.type and a.kind == b.kind, (a.type, b.type)
+    n = a.n + b.n
+    validity, nulls = None, 0
+    if a.validity is not None or b.validity is not None:
+        by = rt.empty(n)
+        for col, lo in ((a, 0), (b, a.n)):
+            part = by[lo:lo + col.n]
+            if col.n == 0:
+                continue
+            if col.validity is None:
+                part.fill_(1)
+            else:
+                rt.call("xchg_bitmap_unpack", _vp(col.validity), 0, col.n, _vp(part), rt.stream)
+        validity = rt.zeros(((n + 31) // 32) * 4)
+        cnt = rt.zeros(1, torch.int64)
+        rt.call("xchg_bitmap_pack", _vp(by), n, _vp(validity), _vp(cnt), rt.stream)
+        nulls = cnt
+    if a.kind == "fixed":
+        data = rt.empty(n * a.width)
+        data[: a.n * a.width].copy_(a.data[: a.n * a.width])
+        data[a.n * a.width:].copy_(b.data[: b.n * b.width])
+        return DeviceColumn(a.type, n, "fixed", a.width, data, None, validity, nulls)
+    if a.kind != "var":
+        raise NotImplementedError(f"concatenation of {a.type} columns")
+    oa, ob = _string_offsets(rt, a), _string_offsets(rt, b)
+    bytes_a = int(oa[a.n].item()) - int(oa[0].item()) if a.n else 0
+    bytes_b = int(ob[b.n].item()) - int(ob[0].item()) if b.n else 0
+    off = rt.empty(n + 1, torch.int64)
+    rt.call("xchg_offsets_rebase", _vp(oa), a.n + 1, 0, _vp(off), rt.stream)
+    tail = off[a.n:]
+    rt.call("xchg_offsets_rebase", _vp(ob), b.n + 1, bytes_a, _vp(tail), rt.stream)
+    data = rt.empty(bytes_a + bytes_b)
+    a0 = int(oa[0].item()) if a.n else 0
+    b0 = int(ob[0].item()) if b.n else 0
+    data[:bytes_a].copy_(a.data[a0:a0 + bytes_a])
+    data[bytes_a:].copy_(b.data[b0:b0 + bytes_b])
+    return DeviceColumn(a.type, n, "var", a.width, data, off, validity, nulls)
+
+
 def _is_int_key(kt: int) -> bool:
     return kt not in (_cabi.F32, _cabi.F64)
 

@@ -600,7 +600,8 @@ class DeviceExchange:
                            if dist_path else mine)
                 boundaries = (SortTaskSpec.boundaries_from_samples(samples, sk, r_total)
                               if r_total > 1 else [])
-            boundaries = [(None,) if b is None else b for b in boundaries]
+            nkeys = len(sk.get_columns())
+            boundaries = [(None,) * nkeys if b is None else b for b in boundaries]
         else:
             boundaries = []
 
@@ -658,5 +659,6 @@ class DeviceExchange:
                 if key is not None:
                     SortKey(key).validate_schema(b.schema)
                 break
-        pruned = [agg.prune_columns(b, [key] if key is not None else [], aggs) for b in blocks]
-        return self.export(self.aggregate(self.stage(pruned), key, aggs, boundaries, seed, group))
+        pruned = [agg.prune_columns(b, agg.key_list(key), aggs) for b in blocks]
+        out = self.export(self.aggregate(self.stage(pruned), key, aggs, boundaries, seed, group))
+        return [agg.null_typed_like_reference(t) for t in out]

@@ -399,6 +399,33 @@ int xchg_dense_groups(const uint64_t* norm_keys, const uint8_t* validity, int64_
                       uint64_t n, uint64_t key_min, uint64_t range, void* workspace,
                       uint64_t workspace_bytes, uint32_t* row_gid_out, uint64_t* group_keys_out,
                       uint64_t* num_groups_out, void* stream);
+/*
+ * Grouping of SORTED rows, for any key: several key columns, string / binary keys.
+ * Replaces the run detection of ArrowBlockAccessor.combine (arrow_block.py:478-497: walk
+ * the sorted block, keys_equal with NaN == NaN and null as its own group) and of
+ * _get_block_boundaries (python/ray/data/block.py:515-592).  perm = the stable sort of the
+ * rows by the key columns (xchg_sort_column chained over the columns, string keys through
+ * xchg_string_* keys); flags = n bytes, zeroed by the caller.
+ *
+ * xchg_group_flags_fixed: flags[i] |= sorted row i differs from sorted row i-1 in this
+ *   column; norm_sorted = the column's radix keys in SORTED order (xchg_normalize_keys
+ *   with perm), validity (may be NULL) indexed by original row id.
+ * xchg_group_flags_bytes: the same for a variable-width column (int64 offsets + bytes).
+ * xchg_groups_from_flags: scan of the flags -> row_gid_out[original row] = group id in
+ *   key order, group_first_out[g] = original row id of group g's first row (the take index
+ *   of the output key columns).  perm NULL = identity (rows already sorted).  Synchronises
+ *   the stream (reads the group count).
+ */
+int xchg_group_flags_fixed(const uint64_t* norm_sorted, const uint8_t* validity,
+                           int64_t validity_bit_offset, const uint32_t* perm, uint64_t n,
+                           uint8_t* flags, void* stream);
+int xchg_group_flags_bytes(const int64_t* offsets, const uint8_t* data, const uint8_t* validity,
+                           int64_t validity_bit_offset, const uint32_t* perm, uint64_t n,
+                           uint8_t* flags, void* stream);
+int xchg_groups_from_flags_bytes(uint64_t n, uint64_t* bytes_out);
+int xchg_groups_from_flags(const uint8_t* flags, const uint32_t* perm, uint64_t n, void* workspace,
+                           uint64_t workspace_bytes, uint32_t* row_gid_out, uint32_t* group_first_out,
+                           uint64_t* num_groups_out, void* stream);
 /* order = permutation that sorts the group list (from xchg_sort_column);
  * row_gid_out[i] = position of row i's group in that order. */
 int xchg_group_ids(const uint32_t* order, const uint32_t* group_slots, uint64_t num_groups,

@@ -534,6 +534,52 @@ class FakeLib:
         ngroups._obj.value = g
         return 0
 
+    def xchg_group_flags_fixed(self, norm, validity, vbit, perm, n, flags, stream):
+        if n == 0:
+            return 0
+        k = _arr(norm, np.uint64, n)
+        fl = _arr(flags, np.uint8, n)
+        diff = np.ones(n, bool)
+        diff[1:] = k[1:] != k[:-1]
+        if _addr(validity):
+            p = _arr(perm, np.uint32, n).astype(np.int64)
+            v = _bits(validity, vbit, p)
+            diff[1:] |= v[1:] != v[:-1]
+        fl[diff] = 1
+        return 0
+
+    def xchg_group_flags_bytes(self, off, data, validity, vbit, perm, n, flags, stream):
+        if n == 0:
+            return 0
+        p = _arr(perm, np.uint32, n).astype(np.int64)
+        nrows = int(p.max()) + 1
+        rows = self._rows_bytes(off, data, nrows)
+        v = _bits(validity, vbit, p) if _addr(validity) else np.ones(n, bool)
+        fl = _arr(flags, np.uint8, n)
+        fl[0] = 1
+        for i in range(1, n):
+            a, b = int(p[i - 1]), int(p[i])
+            if v[i] != v[i - 1] or (v[i] and rows[a] != rows[b]):
+                fl[i] = 1
+        return 0
+
+    def xchg_groups_from_flags_bytes(self, n, out):
+        out._obj.value = (n // 4096 + 2) * 4 + 1024
+        return 0
+
+    def xchg_groups_from_flags(self, flags, perm, n, ws, wsb, rgid, first, ngroups, stream):
+        ngroups._obj.value = 0
+        if n == 0:
+            return 0
+        fl = _arr(flags, np.uint8, n).astype(np.int64)
+        gid = np.cumsum(fl) - 1
+        p = _arr(perm, np.uint32, n).astype(np.int64) if _addr(perm) else np.arange(n, dtype=np.int64)
+        _arr(rgid, np.uint32, n)[p] = gid.astype(np.uint32)
+        g = int(gid[-1]) + 1
+        _arr(first, np.uint32, g)[:] = p[fl == 1].astype(np.uint32)
+        ngroups._obj.value = g
+        return 0
+
     def xchg_agg_count_rows(self, rgid, n, num_groups, rows, stream):
         if n == 0:
             return 0

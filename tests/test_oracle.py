@@ -125,10 +125,16 @@ def test_golden_shuffle(case):
 def test_golden_aggregate(case):
     blocks = [G.load(n) for n in case["inputs"]]
     got = O.groupby_aggregate(blocks, case["key"], [tuple(a) for a in case["aggs"]])
-    exp = pa.concat_tables([t for t in (G.load(n) for n in case["outputs"]) if t.num_rows])
+    # (a block that holds only the null group has a null-typed key column in the reference:
+    # the concatenation promotes it back)
+    exp = pa.concat_tables([t for t in (G.load(n) for n in case["outputs"]) if t.num_rows],
+                           promote_options="permissive")
     assert got.schema.names == exp.schema.names
     for n in exp.schema.names:
         assert got[n].type == exp[n].type, n
+        if pa.types.is_string(exp[n].type) or pa.types.is_binary(exp[n].type):
+            assert got[n].to_pylist() == exp[n].to_pylist(), n
+            continue
         a, b = exp[n].to_numpy(), got[n].to_numpy()
         np.testing.assert_allclose(b, a, rtol=1e-12, atol=1e-12, equal_nan=True, err_msg=n)
 
