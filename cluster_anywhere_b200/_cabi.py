@@ -51,6 +51,7 @@ _SIGNATURES = {
                                   ctypes.POINTER(c_uint64), _P]),
     "xchg_group_flags_fixed": (c_int, [_P, _P, c_int64, _P, c_uint64, _P, _P]),
     "xchg_group_flags_bytes": (c_int, [_P, _P, _P, c_int64, _P, c_uint64, _P, _P]),
+    "xchg_group_first_rows": (c_int, [_P, c_uint64, c_uint64, _P, _P]),
     "xchg_groups_from_flags_bytes": (c_int, [c_uint64, ctypes.POINTER(c_uint64)]),
     "xchg_groups_from_flags": (c_int, [_P, _P, c_uint64, _P, c_uint64, _P, _P, ctypes.POINTER(c_uint64), _P]),
     "xchg_agg_count_rows": (c_int, [_P, c_uint64, c_uint64, _P, _P]),

@@ -522,3 +522,77 @@ def group_cut_points(rt: dev.Runtime, result: DeviceTable, key, boundaries: Sequ
     desc = [False] * len(cols)
     lower, upper, flags = keymod.normalize_boundaries(boundaries, ktypes, desc)
     return dev.partition_cuts(rt, norms, g, lower, upper, flags, desc, [t[0] for t in thr], [t[1] for t in thr])
+
+
+# ---------------------------------------------------------------------------
+# Group boundaries of a key-sorted block, distinct values
+# ---------------------------------------------------------------------------
+
+def block_boundaries(rt: dev.Runtime, table: DeviceTable, key_names: Sequence[str]) -> np.ndarray:
+    """Boundaries of the groups of a block that is SORTED by ``key_names``: the start index
+    of every group and ``num_rows`` at the end -- ``_get_block_boundaries``
+    (python/ray/data/block.py:515-592), which GroupedData.map_groups applies to every block
+    of the sorted dataset (grouped_data.py:196-213).  NaN == NaN and null == null, per column.
+    Run marks per key column in storage order (no permutation) + scan, on the device."""
+    n = table.num_rows
+    if n == 0:
+        return np.array([0, 0], dtype=int)
+    if not key_names:
+        return np.array([0, n], dtype=int)
+    flags = rt.zeros(n)
+    for name in key_names:
+        col = table.column(name)
+        if dev.is_string_key(col):
+            rt.call("xchg_group_flags_bytes", _vp(dev._string_offsets(rt, col)), _vp(col.data),
+                    _vp(col.validity), 0, None, n, _vp(flags), rt.stream)
+            continue
+        if col.kind != "fixed":
+            raise NotImplementedError(f"group key of type {col.type} is not supported by the B200 engine")
+        nk = rt.empty(n, torch.int64)
+        rt.call("xchg_normalize_keys", _vp(col.data), dev.key_type_of(col.type), 0, _vp(col.validity), 0, None, n,
+                _vp(nk), rt.stream)
+        rt.call("xchg_group_flags_fixed", _vp(nk), _vp(col.validity), 0, None, n, _vp(flags), rt.stream)
+    wsb = ctypes.c_uint64()
+    _cabi.check(_cabi.load().xchg_groups_from_flags_bytes(n, ctypes.byref(wsb)))
+    ws = rt.empty(wsb.value)
+    rgid = rt.empty(n, torch.int32)
+    first = rt.empty(n, torch.int32)
+    g_out = ctypes.c_uint64()
+    rt.call("xchg_groups_from_flags", _vp(flags), None, n, _vp(ws), wsb.value, _vp(rgid), _vp(first),
+            ctypes.byref(g_out), rt.stream, launches=3)
+    g = int(g_out.value)
+    starts = first[:g].cpu().numpy().view(np.uint32).astype(int)
+    return np.concatenate([starts, [n]]).astype(int)
+
+
+def _get_block_boundaries(columns: Sequence[np.ndarray]) -> np.ndarray:
+    """The reference's entry point (block.py:515): key columns of a sorted block as 1-D numpy
+    arrays (object arrays with None for strings, float arrays with NaN) -> boundaries."""
+    arrays = {}
+    for i, arr in enumerate(columns):
+        arr = np.asarray(arr)
+        if arr.dtype == object:
+            arrays[f"c{i}"] = pa.array(arr.tolist())
+        else:
+            arrays[f"c{i}"] = pa.array(arr)
+    table = pa.table(arrays)
+    rt = dev.default_runtime()
+    return block_boundaries(rt, dev.stage_table(rt, table), list(arrays))
+
+
+def unique_values(rt: dev.Runtime, table: DeviceTable, column: str) -> DeviceColumn:
+    """Distinct values of one column in ascending order, null last when present
+    (``Dataset.unique`` -> ``Unique`` aggregate, python/ray/data/dataset.py:2182-2221,
+    aggregate.py:445-489: ``pac.unique`` per block, set union across blocks)."""
+    n = table.num_rows
+    kc = table.column(column)
+    if n == 0:
+        return kc
+    if kc.kind == "fixed":
+        rgid, sorted_keys, g, kt = group_rows(rt, kc, n)
+        # first row of every group: any row will do, the values are equal
+        first = rt.empty(g, torch.int32)
+        rt.call("xchg_group_first_rows", _vp(rgid), n, g, _vp(first), rt.stream)
+    else:
+        rgid, g, first = group_rows_sorted(rt, table, [column])
+    return dev.take_column(rt, kc, first, g)

@@ -251,6 +251,31 @@ class B200ArrowBlockAccessor:
 
         return self._reduce(agg.KIND_MEAN, on, ignore_nulls)
 
+    def get_block_boundaries(self, keys) -> "np.ndarray":
+        """Group boundaries of this block, which must be sorted by ``keys`` (a column name
+        or a list): ``_get_block_boundaries`` (python/ray/data/block.py:515-592) as
+        GroupedData.map_groups uses it (grouped_data.py:196-213)."""
+        from . import aggregate as agg
+
+        keys = agg.key_list(keys)
+        if self.num_rows() == 0:
+            return np.array([0, 0], dtype=int)
+        rt = self.rt
+        return agg.block_boundaries(rt, dev.stage_table(rt, self._table.select(keys)), keys)
+
+    def unique(self, column: str) -> list:
+        """Distinct values of ``column`` (``pac.unique`` of the reference's Unique aggregate,
+        python/ray/data/aggregate.py:468-472), ascending, null last."""
+        from . import aggregate as agg
+
+        if self.num_rows() == 0:
+            return []
+        rt = self.rt
+        dt = dev.stage_table(rt, self._table.select([column]))
+        col = agg.unique_values(rt, dt, column)
+        out = dev.export_table(rt, dev.DeviceTable([column], [col], col.n, pa.schema([(column, col.type)])))
+        return out[column].to_pylist()
+
     @staticmethod
     def _group_key(sort_key: SortKey):
         """None (one global group), a column name, or the list of key columns."""

@@ -712,7 +712,8 @@ k_group_flags_fixed(const uint64_t* __restrict__ norm, const uint8_t* __restrict
     if (!diff) {
       diff = norm[i] != norm[i - 1];
       if (!diff && validity)
-        diff = bit_is_set(validity, (int64_t)perm[i] + vbit) != bit_is_set(validity, (int64_t)perm[i - 1] + vbit);
+        diff = bit_is_set(validity, (int64_t)(perm ? perm[i] : (uint32_t)i) + vbit) !=
+               bit_is_set(validity, (int64_t)(perm ? perm[i - 1] : (uint32_t)(i - 1)) + vbit);
     }
     if (diff) flags[i] = 1;
   }
@@ -728,7 +729,7 @@ k_group_flags_bytes(const int64_t* __restrict__ offsets, const uint8_t* __restri
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     bool diff = i == 0;
     if (!diff) {
-      const uint32_t a = perm[i - 1], b = perm[i];
+      const uint32_t a = perm ? perm[i - 1] : (uint32_t)(i - 1), b = perm ? perm[i] : (uint32_t)i;
       const bool va = validity ? bit_is_set(validity, (int64_t)a + vbit) : true;
       const bool vb = validity ? bit_is_set(validity, (int64_t)b + vbit) : true;
       if (va != vb) {
@@ -783,6 +784,13 @@ k_groups_emit(const uint8_t* __restrict__ flags, uint64_t n, const uint32_t* __r
       if (b[j]) group_first[r - 1] = row;
     }
   }
+}
+
+__global__ void __launch_bounds__(AG_THREADS)
+k_group_first_rows(const uint32_t* __restrict__ rgid, uint64_t n, uint32_t* __restrict__ first) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    atomicMin(&first[rgid[i]], (uint32_t)i);
 }
 
 bool key_type_is_int(int t) { return t >= XCHG_I8 && t <= XCHG_U64; }
@@ -961,7 +969,6 @@ extern "C" int xchg_group_flags_fixed(const uint64_t* norm_sorted, const uint8_t
   cudaStream_t s = (cudaStream_t)stream;
   if (n == 0) return XCHG_OK;
   XCHG_REQUIRE(norm_sorted && flags, "NULL keys / flags");
-  XCHG_REQUIRE(!validity || perm, "validity needs the permutation");
   XCHG_LAUNCH(XK_AGGREGATE, s, k_group_flags_fixed<<<ag_grid(n), AG_THREADS, 0, s>>>(
       norm_sorted, validity, validity_bit_offset, perm, n, flags));
   XCHG_LAUNCH_CHECK();
@@ -973,9 +980,22 @@ extern "C" int xchg_group_flags_bytes(const int64_t* offsets, const uint8_t* dat
                                       uint8_t* flags, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
   if (n == 0) return XCHG_OK;
-  XCHG_REQUIRE(offsets && perm && flags, "NULL offsets / perm / flags");
+  XCHG_REQUIRE(offsets && flags, "NULL offsets / flags");
   XCHG_LAUNCH(XK_AGGREGATE, s, k_group_flags_bytes<<<ag_grid(n), AG_THREADS, 0, s>>>(
       offsets, data, validity, validity_bit_offset, perm, n, flags));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+extern "C" int xchg_group_first_rows(const uint32_t* row_gid, uint64_t n, uint64_t num_groups,
+                                     uint32_t* first_out, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  if (num_groups == 0) return XCHG_OK;
+  XCHG_REQUIRE(first_out != nullptr, "NULL first_out");
+  XCHG_CUDA_TRY(cudaMemsetAsync(first_out, 0xFF, num_groups * 4, s));
+  if (n == 0) return XCHG_OK;
+  XCHG_REQUIRE(row_gid != nullptr, "NULL row_gid");
+  XCHG_LAUNCH(XK_AGGREGATE, s, k_group_first_rows<<<ag_grid(n), AG_THREADS, 0, s>>>(row_gid, n, first_out));
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
 }

@@ -645,6 +645,19 @@ class DeviceExchange:
         local_bounds = list(boundaries[int(ob[rank]):int(ob[rank + 1]) - 1])
         return DeviceDataset(out, cut_ranges(out, local_bounds, my_blocks))
 
+    def unique_blocks(self, blocks: Sequence[pa.Table], column: str) -> list:
+        """``Dataset.unique(column)`` (python/ray/data/dataset.py:2182-2221) over host blocks on
+        this rank: the distinct values of the column, ascending, null last."""
+        from .. import aggregate as agg
+
+        nonempty = [b.select([column]) for b in blocks if b.num_rows > 0 and b.num_columns > 0]
+        if not nonempty:
+            return []
+        ds = self.stage(nonempty)
+        col = agg.unique_values(self.rt, ds.table, column)
+        t = dev.export_table(self.rt, dev.DeviceTable([column], [col], col.n, pa.schema([(column, col.type)])))
+        return t[column].to_pylist()
+
     def aggregate_blocks(self, blocks: Sequence[pa.Table], key: Optional[str], aggs: Sequence,
                          boundaries: Optional[list] = None, seed: int = 0, group=None) -> List[pa.Table]:
         """Host blocks in, aggregated host blocks out (this rank's run when distributed).

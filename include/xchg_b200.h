@@ -405,7 +405,9 @@ int xchg_dense_groups(const uint64_t* norm_keys, const uint8_t* validity, int64_
  * the sorted block, keys_equal with NaN == NaN and null as its own group) and of
  * _get_block_boundaries (python/ray/data/block.py:515-592).  perm = the stable sort of the
  * rows by the key columns (xchg_sort_column chained over the columns, string keys through
- * xchg_string_* keys); flags = n bytes, zeroed by the caller.
+ * xchg_string_* keys), or NULL when the rows are stored in key order already (the block of
+ * a sorted dataset: GroupedData.map_groups, grouped_data.py:196-213); flags = n bytes,
+ * zeroed by the caller.
  *
  * xchg_group_flags_fixed: flags[i] |= sorted row i differs from sorted row i-1 in this
  *   column; norm_sorted = the column's radix keys in SORTED order (xchg_normalize_keys
@@ -426,6 +428,11 @@ int xchg_groups_from_flags_bytes(uint64_t n, uint64_t* bytes_out);
 int xchg_groups_from_flags(const uint8_t* flags, const uint32_t* perm, uint64_t n, void* workspace,
                            uint64_t workspace_bytes, uint32_t* row_gid_out, uint32_t* group_first_out,
                            uint64_t* num_groups_out, void* stream);
+/* first_out[g] = smallest row index whose group id is g (row_gid from any of the grouping
+ * front ends): the row to take a group's key value from.  Dataset.unique
+ * (python/ray/data/dataset.py:2182-2221) is this + a take of the column. */
+int xchg_group_first_rows(const uint32_t* row_gid, uint64_t n, uint64_t num_groups, uint32_t* first_out,
+                          void* stream);
 /* order = permutation that sorts the group list (from xchg_sort_column);
  * row_gid_out[i] = position of row i's group in that order. */
 int xchg_group_ids(const uint32_t* order, const uint32_t* group_slots, uint64_t num_groups,

@@ -107,6 +107,19 @@ def main():
         if bounds is not None:
             ks = [g["k"].to_pylist() for g in got]
             assert all(k is None or k < -20 for k in ks[0]) and all(-20 <= k < 0 for k in ks[1])
+    # general keys (string key; int + string): sorted grouping, partials with string key
+    # columns over the exchange, mixed-key splitters
+    for gkey in ("s", ["k", "s"]):
+        aggs2 = [Count(), Sum("f"), Mean("f")]
+        exp2 = O.groupby_aggregate(all_blocks, gkey, [("count",), ("sum", "f"), ("mean", "f")])
+        out = ex.aggregate_blocks(mine, gkey, aggs2, seed=2)
+        outs = [None] * w
+        dist.all_gather_object(outs, out)
+        got = [b for part in outs for b in part]
+        assert len(got) == len(all_blocks)
+        keys = tuple([gkey] if isinstance(gkey, str) else gkey)
+        assert_tables_close(pa.concat_tables([g for g in got if g.num_rows], promote_options="permissive"),
+                            exp2, exact=keys)
     out = ex.aggregate_blocks(mine, None, [Count(), Sum("k")])
     outs = [None] * w
     dist.all_gather_object(outs, out)

@@ -542,7 +542,7 @@ class FakeLib:
         diff = np.ones(n, bool)
         diff[1:] = k[1:] != k[:-1]
         if _addr(validity):
-            p = _arr(perm, np.uint32, n).astype(np.int64)
+            p = _arr(perm, np.uint32, n).astype(np.int64) if _addr(perm) else np.arange(n, dtype=np.int64)
             v = _bits(validity, vbit, p)
             diff[1:] |= v[1:] != v[:-1]
         fl[diff] = 1
@@ -551,7 +551,7 @@ class FakeLib:
     def xchg_group_flags_bytes(self, off, data, validity, vbit, perm, n, flags, stream):
         if n == 0:
             return 0
-        p = _arr(perm, np.uint32, n).astype(np.int64)
+        p = _arr(perm, np.uint32, n).astype(np.int64) if _addr(perm) else np.arange(n, dtype=np.int64)
         nrows = int(p.max()) + 1
         rows = self._rows_bytes(off, data, nrows)
         v = _bits(validity, vbit, p) if _addr(validity) else np.ones(n, bool)
@@ -561,6 +561,15 @@ class FakeLib:
             a, b = int(p[i - 1]), int(p[i])
             if v[i] != v[i - 1] or (v[i] and rows[a] != rows[b]):
                 fl[i] = 1
+        return 0
+
+    def xchg_group_first_rows(self, rgid, n, g, first, stream):
+        if g == 0:
+            return 0
+        out = _arr(first, np.uint32, g)
+        out[:] = 0xFFFFFFFF
+        if n:
+            np.minimum.at(out, _arr(rgid, np.uint32, n).astype(np.int64), np.arange(n, dtype=np.uint32))
         return 0
 
     def xchg_groups_from_flags_bytes(self, n, out):
