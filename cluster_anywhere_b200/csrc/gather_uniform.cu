@@ -47,21 +47,49 @@ __device__ __forceinline__ uint32_t udiv_magic(uint32_t x, uint32_t magic) {
   return magic ? __umulhi(x, magic) : x;
 }
 
-template <bool VEC16>
+// Several output segments in ONE launch (the multi-GPU exchange: segment d = the rows this
+// rank sends to destination d, out[d] = a pointer into that peer's arena).  The tiles of
+// the segments are interleaved (tile r of every segment, then tile r+1, ...), so a rank
+// stores to all its peers at once and every GPU's NVLink ingress is shared evenly by all
+// senders for the whole kernel, whatever the ranks' relative progress -- one launch per
+// destination leaves that to chance.
+constexpr int GU_MAX_SEGS = 16;
+struct GatherSegs {
+  uint64_t row0[GU_MAX_SEGS];  // first entry of the segment in idx
+  uint64_t n[GU_MAX_SEGS];     // rows
+  uint8_t* out[GU_MAX_SEGS];
+  int nseg;
+};
+
+template <bool VEC16, bool MULTI>
 __global__ void __launch_bounds__(GU_THREADS)
-k_gather_rows_uniform(const uint8_t* __restrict__ in, uint32_t w, const uint32_t* __restrict__ idx,
-                      uint64_t n_out, uint8_t* __restrict__ out, uint32_t rows_per_tile,
-                      uint32_t slot, uint32_t magic_w, uint32_t magic_cpr) {
+k_gather_rows_uniform(const uint8_t* __restrict__ in, uint32_t w, const uint32_t* __restrict__ idx_,
+                      uint64_t n_out_, uint8_t* __restrict__ out_, uint32_t rows_per_tile,
+                      uint32_t slot, uint32_t magic_w, uint32_t magic_cpr, GatherSegs segs,
+                      uint64_t max_tiles) {
   extern __shared__ __align__(16) uint8_t smem[];
   uint8_t* stage = smem;
   int64_t* m_src = reinterpret_cast<int64_t*>(smem + GU_STAGE + 32);
   uint32_t* m_a0 = reinterpret_cast<uint32_t*>(m_src + GU_MAX_ROWS);
   const uint32_t stage_s = (uint32_t)__cvta_generic_to_shared(stage);
   const int tid = threadIdx.x;
-  const uint64_t ntiles = (n_out + rows_per_tile - 1) / rows_per_tile;
   const uint32_t cpr = slot >> 4;  // 16-byte chunks per slot
+  const uint64_t nwork = MULTI ? max_tiles * (uint64_t)segs.nseg
+                               : (n_out_ + rows_per_tile - 1) / rows_per_tile;
 
-  for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+  for (uint64_t work = blockIdx.x; work < nwork; work += gridDim.x) {
+    const uint32_t* idx = idx_;
+    uint64_t n_out = n_out_;
+    uint8_t* out = out_;
+    uint64_t tile = work;
+    if constexpr (MULTI) {
+      const int sg = (int)(work % (uint64_t)segs.nseg);
+      tile = work / (uint64_t)segs.nseg;
+      idx = idx_ + segs.row0[sg];
+      n_out = segs.n[sg];
+      out = segs.out[sg];
+      if (tile * rows_per_tile >= n_out) continue;  // uniform per CTA: no barrier is skipped
+    }
     const uint64_t r0 = tile * rows_per_tile;
     const uint32_t T = (uint32_t)min((uint64_t)rows_per_tile, n_out - r0);
 
@@ -185,17 +213,30 @@ k_gather_rows_uniform(const uint8_t* __restrict__ in, uint32_t w, const uint32_t
 
 }  // namespace
 
-int xchg_internal_gather_rows_uniform(const uint8_t* in, uint32_t w, const uint32_t* idx,
-                                      uint64_t n_out, uint8_t* out, cudaStream_t s) {
+static GatherSegs no_segs() {
+  GatherSegs g;
+  g.nseg = 0;
+  return g;
+}
+
+static int gather_uniform_launch(const uint8_t* in, uint32_t w, const uint32_t* idx, uint64_t n_out,
+                                 uint8_t* out, const GatherSegs* multi, cudaStream_t s) {
   static bool attr_done = false;
   if (!attr_done) {
-    XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<false>,
+    XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<false, false>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GU_SMEM));
-    XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<true>,
+    XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<true, false>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GU_SMEM));
+    XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<false, true>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GU_SMEM));
+    XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<true, true>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GU_SMEM));
     attr_done = true;
   }
-  const bool vec16 = (w % 16 == 0) && ((((uintptr_t)in) | ((uintptr_t)out)) % 16 == 0);
+  uintptr_t align_bits = (uintptr_t)in | (uintptr_t)out;
+  if (multi)
+    for (int d = 0; d < multi->nseg; ++d) align_bits |= (uintptr_t)multi->out[d];
+  const bool vec16 = (w % 16 == 0) && (align_bits % 16 == 0);
   const uint32_t slot = vec16 ? w : ((w + 15u + 15u) & ~15u);
   const uint32_t rpt = std::min<uint32_t>(GU_MAX_ROWS, GU_STAGE / slot);
   if (rpt == 0) return 1;  // row wider than the stage: caller takes the generic path
@@ -203,17 +244,60 @@ int xchg_internal_gather_rows_uniform(const uint8_t* in, uint32_t w, const uint3
   // exact for every dividend below 2^32 / divisor, which bounds all uses (tile bytes, chunks)
   const uint32_t magic_w = w == 1 ? 0u : (uint32_t)((0x100000000ull + w - 1) / w);
   const uint32_t magic_cpr = cpr == 1 ? 0u : (uint32_t)((0x100000000ull + cpr - 1) / cpr);
-  const uint64_t ntiles = (n_out + rpt - 1) / rpt;
+  uint64_t ntiles = (n_out + rpt - 1) / rpt;
+  uint64_t max_tiles = 0;
+  if (multi) {
+    for (int d = 0; d < multi->nseg; ++d) max_tiles = std::max<uint64_t>(max_tiles, (multi->n[d] + rpt - 1) / rpt);
+    ntiles = max_tiles * (uint64_t)multi->nseg;
+    if (ntiles == 0) return XCHG_OK;
+  }
   // persistent CTAs (3 resident per SM, 8 waves of tiles each by default); a cap leaves
   // SMs' shared memory to kernels running beside a link-bound peer-store gather
   const int cap = xchg_gather_ctas_per_sm();
   const int grid = (int)std::min<uint64_t>(ntiles, (uint64_t)xchg_sm_count() * (cap ? cap : 3 * 8));
-  if (vec16)
-    XCHG_LAUNCH(XK_GATHER_ROWS, s, k_gather_rows_uniform<true><<<grid, GU_THREADS, GU_SMEM, s>>>(
-        in, w, idx, n_out, out, rpt, slot, magic_w, magic_cpr));
-  else
-    XCHG_LAUNCH(XK_GATHER_ROWS, s, k_gather_rows_uniform<false><<<grid, GU_THREADS, GU_SMEM, s>>>(
-        in, w, idx, n_out, out, rpt, slot, magic_w, magic_cpr));
+  const GatherSegs sg = multi ? *multi : no_segs();
+#define XCHG_GU_LAUNCH(VEC, MULTI)                                                                   \
+  XCHG_LAUNCH(XK_GATHER_ROWS, s,                                                                     \
+              k_gather_rows_uniform<VEC, MULTI><<<grid, GU_THREADS, GU_SMEM, s>>>(                    \
+                  in, w, idx, n_out, out, rpt, slot, magic_w, magic_cpr, sg, max_tiles))
+  if (multi) {
+    if (vec16) XCHG_GU_LAUNCH(true, true);
+    else XCHG_GU_LAUNCH(false, true);
+  } else {
+    if (vec16) XCHG_GU_LAUNCH(true, false);
+    else XCHG_GU_LAUNCH(false, false);
+  }
+#undef XCHG_GU_LAUNCH
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
+}
+
+int xchg_internal_gather_rows_uniform(const uint8_t* in, uint32_t w, const uint32_t* idx,
+                                      uint64_t n_out, uint8_t* out, cudaStream_t s) {
+  return gather_uniform_launch(in, w, idx, n_out, out, nullptr, s);
+}
+
+extern "C" int xchg_gather_rows_multi(const void* in, uint32_t row_bytes, const uint32_t* idx, int nseg,
+                                      const uint64_t* seg_row0_host, const uint64_t* seg_rows_host,
+                                      void* const* seg_out_host, void* stream) {
+  if (nseg == 0) return XCHG_OK;
+  XCHG_REQUIRE(nseg > 0 && nseg <= GU_MAX_SEGS, "nseg must be in [1, %d]", GU_MAX_SEGS);
+  XCHG_REQUIRE(in && idx && seg_row0_host && seg_rows_host && seg_out_host, "NULL argument");
+  XCHG_REQUIRE(row_bytes > 0, "row_bytes must be positive");
+  GatherSegs g;
+  g.nseg = nseg;
+  for (int d = 0; d < nseg; ++d) {
+    XCHG_REQUIRE(seg_rows_host[d] == 0 || seg_out_host[d], "NULL output of segment %d", d);
+    XCHG_REQUIRE(seg_rows_host[d] <= XCHG_MAX_ROWS, "segment %d exceeds XCHG_MAX_ROWS", d);
+    g.row0[d] = seg_row0_host[d];
+    g.n[d] = seg_rows_host[d];
+    g.out[d] = (uint8_t*)seg_out_host[d];
+  }
+  const int rc = gather_uniform_launch((const uint8_t*)in, row_bytes, idx, 0, nullptr, &g, (cudaStream_t)stream);
+  if (rc == 1) {
+    xchg_set_error("rows of %u bytes exceed the staging tile of xchg_gather_rows_multi; gather the "
+                   "segments one by one with xchg_gather_rows", row_bytes);
+    return XCHG_ERR_LIMIT;
+  }
+  return rc;
 }

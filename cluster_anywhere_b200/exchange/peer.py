@@ -179,8 +179,25 @@ def store_columns(rt: dev.Runtime, pl: ExchangePlan, cols: Sequence[int]) -> Non
         # rank stores into a different peer, so each GPU's NVLink ingress serves one
         # sender at a time instead of all G-1 at once (in plain 0..G-1 order every rank
         # hits destination 0 together, then 1, ...: an 8-GPU step took 95 ms)
-        for step in range(G):
-            d = (rank + 1 + step) % G
+        order = [(rank + 1 + step) % G for step in range(G)]
+        multi = (c.kind == "var" and uniform is not None and uniform > 0 and G <= 16
+                 and os.environ.get("XCHG_MULTI_STORE", "1") == "1")
+        if multi:
+            # ONE launch storing to every destination at once (tiles of the destinations
+            # interleaved): each peer's ingress is shared evenly by all senders throughout
+            dests = [d for d in order if int(pl.send_counts[d]) > 0]
+            if dests:
+                row0 = (ctypes.c_uint64 * len(dests))(*[int(pl.cuts[d]) for d in dests])
+                rows = (ctypes.c_uint64 * len(dests))(*[int(pl.send_counts[d]) for d in dests])
+                outs = (ctypes.c_void_p * len(dests))(*[
+                    int(arena.ptrs[d]) + pl.offsets_of[d][(j, "data")] + int(pl.prefix_rows[rank, d]) * uniform
+                    for d in dests])
+                try:
+                    rt.call("xchg_gather_rows_multi", _vp(c.data), uniform, _ptr(perm_ptr), len(dests), row0, rows,
+                            outs, rt.stream)
+                except dev.XchgError:
+                    multi = False  # rows wider than the staging tile: one launch per destination
+        for d in order:
             k = int(pl.send_counts[d])
             if k == 0:
                 continue
@@ -202,8 +219,9 @@ def store_columns(rt: dev.Runtime, pl: ExchangePlan, cols: Sequence[int]) -> Non
             elif c.kind == "bits":
                 rt.call("xchg_gather_bitmap_bytes", _vp(c.data), 0, idx, k, _ptr(base, data_off + pre), rt.stream)
             elif uniform is not None:
-                rt.call("xchg_gather_rows", _vp(c.data), uniform, idx, k, _ptr(base, data_off + pre * uniform),
-                        rt.stream)
+                if not multi:
+                    rt.call("xchg_gather_rows", _vp(c.data), uniform, idx, k, _ptr(base, data_off + pre * uniform),
+                            rt.stream)
             else:
                 pre_bytes = int(M[:rank, d, 1 + 3 * j].sum())
                 if c.uniform is not None:  # uniform here, ragged elsewhere

@@ -294,6 +294,16 @@ int xchg_gather_bytes(const uint8_t* in_data, const int64_t* in_off, const uint3
                       void* stream);
 /* Uniform-width rows (every row `width` bytes; GraySort payload, tensor rows):
  * out row i = in row idx[i]; no offsets are read. */
+/* xchg_gather_rows_multi: the same for up to 16 output segments in ONE launch: segment d
+ * takes idx[seg_row0[d] .. seg_row0[d] + seg_rows[d]) and writes seg_out[d] (HOST arrays of
+ * nseg entries; seg_out[d] may point into a peer GPU's memory).  The segments' tiles are
+ * interleaved so that all outputs are written at the same pace: the multi-GPU exchange's
+ * stores reach every peer at once instead of one destination after the other.  Replaces the
+ * per-reducer transfers of pull_based_shuffle_task_scheduler.py:84-120 like xchg_gather_rows
+ * into a peer arena does.  XCHG_ERR_LIMIT when a row does not fit the staging tile (~56 KB). */
+int xchg_gather_rows_multi(const void* in_data, uint32_t width, const uint32_t* idx, int nseg,
+                           const uint64_t* seg_row0_host, const uint64_t* seg_rows_host,
+                           void* const* seg_out_host, void* stream);
 int xchg_gather_rows(const uint8_t* in_data, uint32_t width, const uint32_t* idx,
                      uint64_t n_out, uint8_t* out_data, void* stream);
 

@@ -227,6 +227,13 @@ class FakeLib:
     def xchg_gather_rows(self, inp, width, idx, n, out, stream):
         return self.xchg_gather_fixed(inp, width, idx, n, out, stream)
 
+    def xchg_gather_rows_multi(self, inp, width, idx, nseg, row0, rows, outs, stream):
+        for d in range(nseg):
+            if rows[d]:
+                ix = ctypes.c_void_p(_addr(idx) + 4 * int(row0[d]))
+                self.xchg_gather_fixed(inp, width, ix, int(rows[d]), ctypes.c_void_p(outs[d]), stream)
+        return 0
+
     def xchg_gather_bitmap(self, inp, bit_off, idx, n, out, null_count, stream):
         if n == 0:
             return 0
