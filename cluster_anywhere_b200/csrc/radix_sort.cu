@@ -179,12 +179,15 @@ __device__ __forceinline__ uint32_t digit_of(uint64_t key, uint32_t val, int shi
 // ~1.2 ms per 125 M rows), whereas the votes and logic ops spread over the four
 // schedulers' ordinary pipes.
 __device__ __forceinline__ unsigned match_digit(uint32_t d) {
+  // Per bit: test, ballot, select the all-ones / zero mask, one LOP3 for m &= v ^ mask
+  // (ptxas emits six instructions per bit for this; a hand-written four-instruction PTX
+  // sequence assembles in isolation but fails register allocation inside these kernels).
   unsigned m = 0xffffffffu;
 #pragma unroll
   for (int b = 0; b < 8; ++b) {
-    const bool p = (d >> b) & 1u;
+    const bool p = (d & (1u << b)) != 0u;
     const unsigned v = __ballot_sync(0xffffffffu, p);
-    m &= p ? v : ~v;
+    m &= v ^ (p ? 0u : 0xffffffffu);
   }
   return m;
 }
