@@ -50,6 +50,32 @@ def timed(fn, steps, warmup, lib):
     return e0.elapsed_time(e1) / steps, ks
 
 
+def range_sort(args, rt, ex, lib, peak):
+    """configs[0]: ray.data.range(10_000_000).sort('id', descending=True): one int64 column in 76
+    blocks (what _autodetect_parallelism gives on an 8-CPU host), ascending input and a
+    shuffled variant.  80 MB: launch- and latency-bound on a B200; reported, not tuned for."""
+    import pyarrow as pa
+    import torch
+
+    from cluster_anywhere_b200 import SortKey
+    from cluster_anywhere_b200 import device as dev
+    from cluster_anywhere_b200.exchange import DeviceDataset
+
+    n, blocks = 10_000_000, 76
+    for name, ids in (("ascending input", torch.arange(n, dtype=torch.int64, device=rt.device)),
+                      ("shuffled input (seed 1)", torch.randperm(n, device=rt.device,
+                                                                 generator=torch.Generator(device=rt.device).manual_seed(1)))):
+        col = dev.DeviceColumn(pa.int64(), n, "fixed", 8, ids.view(torch.uint8))
+        table = dev.DeviceTable(["id"], [col], n, pa.schema([("id", pa.int64())]))
+        ds = DeviceDataset(table, [(i * n // blocks, (i + 1) * n // blocks) for i in range(blocks)])
+        sk = SortKey("id", descending=True)
+        ms, ks = timed(lambda i: ex.sort(ds, sk, seed=i), args.steps, args.warmup, lib)
+        gbs = 2 * n * 8 / ms / 1e6
+        print(json.dumps({"op": "sort(range)", "workload": f"range({n}).sort('id', descending=True), {blocks} blocks, "
+                          f"{name}: BASELINE configs[0]", "ms_per_step": ms, "rows_per_s": n / ms * 1e3,
+                          "gb_per_s_algorithmic": gbs, "frac_of_measured_hbm": gbs / peak, "kernels": ks}), flush=True)
+
+
 def string_sort(args, rt, ex, lib, peak):
     """configs[4] at a stated sub-scale: Dataset.sort on a string key drawn Zipf(1.2) from a
     vocabulary of 8..31-byte strings, with a 16..256-byte binary payload."""
@@ -127,6 +153,8 @@ def main():
         os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
 
     only = set(x for x in args.only.split(",") if x)
+    if not only or "c1" in only:
+        range_sort(args, rt, ex, lib, peak)
     if not only or "strings" in only:
         string_sort(args, rt, ex, lib, peak)
     if only and "shuffle" not in only and "aggregate" not in only:
