@@ -30,6 +30,7 @@ def make_block(rng, n):
         "s": pa.array(s, pa.string()),
         "b": pa.array(rng.random(n) < 0.5),
         "p": pa.array([bytes(rng.integers(0, 256, 10, dtype=np.uint8)) for _ in range(n)], pa.binary()),
+        "q": pa.array([bytes(rng.integers(0, 256, 48, dtype=np.uint8)) for _ in range(n)], pa.binary()),
     })
 
 

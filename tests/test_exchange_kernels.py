@@ -136,6 +136,9 @@ def test_single_rank_map_exchange_reduce(engine, cols, desc):
             t = t.append_column("b", pa.array(rng.random(n) < 0.5))
             t = t.append_column("p", pa.array([bytes(rng.integers(0, 256, 12, dtype=np.uint8))
                                                for _ in range(n)], pa.binary()))
+            # 32-byte rows: the 16-byte-vector variant of the (multi-destination) row gather
+            t = t.append_column("q", pa.array([bytes(rng.integers(0, 256, 32, dtype=np.uint8))
+                                               for _ in range(n)], pa.binary()))
             blocks.append(t)
         ex = DeviceExchange()
         sk = SortKey(cols, desc)
