@@ -26,7 +26,7 @@ class SortAggregateTaskSpec(ExchangeTaskSpec):
             aggs: list) -> list:
         """aggregate_task_spec.py:38-59.  The reference sorts the block, slices it at the
         boundaries and combines every slice; the groups of different slices are
-        disjoint key ranges, so ONE hash aggregate of the whole block (K8, output
+        disjoint key ranges, so ONE group aggregate of the whole block (K8, output
         sorted by key) cut at the same boundaries (K4) yields the same R partial
         blocks."""
         stats = BlockExecStats.builder()

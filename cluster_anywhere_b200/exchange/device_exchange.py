@@ -557,8 +557,9 @@ class DeviceExchange:
         under the pull- or push-based schedule.  The result is fully determined: one row
         per distinct key, sorted by key, cut into R range partitions by the boundaries.
 
-        One GPU: ONE hash aggregate over all resident rows (K8) and the boundary search
-        over the sorted groups (K4).  G GPUs: local hash aggregate -> partial rows (one
+        One GPU: ONE group aggregate over all resident rows (K8: direct-address, hash or
+        sorted grouping by key type) and the boundary search
+        over the sorted groups (K4).  G GPUs: local aggregate -> partial rows (one
         per local group) -> range split by the G-1 splitters (K4) -> all-to-all-v of the
         partials over NVLink (a few bytes per GROUP, not per row) -> merge (K9) ->
         finalize -> this rank's run of output blocks."""
