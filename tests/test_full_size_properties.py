@@ -85,3 +85,79 @@ def test_graysort_shard_full_size_properties():
     again = ex.sort(DeviceDataset(out.table, out.block_ranges), sk, boundaries=[], seed=1)
     assert torch.equal(again.table.column("c_1").data[: N * W], out.table.column("c_1").data[: N * W])
     assert torch.equal(again.table.column("c_0").data.view(torch.int64)[:N], ok)
+
+
+def test_random_shuffle_shard_full_size_properties():
+    """configs[2] per-GPU shard: 25 M rows of 1 KiB.  The output is a permutation of the input
+    rows (every row carries its id), rows stay intact, the same seed gives the same output,
+    another seed a different one, and the rows of an input block do not stay together."""
+    rt = dev.default_runtime()
+    n, w = 25_000_000, 1024
+    data = torch.empty(n * w + 64, dtype=torch.uint8, device=rt.device)[: n * w]
+    words = data.view(torch.int64).view(n, w // 8)
+    ids = torch.arange(n, dtype=torch.int64, device=rt.device)
+    words[:] = ids[:, None]                      # every 8-byte word of row i holds i ...
+    words[:, 1] = ids * 0x9E3779B97F4A7C15 % (2**62)  # ... but word 1: a hash of i
+    typ = pa.large_list(pa.uint8())
+    col = dev.DeviceColumn(typ, n, "var", 1, data, None, None, 0, uniform=w)
+    table = dev.DeviceTable(["data"], [col], n, pa.schema([("data", typ)]))
+    blocks = 24
+    ds = DeviceDataset(table, [(i * n // blocks, (i + 1) * n // blocks) for i in range(blocks)])
+    ex = DeviceExchange(rt)
+    out = ex.random_shuffle(ds, 42)
+    assert out.num_rows == n and len(out.block_ranges) == blocks
+    ow = out.table.column("data").data[: n * w].view(torch.int64).view(n, w // 8)
+    got = ow[:, 0].clone()
+    assert bool((ow[:, 5] == got).all()) and bool((ow[:, 127] == got).all()), "row torn"
+    assert bool((ow[:, 1] == got * 0x9E3779B97F4A7C15 % (2**62)).all()), "row torn"
+    assert bool((torch.sort(got).values == ids).all()), "not a permutation of the input rows"
+    # rows of input block 0 are spread over the output, not contiguous
+    first_block = (got < n // blocks)
+    per_out_block = torch.stack([first_block[lo:hi].sum() for lo, hi in out.block_ranges]).cpu().numpy()
+    assert per_out_block.min() > 0 and per_out_block.max() < 2 * (n // blocks) // blocks
+    del out, ow
+    again = ex.random_shuffle(ds, 42).table.column("data").data[: n * w].view(torch.int64).view(n, w // 8)[:, 0]
+    assert torch.equal(again, got), "same seed, different output"
+    del again
+    other = ex.random_shuffle(ds, 43).table.column("data").data[: n * w].view(torch.int64).view(n, w // 8)[:, 0]
+    assert not torch.equal(other, got)
+
+
+def test_groupby_aggregate_shard_full_size_properties():
+    """configs[3] per-GPU shard: 250 M rows, int32 key with 10 M distinct values, float32 value,
+    Sum / Mean / Count.  Counts add up to the row count and equal a torch.bincount of the keys,
+    the group keys are the sorted distinct keys, sums match an fp64 index_add within 1e-6
+    relative (the stated tolerance), mean = sum / count."""
+    from cluster_anywhere_b200 import Count, Mean, Sum
+
+    rt = dev.default_runtime()
+    n, g = 250_000_000, 10_000_000
+    gen = torch.Generator(device=rt.device)
+    gen.manual_seed(4)
+    k = torch.randint(0, g, (n,), dtype=torch.int32, device=rt.device, generator=gen)
+    v = torch.randn(n, dtype=torch.float32, device=rt.device, generator=gen)
+    kc = dev.DeviceColumn(pa.int32(), n, "fixed", 4, k.view(torch.uint8))
+    vc = dev.DeviceColumn(pa.float32(), n, "fixed", 4, v.view(torch.uint8))
+    table = dev.DeviceTable(["k", "v"], [kc, vc], n, pa.schema([("k", pa.int32()), ("v", pa.float32())]))
+    ds = DeviceDataset(table, [(i * n // 16, (i + 1) * n // 16) for i in range(16)])
+    out = DeviceExchange(rt).aggregate(ds, "k", [Sum("v"), Mean("v"), Count()], seed=1)
+    G = out.num_rows
+    t = out.table
+    keys = t.column("k").data.view(torch.int64)[:G]
+    cnt = t.column("count()").data.view(torch.int64)[:G]
+    sm = t.column("sum(v)").data.view(torch.float64)[:G]
+    mean = t.column("mean(v)").data.view(torch.float64)[:G]
+    exp_cnt = torch.bincount(k.to(torch.int64), minlength=g)
+    present = torch.nonzero(exp_cnt).flatten()
+    assert G == present.numel() and torch.equal(keys, present)
+    assert torch.equal(cnt, exp_cnt[present]) and int(cnt.sum().item()) == n
+    exp_sum = torch.zeros(g, dtype=torch.float64, device=rt.device).index_add_(0, k.to(torch.int64), v.to(torch.float64))
+    es = exp_sum[present]
+    tol = 1e-6 * torch.maximum(es.abs(), sm.abs()) + 1e-9
+    assert bool(((sm - es).abs() <= tol).all())
+    assert bool(((mean - sm / cnt.to(torch.float64)).abs() <= 1e-12 * mean.abs() + 1e-15).all())
+    last = 0
+    for lo, hi in out.block_ranges:
+        assert lo == last
+        last = hi
+    assert last == G and len(out.block_ranges) == 16
