@@ -57,6 +57,22 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def exchange_roofline(total_rows: int, world: int, hbm_gbs: float, ms_per_step: float) -> dict:
+    """lower bound of one step = the slower of the HBM bound (every row read
+    once and written once: 2 x row bytes) and the NVLink bound (a row leaves its GPU with
+    probability (G-1)/G; 900 GB/s per direction per GPU nominal, 770 GB/s measured peer copy,
+    B200_PROFILING.md); fraction = bound / measured step."""
+    per_gpu_bytes = total_rows * ROW_BYTES / world
+    t_hbm = 2 * per_gpu_bytes / (hbm_gbs * 1e9) * 1e3
+    out = {"hbm_bound_ms": t_hbm}
+    for name, gbs in (("nominal_900", 900.0), ("measured_770", 770.0)):
+        t_nv = per_gpu_bytes * (world - 1) / world / (gbs * 1e9) * 1e3
+        lb = max(t_hbm, t_nv)
+        out[name] = {"nvlink_bound_ms": t_nv, "bound_ms": lb,
+                     "binding": "nvlink" if t_nv > t_hbm else "hbm", "frac": lb / ms_per_step}
+    return out
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons DURING the timed region."""
 
@@ -553,6 +569,7 @@ def run_b200(args):
                        "partitioning": "range (sampled boundaries), R = number of input blocks"},
             "gb_per_s_algorithmic": value * 2 * ROW_BYTES / 1e9,
             "frac_of_hbm_roofline": value * 2 * ROW_BYTES / 1e9 / (peak * world),
+            "exchange_roofline": exchange_roofline(total_rows, world, peak, ms_per_step),
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roofline,
