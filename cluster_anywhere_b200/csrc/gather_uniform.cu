@@ -19,16 +19,33 @@
 // Algorithmic bytes: 2*w + 4 per row.  Rows whose width and both base pointers are
 // multiples of 16 take the vector variant (16-byte words, no re-alignment).
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 
 namespace {
 
 constexpr int GU_THREADS = 256;
-constexpr int GU_STAGE = 56 * 1024;
+constexpr int GU_STAGE_DEFAULT_KB = 56;
+constexpr int GU_STAGE_MAX = 56 * 1024;
 constexpr int GU_MAX_ROWS = 1024;
-// stage | pad | int64 src[GU_MAX_ROWS] | uint32 a0[GU_MAX_ROWS]
-constexpr size_t GU_SMEM = GU_STAGE + 32 + (size_t)GU_MAX_ROWS * (8 + 4);
+// int64 src[GU_MAX_ROWS] | uint32 a0[GU_MAX_ROWS] | stage | pad
+constexpr size_t GU_META = (size_t)GU_MAX_ROWS * (8 + 4);
+constexpr size_t gu_smem(int stage_bytes) { return GU_META + (size_t)stage_bytes + 32; }
+
+// Bytes of row staging per CTA.  Smaller stages let more CTAs share an SM, so that more
+// of them are in their (latency-bound) load phase while others write out: XCHG_GATHER_STAGE_KB
+// (16..56) overrides the default.
+static int gu_stage_bytes() {
+  static int v = 0;
+  if (v == 0) {
+    const char* e = getenv("XCHG_GATHER_STAGE_KB");
+    int kb = e ? atoi(e) : 0;
+    if (kb < 16 || kb > 56) kb = GU_STAGE_DEFAULT_KB;
+    v = kb * 1024;
+  }
+  return v;
+}
 
 // .L2::64B: a miss fetches the 64 bytes around the access from HBM instead of the whole
 // 128-byte line (measured on B200, profiles/r01_fetch_granularity.md: 127 B of DRAM
@@ -68,9 +85,9 @@ k_gather_rows_uniform(const uint8_t* __restrict__ in, uint32_t w, const uint32_t
                       uint32_t slot, uint32_t magic_w, uint32_t magic_cpr, GatherSegs segs,
                       uint64_t max_tiles) {
   extern __shared__ __align__(16) uint8_t smem[];
-  uint8_t* stage = smem;
-  int64_t* m_src = reinterpret_cast<int64_t*>(smem + GU_STAGE + 32);
+  int64_t* m_src = reinterpret_cast<int64_t*>(smem);
   uint32_t* m_a0 = reinterpret_cast<uint32_t*>(m_src + GU_MAX_ROWS);
+  uint8_t* stage = smem + GU_META;
   const uint32_t stage_s = (uint32_t)__cvta_generic_to_shared(stage);
   const int tid = threadIdx.x;
   const uint32_t cpr = slot >> 4;  // 16-byte chunks per slot
@@ -224,13 +241,13 @@ static int gather_uniform_launch(const uint8_t* in, uint32_t w, const uint32_t* 
   static bool attr_done = false;
   if (!attr_done) {
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<false, false>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GU_SMEM));
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gu_smem(GU_STAGE_MAX)));
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<true, false>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GU_SMEM));
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gu_smem(GU_STAGE_MAX)));
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<false, true>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GU_SMEM));
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gu_smem(GU_STAGE_MAX)));
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<true, true>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GU_SMEM));
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gu_smem(GU_STAGE_MAX)));
     attr_done = true;
   }
   uintptr_t align_bits = (uintptr_t)in | (uintptr_t)out;
@@ -238,7 +255,12 @@ static int gather_uniform_launch(const uint8_t* in, uint32_t w, const uint32_t* 
     for (int d = 0; d < multi->nseg; ++d) align_bits |= (uintptr_t)multi->out[d];
   const bool vec16 = (w % 16 == 0) && (align_bits % 16 == 0);
   const uint32_t slot = vec16 ? w : ((w + 15u + 15u) & ~15u);
-  const uint32_t rpt = std::min<uint32_t>(GU_MAX_ROWS, GU_STAGE / slot);
+  int stage_bytes = gu_stage_bytes();
+  if (slot > (uint32_t)stage_bytes) stage_bytes = GU_STAGE_MAX;  // wide rows: the largest stage
+  const size_t smem_bytes = gu_smem(stage_bytes);
+  // CTAs of this shape an SM holds (227 KB of shared memory, 1 KB reserved per CTA)
+  const int resident = std::max(1, (int)((227 * 1024) / (smem_bytes + 1024)));
+  const uint32_t rpt = std::min<uint32_t>(GU_MAX_ROWS, (uint32_t)stage_bytes / slot);
   if (rpt == 0) return 1;  // row wider than the stage: caller takes the generic path
   const uint32_t cpr = slot >> 4;
   // exact for every dividend below 2^32 / divisor, which bounds all uses (tile bytes, chunks)
@@ -254,11 +276,11 @@ static int gather_uniform_launch(const uint8_t* in, uint32_t w, const uint32_t* 
   // persistent CTAs (3 resident per SM, 8 waves of tiles each by default); a cap leaves
   // SMs' shared memory to kernels running beside a link-bound peer-store gather
   const int cap = xchg_gather_ctas_per_sm();
-  const int grid = (int)std::min<uint64_t>(ntiles, (uint64_t)xchg_sm_count() * (cap ? cap : 3 * 8));
+  const int grid = (int)std::min<uint64_t>(ntiles, (uint64_t)xchg_sm_count() * (cap ? cap : resident * 8));
   const GatherSegs sg = multi ? *multi : no_segs();
 #define XCHG_GU_LAUNCH(VEC, MULTI)                                                                   \
   XCHG_LAUNCH(XK_GATHER_ROWS, s,                                                                     \
-              k_gather_rows_uniform<VEC, MULTI><<<grid, GU_THREADS, GU_SMEM, s>>>(                    \
+              k_gather_rows_uniform<VEC, MULTI><<<grid, GU_THREADS, smem_bytes, s>>>(                    \
                   in, w, idx, n_out, out, rpt, slot, magic_w, magic_cpr, sg, max_tiles))
   if (multi) {
     if (vec16) XCHG_GU_LAUNCH(true, true);
