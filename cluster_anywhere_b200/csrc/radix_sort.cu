@@ -628,7 +628,8 @@ constexpr size_t ls_smem(int threads, int items) {
 }
 constexpr int ls_min_blocks(int threads, int items) {
   // registers: 3 per item + ranks + ~28; shared memory: 12 B per row + counters
-  return items >= 16 ? (threads >= 512 ? 1 : (threads >= 256 ? 2 : 4)) : (threads >= 256 ? 4 : 8);
+  return items >= 16 ? (threads >= 512 ? 1 : (threads >= 256 ? 2 : 4))
+                     : (threads >= 512 ? 2 : (threads >= 256 ? 4 : 8));
 }
 
 // One CTA per small segment: load it, LSD-sort it by the remaining (lower) places in
@@ -1009,9 +1010,12 @@ static int local_sort_level(const uint64_t* src_k, const uint32_t* src_v, uint64
                             cudaStream_t s) {
   static bool attr_done = false;
   static int wide2 = -1;  // XCHG_LS_WIDE2=1: 256-thread CTAs for the 2048-row class
+  static int wide3 = -1;  // XCHG_LS_WIDE3=1: 512-thread CTAs (8 rows per thread) for the 4096-row class
   if (wide2 < 0) {
     const char* e = getenv("XCHG_LS_WIDE2");
     wide2 = (e && atoi(e) == 1) ? 1 : 0;
+    const char* f = getenv("XCHG_LS_WIDE3");
+    wide3 = (f && atoi(f) == 1) ? 1 : 0;
   }
   if (!attr_done) {
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_local_sort<128, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1022,6 +1026,8 @@ static int local_sort_level(const uint64_t* src_k, const uint32_t* src_v, uint64
                                        (int)ls_smem(256, 16)));
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_local_sort<512, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)ls_smem(512, 16)));
+    XCHG_CUDA_TRY(cudaFuncSetAttribute(k_local_sort<512, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)ls_smem(512, 8)));
     attr_done = true;
   }
 #define XCHG_LOCAL_SORT(CLS, THREADS, ITEMS)                                                         \
@@ -1032,7 +1038,7 @@ static int local_sort_level(const uint64_t* src_k, const uint32_t* src_v, uint64
   XCHG_LOCAL_SORT(0, 128, 4);
   XCHG_LOCAL_SORT(1, 128, 8);
   if (wide2) { XCHG_LOCAL_SORT(2, 256, 8); } else { XCHG_LOCAL_SORT(2, 128, 16); }
-  XCHG_LOCAL_SORT(3, 256, 16);
+  if (wide3) { XCHG_LOCAL_SORT(3, 512, 8); } else { XCHG_LOCAL_SORT(3, 256, 16); }
   XCHG_LOCAL_SORT(4, 512, 16);
 #undef XCHG_LOCAL_SORT
   XCHG_LAUNCH_CHECK();
