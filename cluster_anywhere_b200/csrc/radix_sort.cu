@@ -192,6 +192,26 @@ __device__ __forceinline__ unsigned match_digit(uint32_t d) {
   return m;
 }
 
+// The same in four instructions per bit instead of the six ptxas emits for the C++ form
+// (bit test into a predicate, ballot, select of the all-ones / zero mask, one LOP3):
+// 15 % fewer instructions in a onesweep pass.  ptxas fails register allocation ("register
+// count of '7'", the predicate file) when 16 of these per thread sit inside the local
+// sort's pass loop, so the 16-row-per-thread local sorts keep match_digit.
+__device__ __forceinline__ unsigned match_digit_asm(uint32_t d) {
+  unsigned m = 0xffffffffu;
+#define XCHG_MATCH_BIT(MASK)                                                                     \
+  asm volatile("{\n\t.reg .pred p;\n\t.reg .b32 t, v, x;\n\t"                                   \
+               "and.b32 t, %1, " #MASK ";\n\tsetp.ne.u32 p, t, 0;\n\t"                           \
+               "vote.sync.ballot.b32 v, p, 0xffffffff;\n\tselp.b32 x, 0, 0xffffffff, p;\n\t"      \
+               "lop3.b32 %0, %0, v, x, 0x60;\n\t}"                                               \
+               : "+r"(m)                                                                         \
+               : "r"(d));
+  XCHG_MATCH_BIT(1) XCHG_MATCH_BIT(2) XCHG_MATCH_BIT(4) XCHG_MATCH_BIT(8)
+  XCHG_MATCH_BIT(16) XCHG_MATCH_BIT(32) XCHG_MATCH_BIT(64) XCHG_MATCH_BIT(128)
+#undef XCHG_MATCH_BIT
+  return m;
+}
+
 // Bump of a warp-PRIVATE shared-memory counter by the lanes whose predicate is set:
 // returns the old value.  Plain load + add + store, predicated (no divergent branch):
 // within one call the active lanes hold distinct digits, hence distinct addresses, and
@@ -302,7 +322,7 @@ k_onesweep(const uint64_t* __restrict__ keys_in_, const uint32_t* __restrict__ v
 #pragma unroll
     for (int u = 0; u < RS_BATCH; ++u) {
       d[u] = digit_of<MODE>(key[h + u], val[h + u], shift, validity, vbit);
-      m[u] = match_digit(d[u]);
+      m[u] = match_digit_asm(d[u]);
     }
     uint32_t prev[RS_BATCH];
 #pragma unroll
@@ -696,7 +716,8 @@ k_local_sort(const uint64_t* __restrict__ src_keys, const uint32_t* __restrict__
 #pragma unroll
       for (int u = 0; u < BATCH; ++u) {
         d[u] = (uint32_t)(key[h + u] >> shift) & 255u;
-        m[u] = match_digit(d[u]);
+        if constexpr (LS_ITEMS <= 8) m[u] = match_digit_asm(d[u]);
+        else m[u] = match_digit(d[u]);
       }
       uint32_t prev[BATCH];
 #pragma unroll
@@ -1009,13 +1030,16 @@ static int local_sort_level(const uint64_t* src_k, const uint32_t* src_v, uint64
                             uint64_t* const* small, const uint32_t* nsmall, const LocalPlaces& lp,
                             cudaStream_t s) {
   static bool attr_done = false;
-  static int wide2 = -1;  // XCHG_LS_WIDE2=1: 256-thread CTAs for the 2048-row class
-  static int wide3 = -1;  // XCHG_LS_WIDE3=1: 512-thread CTAs (8 rows per thread) for the 4096-row class
+  // 8 rows per thread (256 / 512 threads) for the 2048- and 4096-row classes: same speed as
+  // 16 rows per thread on fewer threads, and the shape that can use match_digit_asm;
+  // XCHG_LS_WIDE2=0 / XCHG_LS_WIDE3=0 select 128 x 16 / 256 x 16
+  static int wide2 = -1;
+  static int wide3 = -1;
   if (wide2 < 0) {
     const char* e = getenv("XCHG_LS_WIDE2");
-    wide2 = (e && atoi(e) == 1) ? 1 : 0;
+    wide2 = (e && atoi(e) == 0) ? 0 : 1;
     const char* f = getenv("XCHG_LS_WIDE3");
-    wide3 = (f && atoi(f) == 1) ? 1 : 0;
+    wide3 = (f && atoi(f) == 0) ? 0 : 1;
   }
   if (!attr_done) {
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_local_sort<128, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
