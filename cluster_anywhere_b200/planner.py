@@ -348,12 +348,16 @@ def generate_sort_fn(sort_key: SortKey, batch_format: str, data_context: DataCon
 
     def fn(sort_key: SortKey, refs: List[RefBundle], ctx: TaskContext) -> Tuple[List[RefBundle], StatsDict]:
         blocks, metadata = _flatten(refs)
-        if len(blocks) == 0:
+        device = data_context.shuffle_strategy == ShuffleStrategy.B200_DEVICE_EXCHANGE
+        # (one process per GPU: a rank that holds no block still takes part in the collectives)
+        collective = device and _device_world() > 1
+        if len(blocks) == 0 and not collective:
             return (blocks, {})
-        sort_key.validate_schema(unify_block_metadata_schema(metadata))
+        schema = unify_block_metadata_schema(metadata)
+        if schema is not None or not collective:
+            sort_key.validate_schema(schema)
         num_mappers = len(blocks)
         num_outputs = num_mappers
-        device = data_context.shuffle_strategy == ShuffleStrategy.B200_DEVICE_EXCHANGE
         boundaries = None
         if sort_key.boundaries:
             boundaries = [(b,) for b in sort_key.boundaries]
@@ -420,7 +424,7 @@ def generate_random_shuffle_fn(data_context: DataContext, seed: Optional[int],
             if upstream_map_fn is not None:
                 blocks = [B200ArrowBlockAccessor.for_block(b).to_arrow() for blk in blocks
                           for b in upstream_map_fn([blk])]
-            if len(blocks) == 0:
+            if len(blocks) == 0 and _device_world() <= 1:
                 return ([], {})
             out = DeviceExchange().random_shuffle_blocks(blocks, seed, num_outputs)
             bundles, metas = _bundles_of(out, all(b.owns_blocks for b in refs), st)
@@ -457,11 +461,14 @@ def generate_aggregate_fn(key: Optional[Union[str, List[str]]], aggs: list, batc
 
     def fn(refs: List[RefBundle], ctx: TaskContext) -> Tuple[List[RefBundle], StatsDict]:
         blocks, metadata = _flatten(refs)
-        if len(blocks) == 0:
+        collective = (data_context.shuffle_strategy == ShuffleStrategy.B200_DEVICE_EXCHANGE
+                      and _device_world() > 1)  # a rank without blocks still joins the collectives
+        if len(blocks) == 0 and not collective:
             return (blocks, {})
         unified_schema = unify_block_metadata_schema(metadata)
-        for agg_fn in aggs:
-            agg_fn._validate(unified_schema)
+        if unified_schema is not None or not collective:
+            for agg_fn in aggs:
+                agg_fn._validate(unified_schema)
         num_mappers = len(blocks)
         sort_key = SortKey(key)
         if data_context.shuffle_strategy == ShuffleStrategy.B200_DEVICE_EXCHANGE:

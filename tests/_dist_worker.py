@@ -121,6 +121,31 @@ def main():
         keys = tuple([gkey] if isinstance(gkey, str) else gkey)
         assert_tables_close(pa.concat_tables([g for g in got if g.num_rows], promote_options="permissive"),
                             exp2, exact=keys)
+    # the planner's device strategy over the process group: this rank's bundles in, its run
+    # of the sorted output blocks out
+    from cluster_anywhere_b200 import planner as P
+
+    pctx = P.DataContext(shuffle_strategy=P.ShuffleStrategy.B200_DEVICE_EXCHANGE)
+    bundles, stats = P.execute_all_to_all(P.Sort(P.InputData(), SortKey(["k", "f"], [False, True])),
+                                          [P.RefBundle.from_block(b) for b in mine], pctx)
+    outs = [None] * w
+    dist.all_gather_object(outs, [b for rb in bundles for b in rb.block_refs])
+    got = [b for part in outs for b in part]
+    assert len(got) == len(all_blocks) and set(stats) == {"map", "reduce"}
+    assert tables_equal(pa.concat_tables([g for g in got if g.num_rows]),
+                        O.sort_table(full, ["k", "f"], [False, True]))
+    bundles, _ = P.execute_all_to_all(P.Aggregate(P.InputData(), "k", [Count(), Sum("f")]),
+                                      [P.RefBundle.from_block(b) for b in mine], pctx)
+    outs = [None] * w
+    dist.all_gather_object(outs, [b for rb in bundles for b in rb.block_refs])
+    got = pa.concat_tables([b for part in outs for b in part if b.num_rows], promote_options="permissive")
+    assert got["count()"].to_pylist() == O.groupby_aggregate(all_blocks, "k", [("count",)])["count()"].to_pylist()
+    bundles, _ = P.execute_all_to_all(P.RandomShuffle(P.InputData(), seed=11),
+                                      [P.RefBundle.from_block(b) for b in mine], pctx)
+    outs = [None] * w
+    dist.all_gather_object(outs, [b for rb in bundles for b in rb.block_refs])
+    got = pa.concat_tables([b for part in outs for b in part if b.num_rows])
+    assert got.num_rows == full.num_rows and sorted(got["k"].to_pylist()) == sorted(full["k"].to_pylist())
     out = ex.aggregate_blocks(mine, None, [Count(), Sum("k")])
     outs = [None] * w
     dist.all_gather_object(outs, out)
