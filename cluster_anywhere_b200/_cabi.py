@@ -47,7 +47,7 @@ _SIGNATURES = {
     "xchg_agg_stats_init": (c_int, [_P, _P, c_uint64, _P]),
     "xchg_key_minmax": (c_int, [_P, _P, c_int64, c_uint64, _P, ctypes.POINTER(c_uint64), _P]),
     "xchg_dense_groups_bytes": (c_int, [c_uint64, ctypes.POINTER(c_uint64)]),
-    "xchg_dense_groups": (c_int, [_P, _P, c_int64, c_uint64, c_uint64, c_uint64, _P, c_uint64, _P, _P,
+    "xchg_dense_groups": (c_int, [_P, _P, c_int64, c_uint64, c_uint64, c_uint64, _P, c_uint64, _P, _P, _P,
                                   ctypes.POINTER(c_uint64), _P]),
     "xchg_group_flags_fixed": (c_int, [_P, _P, c_int64, _P, c_uint64, _P, _P]),
     "xchg_group_flags_bytes": (c_int, [_P, _P, _P, c_int64, _P, c_uint64, _P, _P]),

@@ -183,9 +183,11 @@ def _resolve_nulls(col: DeviceColumn) -> int:
     return int(nc.item()) if isinstance(nc, torch.Tensor) else int(nc)
 
 
-def group_rows(rt: dev.Runtime, key_col: DeviceColumn, n: int):
-    """K8 front half: -> (row group ids uint32[n], sorted group radix keys, G, key_type).
-    Group ids follow the OUTPUT order (key ascending, NaN, then the null group)."""
+def group_rows(rt: dev.Runtime, key_col: DeviceColumn, n: int, want_rows: bool = False):
+    """K8 front half: -> (row group ids uint32[n], sorted group radix keys, G, key_type,
+    rows per group or None).  Group ids follow the OUTPUT order (key ascending, NaN, then
+    the null group).  ``want_rows``: the direct-address path counts the rows of every group
+    in its marking pass (the hash path returns None: the caller counts them)."""
     if key_col.kind != "fixed":
         raise NotImplementedError(f"group key of type {key_col.type} is not supported by the B200 engine")
     kt = dev.key_type_of(key_col.type)
@@ -206,11 +208,12 @@ def group_rows(rt: dev.Runtime, key_col: DeviceColumn, n: int):
             ws = rt.empty(wsb.value)
             rgid = rt.empty(n, torch.int32)
             gkeys = rt.empty(min(rng, n) + 2, torch.int64)
+            grows = rt.empty(min(rng, n) + 2, torch.int64) if want_rows else None
             g_out = ctypes.c_uint64()
             rt.call("xchg_dense_groups", _vp(norm), _vp(key_col.validity), 0, n, kmin, rng, _vp(ws), wsb.value,
-                    _vp(rgid), _vp(gkeys), ctypes.byref(g_out), rt.stream, launches=5)
+                    _vp(rgid), _vp(gkeys), _vp(grows), ctypes.byref(g_out), rt.stream, launches=6)
             g = int(g_out.value)
-            return rgid, gkeys[:g], g, kt
+            return rgid, gkeys[:g], g, kt, (grows[:g] if want_rows else None)
     cap = max(64, _next_pow2(2 * min(n, _KEY_RANGE.get(kt, n))))
     ws_bytes = ctypes.c_uint64()
     _cabi.check(_cabi.load().xchg_hash_table_bytes(cap, ctypes.byref(ws_bytes)))
@@ -233,7 +236,7 @@ def group_rows(rt: dev.Runtime, key_col: DeviceColumn, n: int):
     rgid = rt.empty(n, torch.int32)
     rt.call("xchg_group_ids", _vp(order), _vp(gslots), g, _vp(slot), n, cap, _vp(ws), _vp(rgid),
             rt.stream, launches=2)
-    return rgid, sorted_keys, g, kt
+    return rgid, sorted_keys, g, kt, None
 
 
 def group_rows_sorted(rt: dev.Runtime, table: DeviceTable, key_names: Sequence[str]):
@@ -356,6 +359,7 @@ def aggregate_table(rt: dev.Runtime, table: DeviceTable, key: Optional[str],
     keys = key_list(key)
     key_cols_out: List[DeviceColumn] = []
     key_fields: List[pa.Field] = []
+    counted = None
     general = len(keys) > 1 or (len(keys) == 1 and table.column(keys[0]).kind != "fixed")
     if general:
         rgid, g, first = group_rows_sorted(rt, table, keys)
@@ -363,7 +367,7 @@ def aggregate_table(rt: dev.Runtime, table: DeviceTable, key: Optional[str],
     elif keys:
         key = keys[0]
         kc = table.column(key)
-        rgid, sorted_keys, g, kt = group_rows(rt, kc, n)
+        rgid, sorted_keys, g, kt, counted = group_rows(rt, kc, n, want_rows=not partial_in)
         kvals = rt.empty(g, torch.int64)
         rt.call("xchg_group_keys_out", _vp(sorted_keys), kt, g, _vp(kvals), rt.stream)
         out_type = pa.int64() if _is_int_type(kt) else pa.float64()
@@ -376,8 +380,10 @@ def aggregate_table(rt: dev.Runtime, table: DeviceTable, key: Optional[str],
         key_cols_out = [DeviceColumn(out_type, g, "fixed", 8, kvals.view(torch.uint8), None, kvalid, knulls)]
         key_fields = [pa.field(key, out_type)]
 
-    rows = rt.zeros(g, torch.int64)
-    if partial_in:
+    rows = counted if counted is not None else rt.zeros(g, torch.int64)
+    if counted is not None:
+        pass  # the direct-address grouping counted the rows of every group on its way
+    elif partial_in:
         rt.call("xchg_agg_merge_rows", _vp(rgid), _vp(table.column(ROWS_COL).data), n, _vp(rows), rt.stream)
     else:
         rt.call("xchg_agg_count_rows", _vp(rgid), n, g, _vp(rows), rt.stream)
@@ -589,7 +595,7 @@ def unique_values(rt: dev.Runtime, table: DeviceTable, column: str) -> DeviceCol
     if n == 0:
         return kc
     if kc.kind == "fixed":
-        rgid, sorted_keys, g, kt = group_rows(rt, kc, n)
+        rgid, sorted_keys, g, kt, _ = group_rows(rt, kc, n)
         # first row of every group: any row will do, the values are equal
         first = rt.empty(g, torch.int32)
         rt.call("xchg_group_first_rows", _vp(rgid), n, g, _vp(first), rt.stream)

@@ -581,6 +581,30 @@ k_dense_mark(const uint64_t* __restrict__ norm, const uint8_t* __restrict__ vali
   }
 }
 
+// Row count per key value instead of a presence byte: the same pass then also yields the
+// groups' row counts (Count, and the rows column of partial rows), which would otherwise
+// cost a second atomic pass over the rows (k_acc_rows_direct).
+__global__ void __launch_bounds__(AG_THREADS)
+k_dense_count(const uint64_t* __restrict__ norm, const uint8_t* __restrict__ validity, int64_t vbit,
+              uint64_t n, uint64_t kmin, uint32_t* __restrict__ counts, uint32_t* null_rows) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  const uint64_t n_up = (n + 31) & ~31ull;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_up; i += stride) {
+    const bool active = i < n;
+    const bool valid = active && (validity ? bit_is_set(validity, (int64_t)i + vbit) : true);
+    const unsigned nulls = __ballot_sync(0xffffffffu, active && !valid);
+    if (nulls && (threadIdx.x & 31) == 0) atomicAdd(null_rows, (uint32_t)__popc(nulls));
+    if (valid) atomicAdd(&counts[norm[i] - kmin], 1u);
+  }
+}
+
+__global__ void __launch_bounds__(AG_THREADS)
+k_dense_presence(const uint32_t* __restrict__ counts, uint64_t range, uint8_t* __restrict__ present) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < range; i += stride)
+    present[i] = counts[i] != 0u;
+}
+
 // tile_sums[t] = number of present values in tile t
 __global__ void __launch_bounds__(256)
 k_dense_tile_sums(const uint8_t* __restrict__ present, uint64_t range, uint32_t* __restrict__ tile_sums) {
@@ -647,7 +671,8 @@ k_dense_scan_sums(uint32_t* tile_sums, uint32_t ntiles, unsigned long long* tota
 __global__ void __launch_bounds__(256)
 k_dense_emit(const uint8_t* __restrict__ present, uint64_t range, uint64_t kmin,
              const uint32_t* __restrict__ tile_excl, uint32_t* __restrict__ rank,
-             uint64_t* __restrict__ group_keys) {
+             uint64_t* __restrict__ group_keys, const uint32_t* __restrict__ counts,
+             uint64_t* __restrict__ group_rows) {
   __shared__ uint32_t ws[8];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint64_t base = (uint64_t)blockIdx.x * DG_TILE + (uint64_t)threadIdx.x * 16;
@@ -677,7 +702,10 @@ k_dense_emit(const uint8_t* __restrict__ present, uint64_t range, uint64_t kmin,
   for (int j = 0; j < 16; ++j) {
     if (base + j < range) {
       rank[base + j] = r;
-      if (b[j]) group_keys[r] = kmin + base + j;
+      if (b[j]) {
+        group_keys[r] = kmin + base + j;
+        if (group_rows) group_rows[r] = counts[base + j];
+      }
       r += b[j];
     }
   }
@@ -881,6 +909,7 @@ extern "C" int xchg_key_minmax(const uint64_t* norm_keys, const uint8_t* validit
 namespace {
 struct DenseWs {
   uint8_t* present;
+  uint32_t* counts;
   uint32_t* rank;
   uint32_t* tile_sums;
   uint32_t* null_present;
@@ -897,6 +926,7 @@ DenseWs dense_carve(void* base, uint64_t range) {
   };
   const uint64_t ntiles = (range + DG_TILE - 1) / DG_TILE;
   w.present = take(range + 16);
+  w.counts = (uint32_t*)take(range * 4);
   w.rank = (uint32_t*)take(range * 4);
   w.tile_sums = (uint32_t*)take((ntiles + 1) * 4);
   w.null_present = (uint32_t*)take(64);
@@ -921,7 +951,7 @@ extern "C" int xchg_dense_groups(const uint64_t* norm_keys, const uint8_t* valid
                                  int64_t validity_bit_offset, uint64_t n, uint64_t key_min,
                                  uint64_t range, void* workspace, uint64_t workspace_bytes,
                                  uint32_t* row_gid_out, uint64_t* group_keys_out,
-                                 uint64_t* num_groups_out, void* stream) {
+                                 uint64_t* group_rows_out, uint64_t* num_groups_out, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
   XCHG_REQUIRE(workspace && row_gid_out && group_keys_out && num_groups_out, "NULL argument");
   XCHG_REQUIRE(n <= XCHG_MAX_ROWS, "n exceeds XCHG_MAX_ROWS");
@@ -940,12 +970,21 @@ extern "C" int xchg_dense_groups(const uint64_t* norm_keys, const uint8_t* valid
   const uint32_t ntiles = (uint32_t)((range + DG_TILE - 1) / DG_TILE);
   XCHG_CUDA_TRY(cudaMemsetAsync(w.present, 0, range + 16, s));
   XCHG_CUDA_TRY(cudaMemsetAsync(w.null_present, 0, 64, s));
-  XCHG_LAUNCH(XK_AGGREGATE, s, k_dense_mark<<<ag_grid(n), AG_THREADS, 0, s>>>(
-      norm_keys, validity, validity_bit_offset, n, key_min, w.present, w.null_present));
+  if (group_rows_out) {
+    XCHG_CUDA_TRY(cudaMemsetAsync(w.counts, 0, range * 4, s));
+    XCHG_LAUNCH(XK_AGGREGATE, s, k_dense_count<<<ag_grid(n), AG_THREADS, 0, s>>>(
+        norm_keys, validity, validity_bit_offset, n, key_min, w.counts, w.null_present));
+    XCHG_LAUNCH(XK_AGGREGATE, s, k_dense_presence<<<ag_grid(range), AG_THREADS, 0, s>>>(w.counts, range,
+                                                                                   w.present));
+  } else {
+    XCHG_LAUNCH(XK_AGGREGATE, s, k_dense_mark<<<ag_grid(n), AG_THREADS, 0, s>>>(
+        norm_keys, validity, validity_bit_offset, n, key_min, w.present, w.null_present));
+  }
   XCHG_LAUNCH(XK_AGGREGATE, s, k_dense_tile_sums<<<ntiles, 256, 0, s>>>(w.present, range, w.tile_sums));
   XCHG_LAUNCH(XK_AGGREGATE, s, k_dense_scan_sums<<<1, 1024, 0, s>>>(w.tile_sums, ntiles, w.total));
   XCHG_LAUNCH(XK_AGGREGATE, s, k_dense_emit<<<ntiles, 256, 0, s>>>(w.present, range, key_min, w.tile_sums,
-                                                               w.rank, group_keys_out));
+                                                               w.rank, group_keys_out, w.counts,
+                                                               group_rows_out));
   XCHG_LAUNCH_CHECK();
   unsigned long long total = 0;
   uint32_t has_null = 0;
@@ -955,6 +994,10 @@ extern "C" int xchg_dense_groups(const uint64_t* norm_keys, const uint8_t* valid
   if (has_null) {  // the null group goes last, with the sentinel key the hash path gives it
     const unsigned long long e = EMPTY;
     XCHG_CUDA_TRY(cudaMemcpyAsync(group_keys_out + total, &e, 8, cudaMemcpyHostToDevice, s));
+    if (group_rows_out) {  // has_null is the number of null rows on the counting path
+      const unsigned long long nr = has_null;
+      XCHG_CUDA_TRY(cudaMemcpyAsync(group_rows_out + total, &nr, 8, cudaMemcpyHostToDevice, s));
+    }
   }
   XCHG_LAUNCH(XK_AGGREGATE, s, k_dense_lookup<<<ag_grid(n), AG_THREADS, 0, s>>>(
       norm_keys, validity, validity_bit_offset, n, key_min, w.rank, (uint32_t)total, row_gid_out));

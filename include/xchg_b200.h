@@ -399,8 +399,10 @@ int xchg_hash_groups(const uint64_t* norm_keys, const uint8_t* validity, int64_t
  * xchg_dense_groups: presence byte per value in [key_min, key_min + range), scan, lookup:
  *   row_gid_out[i] = group id of row i in OUTPUT order (key ascending, null group last);
  *   group_keys_out (range + 1 entries at most; min(range, n) + 1 suffice) receives the
- *   groups' radix keys in that order, UINT64_MAX for the null group.  range <=
- *   XCHG_DENSE_MAX_RANGE.  Synchronises the stream (reads the group count).
+ *   groups' radix keys in that order, UINT64_MAX for the null group.  group_rows_out (may
+ *   be NULL; same length): the number of rows of every group -- the marking pass then counts
+ *   rows per value instead of setting a presence byte, and xchg_agg_count_rows is not needed.
+ *   range <= XCHG_DENSE_MAX_RANGE.  Synchronises the stream (reads the group count).
  */
 int xchg_key_minmax(const uint64_t* norm_keys, const uint8_t* validity, int64_t validity_bit_offset,
                     uint64_t n, void* scratch32, uint64_t* out3_host, void* stream);
@@ -408,7 +410,7 @@ int xchg_dense_groups_bytes(uint64_t range, uint64_t* bytes_out);
 int xchg_dense_groups(const uint64_t* norm_keys, const uint8_t* validity, int64_t validity_bit_offset,
                       uint64_t n, uint64_t key_min, uint64_t range, void* workspace,
                       uint64_t workspace_bytes, uint32_t* row_gid_out, uint64_t* group_keys_out,
-                      uint64_t* num_groups_out, void* stream);
+                      uint64_t* group_rows_out, uint64_t* num_groups_out, void* stream);
 /*
  * Grouping of SORTED rows, for any key: several key columns, string / binary keys.
  * Replaces the run detection of ArrowBlockAccessor.combine (arrow_block.py:478-497: walk

@@ -522,7 +522,7 @@ class FakeLib:
         out._obj.value = rng * 5 + 4096
         return 0
 
-    def xchg_dense_groups(self, norm, validity, vbit, n, kmin, rng, ws, wsb, rgid, gkeys, ngroups, stream):
+    def xchg_dense_groups(self, norm, validity, vbit, n, kmin, rng, ws, wsb, rgid, gkeys, grows, ngroups, stream):
         ngroups._obj.value = 0
         if n == 0:
             return 0
@@ -538,6 +538,8 @@ class FakeLib:
         if (~valid).any():
             _arr(gkeys, np.uint64, g + 1)[g] = self._EMPTY
             g += 1
+        if _addr(grows):
+            _arr(grows, np.uint64, g)[:] = np.bincount(gid.astype(np.int64), minlength=g).astype(np.uint64)
         ngroups._obj.value = g
         return 0
 
