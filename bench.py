@@ -275,8 +275,9 @@ def run_reference(args):
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u64", "data": "synthetic",
-        "config": {"workload": workload_name(args), "sample": sample},
+        "config": config_dict(args, max(1, args.gpus)),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                         "scale": ref.total_rows / float(args.rows_per_gpu * max(1, args.gpus)),
                          "gb_per_s": value * 2 * ROW_BYTES / 1e9,
                          "primitives_only_value": ref.total_rows / prim,
                          "note": "oracle port = the reference's own pyarrow/numpy call sequence; "
@@ -290,6 +291,13 @@ def run_reference(args):
 # ----------------------------------------------------------------------------
 # B200 arm
 # ----------------------------------------------------------------------------
+
+def config_dict(args, world):
+    """The same dict in both arms (the driver compares them)."""
+    return {"workload": workload_name(args), "rows_total": args.rows_per_gpu * world,
+            "cache": "inputs (12.25 GB/GPU) far exceed the 126 MB L2; no flush needed",
+            "partitioning": "range (sampled boundaries), R = number of input blocks"}
+
 
 def workload_name(args):
     return (f"GraySort-style Dataset.sort: int64 key + 90 B binary payload, {args.rows_per_gpu} rows/GPU "
@@ -314,6 +322,9 @@ def build_resident_dataset(rt, n, blocks, seed):
     for s in range(0, n * PAYLOAD, chunk):
         e = min(n * PAYLOAD, s + chunk)
         data[s:e] = torch.randint(0, 256, (e - s,), dtype=torch.uint8, device=rt.device, generator=g)
+    # bytes 0..7 of every payload row repeat the row's key: after the sort a row that lost
+    # its payload (or a payload that lost its key) is detectable (``verify_output``)
+    data[: n * PAYLOAD].view(n, PAYLOAD)[:, :8].copy_(keys.view(torch.uint8).view(n, 8))
     schema = pa.schema([("c_0", pa.int64()), ("c_1", pa.binary())])
     c0 = dev.DeviceColumn(pa.int64(), n, "fixed", 8, keys.view(torch.uint8))
     c1 = dev.DeviceColumn(pa.binary(), n, "var", 1, data, None, None, 0, uniform=PAYLOAD)
@@ -347,6 +358,68 @@ def host_blocks_from_device(rt, keys, data, ranges):
                                                     dbuf.slice(lo * PAYLOAD, m * PAYLOAD)])
         blocks.append(pa.table({"c_0": c0, "c_1": c1}))
     return blocks, (keys_h, data_h, offs_h)
+
+
+def _wrapping_sum(t):
+    """Sum of an int64 tensor modulo 2^64 (torch's integer sum wraps)."""
+    return t.sum(dtype=t.dtype)
+
+
+def input_fingerprint(keys, data, n):
+    """Order-independent fingerprint of this rank's rows: count, sum of keys and sum of the
+    payload word at bytes 8..15 of every row, both modulo 2^64."""
+    import torch
+
+    w = data[: n * PAYLOAD].view(n, PAYLOAD)[:, 8:16].contiguous().view(torch.int64).view(n)
+    return torch.stack([torch.tensor(n, dtype=torch.int64, device=keys.device), _wrapping_sum(keys),
+                        _wrapping_sum(w)])
+
+
+def verify_output(out, fp_in, world):
+    """Checks on the LAST timed step's output, every rank, on the device:
+    order            keys non-decreasing inside the rank and block ranges tile its rows;
+    rank_boundaries  last key of rank g <= first key of the next rank that holds rows;
+    checksum         row count, sum of keys and sum of a payload word (mod 2^64), summed
+                     over ranks, equal the input's;
+    payload_keys     bytes 0..7 of every payload row equal the key beside it."""
+    import torch
+    import torch.distributed as dist
+
+    dev_ = fp_in.device
+    m = out.num_rows
+    if m:
+        k = out.table.column("c_0").data[: m * 8].view(torch.int64)
+        p = out.table.column("c_1").data[: m * PAYLOAD].view(m, PAYLOAD)
+        order = bool((k[1:] >= k[:-1]).all().item()) if m > 1 else True
+        pk = bool((p[:, :8].contiguous().view(torch.int64).view(m) == k).all().item())
+        w = p[:, 8:16].contiguous().view(torch.int64).view(m)
+        fp_out = torch.stack([torch.tensor(m, dtype=torch.int64, device=dev_), _wrapping_sum(k), _wrapping_sum(w)])
+        edge = torch.stack([k[0], k[-1], torch.tensor(1, dtype=torch.int64, device=dev_)])
+    else:
+        order, pk = True, True
+        fp_out = torch.zeros(3, dtype=torch.int64, device=dev_)
+        edge = torch.zeros(3, dtype=torch.int64, device=dev_)
+    last = 0
+    for lo, hi in out.block_ranges:
+        if hi > lo:
+            order = order and lo == last
+            last = hi
+    order = order and last == m
+    fps = torch.stack([fp_in, fp_out])
+    flags = torch.tensor([int(order), int(pk)], dtype=torch.int64, device=dev_)
+    if world > 1:
+        dist.all_reduce(fps)  # int64 sums wrap: still a valid fingerprint mod 2^64
+        dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+        edges = [torch.empty_like(edge) for _ in range(world)]
+        dist.all_gather(edges, edge)
+    else:
+        edges = [edge]
+    es = [e.tolist() for e in edges]
+    es = [e for e in es if e[2]]
+    rb = all(es[i][1] <= es[i + 1][0] for i in range(len(es) - 1))
+    order, pk = bool(flags[0].item()), bool(flags[1].item())
+    return {"order": order, "rank_boundaries": rb, "checksum": bool((fps[0] == fps[1]).all().item()),
+            "payload_keys": pk, "rows": int(fps[1][0].item())}
 
 
 def run_b200(args):
@@ -431,12 +504,15 @@ def run_b200(args):
     if world > 1:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
     ms_per_step = float(tmax.item()) / args.steps
-    out_rows = torch.tensor([out.num_rows], dtype=torch.int64, device=rt.device)
-    if world > 1:
-        dist.all_reduce(out_rows)
-    assert int(out_rows.item()) == n * world, "rows lost in the exchange"
-    del out
     total_rows = n * world
+    verified = verify_output(out, input_fingerprint(keys, data, n), world)
+    del out
+    if not (verified["order"] and verified["rank_boundaries"] and verified["checksum"]
+            and verified["payload_keys"] and verified["rows"] == total_rows):
+        if rank == 0:
+            print(json.dumps({"metric": METRIC, "error": "output verification failed", "verified": verified,
+                              "n_gpus": world}), flush=True)
+        raise SystemExit(3)
     value = total_rows / (ms_per_step / 1e3)
 
     # per-kernel device time over the timed region (rank 0's GPU)
@@ -540,7 +616,8 @@ def run_b200(args):
                   f"({ref.total_rows * ROW_BYTES / 1e9:.2f} GB), R={ref.num_blocks}, pull-based map/reduce on "
                   f"{cores} processes, Arrow IPC hand-off in shared memory")
         cpu = {"value": ref.total_rows / t_cpu, "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": sample, "gb_per_s": ref.total_rows / t_cpu * 2 * ROW_BYTES / 1e9,
+               "sample": sample, "scale": ref.total_rows / float(total_rows),
+               "gb_per_s": ref.total_rows / t_cpu * 2 * ROW_BYTES / 1e9,
                "primitives_only_value": ref.total_rows / t_prim}
 
     if getattr(ex, "timeline", False):
@@ -559,18 +636,27 @@ def run_b200(args):
     if args.trace:
         print(f"[trace rank {rank}] phase ms over the {args.steps} timed steps (e2e.*: over warm-up + e2e steps): "
               + json.dumps({k: round(v, 2) for k, v in ex.phase_ms.items()}), file=sys.stderr, flush=True)
+    xr = exchange_roofline(total_rows, world, peak, ms_per_step)
+    if world > 1 and roofline is not None:
+        # the step's binding bound at N > 1 is the NVLink egress of every GPU:
+        # bytes that must leave a GPU / step time, against 900 GB/s per direction
+        link_bytes = n * ROW_BYTES * (world - 1) / world
+        roofline = {"bound": "nvlink", "achieved": link_bytes / (ms_per_step * 1e-3) / 1e9, "peak": 900.0,
+                    "unit": "GB/s", "frac": xr["nominal_900"]["frac"], "traffic": None,
+                    "peak_source": "NVLink 5 nominal, per direction per GPU (B200_PROFILING.md)",
+                    "algorithmic_bytes_per_step_per_gpu": link_bytes,
+                    "dominant_kernel_hbm": roofline}
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-            "config": {"workload": workload_name(args), "rows_total": total_rows,
-                       "cache": "inputs (12.25 GB/GPU) far exceed the 126 MB L2; no flush needed",
-                       "partitioning": "range (sampled boundaries), R = number of input blocks"},
+            "config": config_dict(args, world),
             "gb_per_s_algorithmic": value * 2 * ROW_BYTES / 1e9,
             "frac_of_hbm_roofline": value * 2 * ROW_BYTES / 1e9 / (peak * world),
-            "exchange_roofline": exchange_roofline(total_rows, world, peak, ms_per_step),
+            "exchange_roofline": xr,
             "gpu_launches": int(launches),
+            "verified": verified,
             "clocks": clocks,
             "roofline": roofline,
             "kernels": kernels,

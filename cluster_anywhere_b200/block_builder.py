@@ -1,235 +1,101 @@
-"""Block builders of the exchange path (host side).
+"""Block builder of the exchange path (host side).
 
-Mirrors ``DelegatingBlockBuilder`` (python/ray/data/_internal/delegating_block_builder.py:
-9-76), ``TableBlockBuilder`` / ``ArrowBlockBuilder`` (_internal/table_block.py:35-156,
-_internal/arrow_block.py:130-160) and ``SizeEstimator`` (_internal/size_estimator.py:9-63).
-The reference uses them in ``ShuffleTaskSpec.reduce`` (concatenate one slice per mapper)
-and to rebuild aggregate outputs row by row; the engine's own reduce paths concatenate
-device buffers instead, so these are the host-facing equivalents for code written against
-the reference's builder API.
+The reference concatenates a reduce task's inputs through ``DelegatingBlockBuilder``
+(python/ray/data/_internal/delegating_block_builder.py:9-76, used by
+``ShuffleTaskSpec.reduce``, planner/exchange/shuffle_task_spec.py:115-118) and rebuilds
+aggregate outputs row by row through ``ArrowBlockBuilder``
+(_internal/table_block.py:35-156).  The engine needs far less: its outputs leave the
+device as whole Arrow tables, so the builder here only has to put tables (and the odd
+row dict from caller code written against the reference's builder API) together in
+arrival order.  Same method names as the reference's builders; own implementation:
+rows are buffered column-wise and turned into a table whenever a table arrives or the
+block is built, sizes come from ``Table.nbytes`` (no sampling estimator, no object
+store).
 """
 from __future__ import annotations
 
-import collections
-import collections.abc
-import pickle
 from typing import Any, Dict, List, Mapping, Optional
 
-import numpy as np
 import pyarrow as pa
 
 from .block import empty_table
 
-# python/ray/data/_internal/table_block.py:25-28
-MAX_UNCOMPACTED_SIZE_BYTES = 50 * 1024 * 1024
 
-
-class _RunningMean:
+class BlockBuilder:
     def __init__(self):
-        self._weight = 0
-        self._mean = 0.0
+        self._tables: List[pa.Table] = []   # finished pieces, arrival order
+        self._cols: Optional[Dict[str, list]] = None  # pending rows, column-wise
+        self._pending = 0
+        self._rows = 0
+        self._table_bytes = 0
+        self._row_bytes = 0.0  # bytes per row of the pieces built from rows so far
+        self._empty: Optional[pa.Table] = None  # schema donor when only empty blocks arrive
 
-    def add(self, x: float, weight: int = 1) -> None:
-        if weight == 0:
-            return
-        n1, n2 = self._weight, weight
-        self._mean = (n1 * self._mean + n2 * x) / (n1 + n2)
-        self._weight += weight
-
-    @property
-    def mean(self) -> float:
-        return self._mean
-
-
-class SizeEstimator:
-    """Serialised-size estimate of a stream of items from a sample of them: the first 10,
-    then every 10th up to 100, then every 100th (size_estimator.py:19-47).  The reference
-    measures with Ray's serialiser; there is no object store here, so pickle stands in."""
-
-    def __init__(self):
-        self._running_mean = _RunningMean()
-        self._count = 0
-
+    # -- input -----------------------------------------------------------------
     def add(self, item: Any) -> None:
-        self._count += 1
-        if self._count <= 10:
-            self._running_mean.add(self._real_size(item), weight=1)
-        elif self._count <= 100:
-            if self._count % 10 == 0:
-                self._running_mean.add(self._real_size(item), weight=10)
-        elif self._count % 100 == 0:
-            self._running_mean.add(self._real_size(item), weight=100)
+        """One row: a mapping column -> value (same columns for every row)."""
+        if not isinstance(item, Mapping):
+            raise ValueError(f"a row must be a mapping of column name to value, got {type(item).__name__}")
+        if self._cols is None:
+            self._cols = {str(k): [] for k in item}
+        if item.keys() != self._cols.keys():
+            raise ValueError(f"row has columns {sorted(item)}, the builder holds {sorted(self._cols)}")
+        for k, v in item.items():
+            self._cols[k].append(v)
+        self._pending += 1
+        self._rows += 1
 
-    def add_block(self, block: List[Any]) -> None:
-        if self._count < 10:
-            for i in range(min(10 - self._count, len(block))):
-                self._running_mean.add(self._real_size(block[i]), weight=1)
-        if self._count < 100:
-            for i in range(10 - (self._count % 10), min(100 - self._count, len(block)), 10):
-                self._running_mean.add(self._real_size(block[i]), weight=10)
-        if (len(block) + (self._count % 100)) // 100 > 1:
-            for i in range(100 - (self._count % 100), len(block), 100):
-                self._running_mean.add(self._real_size(block[i]), weight=100)
-        self._count += len(block)
-
-    def size_bytes(self) -> int:
-        return int(self._running_mean.mean * self._count)
-
-    def _real_size(self, item: Any) -> int:
-        return len(pickle.dumps(item, protocol=pickle.HIGHEST_PROTOCOL))
-
-
-def _is_array_like(value: Any) -> bool:
-    return hasattr(value, "__array__") or hasattr(value, "__array_interface__")
-
-
-class ArrowBlockBuilder:
-    """Rows (dicts) and whole tables in, one Arrow table out."""
-
-    def __init__(self):
-        self._columns: Dict[str, list] = collections.defaultdict(list)
-        self._column_names = None
-        self._tables: List[pa.Table] = []
-        self._tables_size_cursor = 0
-        self._tables_size_bytes = 0
-        self._uncompacted_size = SizeEstimator()
-        self._num_rows = 0
-        self._num_compactions = 0
-
-    def add(self, item: Mapping[str, Any]) -> None:
-        if isinstance(item, np.ndarray):
-            item = {"data": item}
-        if not isinstance(item, collections.abc.Mapping):
-            raise ValueError("Returned elements of an TableBlock must be of type `dict`, "
-                             "got {} (type {}).".format(item, type(item)))
-        item_column_names = item.keys()
-        if self._column_names is not None:
-            if item_column_names != self._column_names:
-                raise ValueError(
-                    "Current row has different columns compared to previous rows. "
-                    f"Columns of current row: {sorted(item_column_names)}, "
-                    f"Columns of previous rows: {sorted(self._column_names)}.")
-        else:
-            self._column_names = item_column_names
-        for key, value in item.items():
-            if _is_array_like(value) and not isinstance(value, np.ndarray):
-                value = np.array(value)
-            self._columns[key].append(value)
-        self._num_rows += 1
-        self._compact_if_needed()
-        self._uncompacted_size.add(item)
-
-    def add_block(self, block: pa.Table) -> None:
+    def add_block(self, block: Any) -> None:
+        """One table (Arrow, or a pandas DataFrame, which is converted)."""
         if not isinstance(block, pa.Table):
-            raise TypeError(f"Got a block of type {type(block)}, expected {pa.Table}."
-                            "If you are mapping a function, ensure it returns an "
-                            f"object with the expected type. Block:\n{block}")
-        self._tables.append(block)
-        self._num_rows += block.num_rows
-
-    @staticmethod
-    def _table_from_pydict(columns: Dict[str, List[Any]]) -> pa.Table:
-        out = {}
-        for name, values in columns.items():
-            if values and isinstance(values[0], np.ndarray):
-                out[name] = pa.array([v.tolist() for v in values])
+            try:
+                import pandas as pd
+            except ImportError:  # pragma: no cover
+                pd = None
+            if pd is not None and isinstance(block, pd.DataFrame):
+                block = pa.Table.from_pandas(block, preserve_index=False)
             else:
-                out[name] = pa.array(values)
-        return pa.table(out)
+                raise TypeError(f"a block must be a pyarrow.Table or pandas.DataFrame, got {type(block).__name__}")
+        if block.num_rows == 0:
+            if self._empty is None and block.num_columns:
+                self._empty = block
+            return
+        self._flush_rows()
+        self._tables.append(block)
+        self._rows += block.num_rows
+        self._table_bytes += block.nbytes
 
-    @staticmethod
-    def _concat_tables(tables: List[pa.Table]) -> pa.Table:
-        tables = [t for t in tables if t.num_columns > 0]
-        if not tables:
-            return empty_table()
-        if len(tables) == 1:
-            return tables[0]
-        return pa.concat_tables(tables, promote_options="permissive")
+    # -- output ----------------------------------------------------------------
+    def _flush_rows(self) -> None:
+        if self._pending:
+            t = pa.table({k: pa.array(v) for k, v in self._cols.items()})
+            self._row_bytes = t.nbytes / t.num_rows
+            self._tables.append(t)
+            self._table_bytes += t.nbytes
+            for v in self._cols.values():
+                v.clear()
+            self._pending = 0
 
     def will_build_yield_copy(self) -> bool:
-        if self._columns:
-            return True
-        return False  # Arrow concatenation is zero-copy (arrow_block.py:_concat_would_copy)
+        """False only when ``build`` can hand back the single table it was given."""
+        return not (len(self._tables) == 1 and self._pending == 0)
 
     def build(self) -> pa.Table:
-        tables = [self._table_from_pydict(self._columns)] if self._columns else []
-        tables.extend(self._tables)
-        if len(tables) > 0:
-            return self._concat_tables(tables)
-        return empty_table()
+        self._flush_rows()
+        if not self._tables:
+            return self._empty if self._empty is not None else empty_table()
+        if len(self._tables) == 1:
+            return self._tables[0]
+        return pa.concat_tables(self._tables, promote_options="permissive")
 
     def num_rows(self) -> int:
-        return self._num_rows
+        return self._rows
 
     def get_estimated_memory_usage(self) -> int:
-        if self._num_rows == 0:
-            return 0
-        for table in self._tables[self._tables_size_cursor:]:
-            self._tables_size_bytes += table.nbytes
-        self._tables_size_cursor = len(self._tables)
-        return self._tables_size_bytes + self._uncompacted_size.size_bytes()
-
-    def _compact_if_needed(self) -> None:
-        assert self._columns
-        if self._uncompacted_size.size_bytes() < MAX_UNCOMPACTED_SIZE_BYTES:
-            return
-        block = self._table_from_pydict(self._columns)
-        self.add_block(block)
-        self._num_rows -= block.num_rows  # add_block counted the rows a second time
-        self._uncompacted_size = SizeEstimator()
-        self._columns.clear()
-        self._num_compactions += 1
+        # pending rows: priced like the rows already converted (or 64 B before any were)
+        return int(self._table_bytes + self._pending * (self._row_bytes or 64.0))
 
 
-class DelegatingBlockBuilder:
-    """Picks the builder from the first thing added; an empty block is remembered and used
-    only if nothing else arrives (delegating_block_builder.py:37-66)."""
-
-    def __init__(self):
-        self._builder: Optional[ArrowBlockBuilder] = None
-        self._empty_block = None
-
-    def add(self, item: Mapping[str, Any]) -> None:
-        assert isinstance(item, collections.abc.Mapping), item
-        if self._builder is None:
-            self._builder = ArrowBlockBuilder()
-        self._builder.add(item)
-
-    def add_batch(self, batch) -> None:
-        from .block_accessor import B200ArrowBlockAccessor
-
-        if isinstance(batch, collections.abc.Mapping):
-            batch = pa.table({k: pa.array(np.asarray(v).tolist() if np.asarray(v).ndim > 1 else np.asarray(v))
-                              for k, v in batch.items()})
-        self.add_block(B200ArrowBlockAccessor.for_block(batch).to_arrow())
-
-    def add_block(self, block) -> None:
-        from .block_accessor import B200ArrowBlockAccessor
-
-        table = B200ArrowBlockAccessor.for_block(block).to_arrow()
-        if table.num_rows == 0:
-            self._empty_block = table
-            return
-        if self._builder is None:
-            self._builder = ArrowBlockBuilder()
-        self._builder.add_block(table)
-
-    def will_build_yield_copy(self) -> bool:
-        if self._builder is None:
-            return True
-        return self._builder.will_build_yield_copy()
-
-    def build(self) -> pa.Table:
-        if self._builder is None:
-            self._builder = ArrowBlockBuilder()
-            if self._empty_block is not None:
-                self._builder.add_block(self._empty_block)
-        return self._builder.build()
-
-    def num_rows(self) -> int:
-        return self._builder.num_rows() if self._builder is not None else 0
-
-    def get_estimated_memory_usage(self) -> int:
-        if self._builder is None:
-            return 0
-        return self._builder.get_estimated_memory_usage()
+# the reference's names for the same role
+ArrowBlockBuilder = BlockBuilder
+DelegatingBlockBuilder = BlockBuilder

@@ -2,6 +2,8 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+
+#include <atomic>
 #include "../../include/xchg_b200.h"
 
 void xchg_set_error(const char* fmt, ...);
@@ -24,6 +26,22 @@ void xchg_set_error(const char* fmt, ...);
       xchg_set_error(__VA_ARGS__);         \
       return XCHG_ERR_INVALID;             \
     }                                      \
+  } while (0)
+
+// Runs the statements the first time the enclosing call site is reached with each CUDA device
+// current (function attributes such as the dynamic shared-memory limit are per device /
+// context, not per process).  Thread-safe: two host threads may both run the body, which
+// is idempotent; a body that fails (XCHG_CUDA_TRY returns) leaves the device unmarked.
+#define XCHG_ONCE_PER_DEVICE(...)                                             \
+  do {                                                                        \
+    static std::atomic<uint64_t> done_mask__{0};                              \
+    int dev__ = 0;                                                            \
+    XCHG_CUDA_TRY(cudaGetDevice(&dev__));                                     \
+    const uint64_t bit__ = 1ull << (dev__ & 63);                              \
+    if (!(done_mask__.load(std::memory_order_acquire) & bit__)) {             \
+      __VA_ARGS__;                                                            \
+      done_mask__.fetch_or(bit__, std::memory_order_release);                 \
+    }                                                                         \
   } while (0)
 
 static inline uint64_t xchg_align_up(uint64_t x, uint64_t a) { return (x + a - 1) / a * a; }

@@ -439,14 +439,12 @@ extern "C" int xchg_gather_offsets(const int64_t* in_off, const uint32_t* idx, u
 static int launch_gather_rows(bool uniform, const uint8_t* in, const int64_t* in_off, uint32_t width,
                               const uint32_t* idx, uint64_t n_out, const int64_t* out_off,
                               uint8_t* out, uint32_t rows_per_tile, cudaStream_t s) {
-  static bool attr_done = false;
-  if (!attr_done) {
+  XCHG_ONCE_PER_DEVICE({
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)GR_SMEM));
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)GR_SMEM));
-    attr_done = true;
-  }
+  });
   const uint64_t ntiles = (n_out + rows_per_tile - 1) / rows_per_tile;
   const int cap = xchg_gather_ctas_per_sm();
   const int grid = (int)std::min<uint64_t>(ntiles, (uint64_t)xchg_sm_count() * (cap ? cap : 3 * 4));

@@ -238,8 +238,7 @@ static GatherSegs no_segs() {
 
 static int gather_uniform_launch(const uint8_t* in, uint32_t w, const uint32_t* idx, uint64_t n_out,
                                  uint8_t* out, const GatherSegs* multi, cudaStream_t s) {
-  static bool attr_done = false;
-  if (!attr_done) {
+  XCHG_ONCE_PER_DEVICE({
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<false, false>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gu_smem(GU_STAGE_MAX)));
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<true, false>,
@@ -248,8 +247,7 @@ static int gather_uniform_launch(const uint8_t* in, uint32_t w, const uint32_t* 
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gu_smem(GU_STAGE_MAX)));
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<true, true>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gu_smem(GU_STAGE_MAX)));
-    attr_done = true;
-  }
+  });
   uintptr_t align_bits = (uintptr_t)in | (uintptr_t)out;
   if (multi)
     for (int d = 0; d < multi->nseg; ++d) align_bits |= (uintptr_t)multi->out[d];

@@ -979,16 +979,11 @@ static int onesweep_pass(int mode, const uint64_t* kin, const uint32_t* vin, uin
                          uint32_t ntiles_seg, cudaStream_t s) {
   int threads, items;
   onesweep_shape(&threads, &items);
-  static bool attr_done[3][4] = {{false}};
 #define XCHG_ONESWEEP_CASE(MODE, SEG, THREADS, ITEMS, SLOT)                                             \
   {                                                                                                    \
-    constexpr int ROW = (SEG) ? 2 : MODE;                                                              \
-    if (!attr_done[ROW][SLOT]) {                                                                       \
-      XCHG_CUDA_TRY(cudaFuncSetAttribute(k_onesweep<MODE, THREADS, ITEMS, SEG>,                        \
+    XCHG_ONCE_PER_DEVICE(XCHG_CUDA_TRY(cudaFuncSetAttribute(k_onesweep<MODE, THREADS, ITEMS, SEG>,     \
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,                  \
-                                         (int)rs_smem(THREADS, ITEMS)));                               \
-      attr_done[ROW][SLOT] = true;                                                                     \
-    }                                                                                                  \
+                                         (int)rs_smem(THREADS, ITEMS))));                              \
     const uint32_t ntiles = (SEG) ? ntiles_seg : (n + THREADS * ITEMS - 1) / (THREADS * ITEMS);        \
     XCHG_LAUNCH(XK_ONESWEEP, s,                                                                        \
                 k_onesweep<MODE, THREADS, ITEMS, SEG><<<ntiles, THREADS, rs_smem(THREADS, ITEMS), s>>>( \
@@ -1029,7 +1024,6 @@ static int seg_hist_pass(const uint64_t* keys, int shift, const Seg* segs, const
 static int local_sort_level(const uint64_t* src_k, const uint32_t* src_v, uint64_t* dst_k, uint32_t* dst_v,
                             uint64_t* const* small, const uint32_t* nsmall, const LocalPlaces& lp,
                             cudaStream_t s) {
-  static bool attr_done = false;
   // 8 rows per thread (256 / 512 threads) for the 2048- and 4096-row classes: same speed as
   // 16 rows per thread on fewer threads, and the shape that can use match_digit_asm;
   // XCHG_LS_WIDE2=0 / XCHG_LS_WIDE3=0 select 128 x 16 / 256 x 16
@@ -1041,7 +1035,7 @@ static int local_sort_level(const uint64_t* src_k, const uint32_t* src_v, uint64
     const char* f = getenv("XCHG_LS_WIDE3");
     wide3 = (f && atoi(f) == 0) ? 0 : 1;
   }
-  if (!attr_done) {
+  XCHG_ONCE_PER_DEVICE({
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_local_sort<128, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)ls_smem(128, 16)));
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_local_sort<256, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1052,8 +1046,7 @@ static int local_sort_level(const uint64_t* src_k, const uint32_t* src_v, uint64
                                        (int)ls_smem(512, 16)));
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_local_sort<512, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)ls_smem(512, 8)));
-    attr_done = true;
-  }
+  });
 #define XCHG_LOCAL_SORT(CLS, THREADS, ITEMS)                                                         \
   if (nsmall[CLS])                                                                                   \
     XCHG_LAUNCH(XK_LOCAL_SORT, s,                                                                    \

@@ -61,8 +61,10 @@ class Runtime:
         self.launches = 0  # kernels launched through this runtime (bench bookkeeping)
         self._size_classes = set()  # sizes of large device buffers handed out so far
         if self.is_cuda:
-            # random row / key gathers: fetch sectors, not 128-byte lines, from HBM
-            gran = int(os.environ.get("XCHG_L2_FETCH_GRANULARITY", "32"))
+            # opt-in only: the device-wide fetch-granularity limit changes nothing measurable
+            # (profiles/r01_fetch_granularity.md; the gathers' .L2::64B loads do the work) and
+            # a library should not alter a device-wide setting of its host process
+            gran = int(os.environ.get("XCHG_L2_FETCH_GRANULARITY", "0"))
             if gran:
                 with torch.cuda.device(self.device):
                     _cabi.call("xchg_set_l2_fetch_granularity", gran)

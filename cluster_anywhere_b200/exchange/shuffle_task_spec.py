@@ -11,6 +11,7 @@ import pyarrow as pa
 
 from ..block import BlockExecStats, BlockMetadata
 from ..block_accessor import B200ArrowBlockAccessor
+from ..block_builder import DelegatingBlockBuilder
 from .interfaces import ExchangeTaskSpec
 
 logger = logging.getLogger(__name__)
@@ -67,9 +68,12 @@ class ShuffleTaskSpec(ExchangeTaskSpec):
                partial_reduce: bool = False) -> Tuple[pa.Table, BlockMetadata]:
         """shuffle_task_spec.py:106-132."""
         stats = BlockExecStats.builder()
-        blocks = [B200ArrowBlockAccessor.for_block(b).to_arrow() for b in mapper_outputs]
-        blocks = [b for b in blocks if b.num_columns > 0]
-        new_block = pa.concat_tables(blocks, promote_options="permissive") if blocks else pa.table({})
+        builder = DelegatingBlockBuilder()
+        for b in mapper_outputs:
+            b = B200ArrowBlockAccessor.for_block(b).to_arrow()
+            if b.num_columns > 0:
+                builder.add_block(b)
+        new_block = builder.build()
         acc = B200ArrowBlockAccessor.for_block(new_block)
         if random_shuffle:
             new_block = acc.random_shuffle(random_seed if random_seed is not None else None)

@@ -283,7 +283,10 @@ int xchg_gather_offsets(const int64_t* in_off, const uint32_t* idx, uint64_t n_o
  *    the GPU race on it, so serialise them.  Left-over contents of an earlier
  *    call are harmless (each call overwrites every slot before reading it).
  *  - The first call on each device resolves the array's device address; make it
- *    outside any stream capture, with the target device current.
+ *    outside any stream capture, with the target device current.  The address is
+ *    cached per device ordinal for the life of the process: after cudaDeviceReset
+ *    (or any teardown of the device's primary context) it is stale and this entry
+ *    point must not be used again in that process.
  * Output is identical to xchg_gather_offsets.
  */
 #define XCHG_STATIC_GATHER_MAX_ROWS ((uint64_t)(64u << 20))

@@ -17,7 +17,7 @@ import _golden as G
 from cluster_anywhere_b200 import Count, Mean, SortKey, Sum
 from cluster_anywhere_b200 import planner as P
 from cluster_anywhere_b200.block import BlockMetadata
-from cluster_anywhere_b200.block_builder import ArrowBlockBuilder, DelegatingBlockBuilder, SizeEstimator
+from cluster_anywhere_b200.block_builder import ArrowBlockBuilder, DelegatingBlockBuilder
 from oracle import exchange_oracle as O
 
 STRATEGIES = [P.ShuffleStrategy.SORT_SHUFFLE_PULL_BASED, P.ShuffleStrategy.SORT_SHUFFLE_PUSH_BASED,
@@ -242,12 +242,12 @@ def test_block_builders():
     assert b.num_rows() == 0 and b.get_estimated_memory_usage() == 0 and b.build().num_rows == 0
     for i in range(25):
         b.add({"x": i, "y": str(i)})
-    assert b.will_build_yield_copy()
+    assert b.will_build_yield_copy() and b.get_estimated_memory_usage() > 0
     b.add_block(pa.table({"x": [100, 101], "y": ["a", "b"]}))
     t = b.build()
     assert b.num_rows() == 27 and t.num_rows == 27
     assert t["x"].to_pylist() == list(range(25)) + [100, 101]
-    assert b.get_estimated_memory_usage() > 0
+    assert b.get_estimated_memory_usage() == t.nbytes
     with pytest.raises(ValueError):
         b.add({"x": 1})  # different columns
     with pytest.raises(ValueError):
@@ -261,23 +261,18 @@ def test_block_builders():
     assert d.build().schema == empty.schema  # the empty block is used when nothing else arrives
     d = DelegatingBlockBuilder()
     d.add_block(empty)
-    d.add_block(pa.table({"x": [1, 2]}))
+    one = pa.table({"x": [1, 2]})
+    d.add_block(one)
+    assert not d.will_build_yield_copy() and d.build() is one
     d.add_block(pa.table({"x": [3]}))
-    assert d.build()["x"].to_pylist() == [1, 2, 3] and d.num_rows() == 3 and not d.will_build_yield_copy()
+    assert d.build()["x"].to_pylist() == [1, 2, 3] and d.num_rows() == 3 and d.will_build_yield_copy()
     d = DelegatingBlockBuilder()
     d.add({"k": 1, "acc": [1.0, 2.0]})
     d.add({"k": 2, "acc": [3.0, 4.0]})
     assert d.build()["acc"].to_pylist() == [[1.0, 2.0], [3.0, 4.0]]
-    # SizeEstimator samples the first 10 items, every 10th up to 100, every 100th after
-    calls = []
+    import pandas as pd
 
-    class Probe(SizeEstimator):
-        def _real_size(self, item):
-            calls.append(item)
-            return 8
-
-    p = Probe()
-    for i in range(1, 351):
-        p.add(i)
-    assert calls == list(range(1, 11)) + list(range(20, 101, 10)) + [200, 300]
-    assert p.size_bytes() == 8 * 350
+    d = DelegatingBlockBuilder()
+    d.add_block(pd.DataFrame({"x": [5, 6]}))
+    d.add({"x": 7})
+    assert d.build()["x"].to_pylist() == [5, 6, 7]

@@ -65,3 +65,29 @@ def test_static_scratch_variant_matches_workspace_variant():
     rc = lib.xchg_gather_offsets_static(_vp(got), _vp(got), too_many, _vp(got), stream)
     assert rc == -4  # XCHG_ERR_LIMIT
     assert b"XCHG_STATIC_GATHER_MAX_ROWS" in lib.xchg_last_error()
+
+
+@pytest.mark.gpu
+def test_static_scratch_variant_at_its_row_limit():
+    """Exactly XCHG_STATIC_GATHER_MAX_ROWS rows: every one of the built-in scratch's tile
+    slots is in use, and the last offset is still the sum of all gathered lengths."""
+    import torch
+
+    from cluster_anywhere_b200 import _cabi
+
+    _cabi._install_test_double(None)
+    lib = _cabi.load()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    n_in, n_out = 1000, 64 << 20
+    g = torch.Generator(device=dev)
+    g.manual_seed(5)
+    lens = torch.randint(0, 9, (n_in,), dtype=torch.int64, device=dev, generator=g)
+    in_off = torch.cat([torch.zeros(1, dtype=torch.int64, device=dev), torch.cumsum(lens, 0)])
+    idx = torch.randint(0, n_in, (n_out,), dtype=torch.int32, device=dev, generator=g)
+    got = torch.empty(n_out + 1, dtype=torch.int64, device=dev)
+    _cabi.check(lib.xchg_gather_offsets_static(_vp(in_off), _vp(idx), n_out, _vp(got), stream),
+                "xchg_gather_offsets_static")
+    torch.cuda.synchronize()
+    exp = torch.cumsum(lens[idx.long()], 0)
+    assert int(got[0].item()) == 0 and torch.equal(got[1:], exp)
