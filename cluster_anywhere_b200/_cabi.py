@@ -37,6 +37,18 @@ _SIGNATURES = {
     "xchg_set_sort_algorithm": (c_int, [c_int]),
     "xchg_partition_bounds": (c_int, [ctypes.POINTER(c_void_p), _P, _P, _P, c_int, c_uint64, _P, _P, _P, c_int, c_int, _P, _P]),
     "xchg_assign_partitions": (c_int, [ctypes.POINTER(c_void_p), _P, c_int, c_uint64, _P, _P, _P, c_int, c_int, _P, _P, _P]),
+    "xchg_sample_keys": (c_int, [_P, c_int, c_int, _P, c_int64, ctypes.POINTER(c_uint64), ctypes.POINTER(c_uint64),
+                                 c_int, c_uint32, c_uint64, c_uint64, _P, c_uint64, ctypes.POINTER(c_uint64), _P]),
+    "xchg_select_boundaries": (c_int, [_P, c_int, c_uint64, c_uint32, c_uint32, c_uint32, _P, _P, _P]),
+    "xchg_partition_hist": (c_int, [_P, c_int, c_int, c_uint64, _P, ctypes.POINTER(c_uint32),
+                                    ctypes.POINTER(ctypes.c_uint8), c_int, _P, _P]),
+    "xchg_partition_workspace_bytes": (c_int, [c_uint64, ctypes.POINTER(c_uint64)]),
+    "xchg_partition_rows": (c_int, [_P, c_int, c_int, c_uint64, _P, ctypes.POINTER(c_uint32),
+                                    ctypes.POINTER(ctypes.c_uint8), c_int, _P, _P, _P, _P, c_uint64, _P]),
+    "xchg_copy_segments": (c_int, [c_int, ctypes.POINTER(c_void_p), ctypes.POINTER(c_void_p),
+                                   ctypes.POINTER(c_uint64), _P]),
+    "xchg_signal_flags": (c_int, [ctypes.POINTER(c_void_p), c_int, c_uint32, _P]),
+    "xchg_wait_flags": (c_int, [_P, c_int, c_uint32, c_uint64, _P, _P]),
     "xchg_shuffle_positions": (c_int, [c_uint64, c_uint64, c_uint64, c_uint64, c_int, _P, _P]),
     "xchg_invert_permutation": (c_int, [_P, c_uint64, c_uint64, _P, _P]),
     "xchg_even_split_dest": (c_int, [_P, c_uint64, c_uint64, c_uint32, _P, _P, _P]),

@@ -18,6 +18,7 @@
 #include <type_traits>
 
 #include "common.cuh"
+#include "keynorm.cuh"
 
 namespace {
 
@@ -33,6 +34,8 @@ constexpr int RS_DEFAULT_THREADS = 256;
 constexpr int RS_DEFAULT_ITEMS = 16;
 constexpr int RS_BATCH = 4;  // items ranked together (independent match / atomic / shuffle chains)
 constexpr size_t rs_smem(int threads, int items) { return (size_t)threads * items * 12 + (BINS + BINS + 32) * 4; }
+// MODE 2 (destination partition) keeps its thresholds behind the pass's own shared memory
+constexpr size_t RS_RULE_SMEM = (size_t)BINS * 8 + BINS;
 // CTAs per SM by items per thread (register budget: 2 regs per key + rank + ~24)
 constexpr int rs_min_blocks(int threads, int items) {
   return (items >= 16 ? 1024 : (items >= 12 ? 1280 : 1536)) / threads;
@@ -46,41 +49,6 @@ constexpr uint32_t FLAG_INCL = 2u << 30;
 constexpr uint32_t VAL_MASK = (1u << 30) - 1;
 
 // ------------------------------------------------------------------ K2 -----
-
-template <typename T>
-__device__ __forceinline__ uint64_t norm_value(T x, bool desc) {
-  if constexpr (std::is_same<T, float>::value) {
-    if (x != x) return 0xFFFFFFFEull;  // NaN after every number, both directions
-    uint32_t b = __float_as_uint(x);
-    if (x == 0.0f) b = 0;  // -0.0 ties with +0.0 (Arrow compares numerically)
-    uint32_t t = (b & 0x80000000u) ? ~b : (b | 0x80000000u);
-    if (desc) t = ~t;
-    return (uint64_t)t;
-  } else if constexpr (std::is_same<T, double>::value) {
-    if (x != x) return 0xFFFFFFFFFFFFFFFEull;
-    uint64_t b = (uint64_t)__double_as_longlong(x);
-    if (x == 0.0) b = 0;
-    uint64_t t = (b >> 63) ? ~b : (b | 0x8000000000000000ull);
-    if (desc) t = ~t;
-    return t;
-  } else {
-    using U = typename std::make_unsigned<T>::type;
-    U u = (U)x;
-    if constexpr (std::is_signed<T>::value) u ^= (U)((U)1 << (sizeof(T) * 8 - 1));
-    if (desc) u = (U)~u;
-    return (uint64_t)u;
-  }
-}
-
-// Key of a null row: one past the largest key a value can take (nulls last in both
-// directions).  64-bit integers have no spare value: they use UINT64_MAX and the
-// sort appends a 9th, validity-driven pass.
-template <typename T>
-__device__ __forceinline__ uint64_t null_key() {
-  if constexpr (std::is_same<T, float>::value) return 0xFFFFFFFFull;
-  else if constexpr (sizeof(T) == 8) return 0xFFFFFFFFFFFFFFFFull;
-  else return 1ull << (sizeof(T) * 8);
-}
 
 template <typename T>
 __global__ void __launch_bounds__(256)
@@ -240,13 +208,41 @@ struct Seg {
 // SEG = false: one LSD / top-level pass over the whole array.  SEG = true: the same pass
 // run independently inside every segment of an MSD level (tile -> segment through
 // tile_seg; digit offsets, look-back and output positions are relative to the segment).
-template <int MODE, int RS_THREADS, int RS_ITEMS, bool SEG>
+// RAW passes (the first pass over a column): the keys are read in their own type and
+// normalised in registers instead of being read from a materialised radix-key array.
+// MODE 2: the "digit" of a row is its destination under the thresholds (keynorm.cuh): the
+// same stable one-pass partition, by range instead of by byte.
+struct RawKeys {
+  const void* keys;       // raw key column (RAW passes), key_type elements
+  int key_type, desc;
+  const uint64_t* thr;    // MODE 2: nthr thresholds in sort order + their strict flags
+  const uint8_t* strict;
+  int nthr;
+};
+
+template <typename T, int RS_ITEMS>
+__device__ __forceinline__ void load_raw_keys(const void* keys_, bool desc, uint32_t warp_base, uint32_t n,
+                                              bool full, uint64_t (&key)[RS_ITEMS]) {
+  const T* keys = reinterpret_cast<const T*>(keys_);
+  if (full) {
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; ++i) key[i] = norm_value<T>(keys[warp_base + 32 * i], desc);
+  } else {
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; ++i) {
+      const uint32_t idx = warp_base + 32 * i;
+      key[i] = idx < n ? norm_value<T>(keys[idx], desc) : 0xFFFFFFFFFFFFFFFFull;
+    }
+  }
+}
+
+template <int MODE, int RS_THREADS, int RS_ITEMS, bool SEG, bool RAW = false>
 __global__ void __launch_bounds__(RS_THREADS, rs_min_blocks(RS_THREADS, RS_ITEMS))
 k_onesweep(const uint64_t* __restrict__ keys_in_, const uint32_t* __restrict__ vals_in_,
            uint64_t* __restrict__ keys_out_, uint32_t* __restrict__ vals_out_, uint32_t n_,
            int shift, const uint32_t* __restrict__ gexcl_, uint32_t* status,
            uint32_t* tile_counter, const uint8_t* __restrict__ validity, int64_t vbit,
-           const Seg* __restrict__ segs, const uint32_t* __restrict__ tile_seg) {
+           const Seg* __restrict__ segs, const uint32_t* __restrict__ tile_seg, RawKeys raw) {
   constexpr int RS_WARPS = RS_THREADS / 32;
   constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
   extern __shared__ __align__(16) uint8_t smem[];
@@ -256,11 +252,19 @@ k_onesweep(const uint64_t* __restrict__ keys_in_, const uint32_t* __restrict__ v
   uint32_t* sbase = reinterpret_cast<uint32_t*>(smem + (size_t)RS_TILE * 12);
   uint32_t* sstart = sbase + BINS;
   uint32_t* smisc = sstart + BINS;  // [0..7] warp sums of the digit scan, [16] tile id
+  uint64_t* thr_s = reinterpret_cast<uint64_t*>(smisc + 32);  // MODE 2 only
+  uint8_t* strict_s = reinterpret_cast<uint8_t*>(thr_s + BINS);
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
   if (tid == 0) smisc[16] = atomicAdd(tile_counter, 1u);
   for (int j = tid; j < RS_WARPS * BINS; j += RS_THREADS) whist[j] = 0;
+  if constexpr (MODE == 2) {
+    for (int j = tid; j < raw.nthr; j += RS_THREADS) {
+      thr_s[j] = raw.thr[j];
+      strict_s[j] = raw.strict[j];
+    }
+  }
   __syncthreads();
   const uint32_t tile = smisc[16];
   const uint64_t* keys_in = keys_in_;
@@ -288,7 +292,21 @@ k_onesweep(const uint64_t* __restrict__ keys_in_, const uint32_t* __restrict__ v
   // ---- load (warp-striped: item i of lane l sits at warp_base + 32*i) ----
   uint64_t key[RS_ITEMS];
   uint32_t val[RS_ITEMS];  // only live in MODE 1 (the compiler drops it otherwise)
-  if (full) {
+  if constexpr (RAW) {
+    const bool dsc = raw.desc != 0;
+    switch (raw.key_type) {  // uniform over the grid
+      case XCHG_I8: load_raw_keys<int8_t>(raw.keys, dsc, warp_base, n, full, key); break;
+      case XCHG_I16: load_raw_keys<int16_t>(raw.keys, dsc, warp_base, n, full, key); break;
+      case XCHG_I32: load_raw_keys<int32_t>(raw.keys, dsc, warp_base, n, full, key); break;
+      case XCHG_I64: load_raw_keys<int64_t>(raw.keys, dsc, warp_base, n, full, key); break;
+      case XCHG_U8: load_raw_keys<uint8_t>(raw.keys, dsc, warp_base, n, full, key); break;
+      case XCHG_U16: load_raw_keys<uint16_t>(raw.keys, dsc, warp_base, n, full, key); break;
+      case XCHG_U32: load_raw_keys<uint32_t>(raw.keys, dsc, warp_base, n, full, key); break;
+      case XCHG_U64: load_raw_keys<uint64_t>(raw.keys, dsc, warp_base, n, full, key); break;
+      case XCHG_F32: load_raw_keys<float>(raw.keys, dsc, warp_base, n, full, key); break;
+      default: load_raw_keys<double>(raw.keys, dsc, warp_base, n, full, key); break;
+    }
+  } else if (full) {
 #pragma unroll
     for (int i = 0; i < RS_ITEMS; ++i) key[i] = keys_in[warp_base + 32 * i];
   } else {
@@ -304,6 +322,23 @@ k_onesweep(const uint64_t* __restrict__ keys_in_, const uint32_t* __restrict__ v
     if constexpr (MODE == 1) val[i] = idx < n ? (vals_in ? vals_in[idx] : idx) : 0xFFFFFFFFu;
     else val[i] = 0u;
   }
+
+  // MODE 2: destinations are found once (a binary search each) and kept, four to a register;
+  // rows past the end of the last tile rank behind every real row (bin 255)
+  uint32_t dg[MODE == 2 ? RS_ITEMS / 4 : 1];
+  if constexpr (MODE == 2) {
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; ++i) {
+      const uint32_t idx = warp_base + 32 * i;
+      const uint32_t d = (full || idx < n) ? dest_of(key[i], thr_s, strict_s, raw.nthr) : 255u;
+      if ((i & 3) == 0) dg[i >> 2] = d;
+      else dg[i >> 2] |= d << (8 * (i & 3));
+    }
+  }
+  auto digit_at = [&](int i) -> uint32_t {
+    if constexpr (MODE == 2) return (dg[i >> 2] >> (8 * (i & 3))) & 255u;
+    else return digit_of<MODE>(key[i], val[i], shift, validity, vbit);
+  };
 
   // ---- rank inside the warp, in (i, lane) = memory order: stable ----
   // RS_BATCH items at a time: match masks first (independent), then the leaders' counter
@@ -321,7 +356,7 @@ k_onesweep(const uint64_t* __restrict__ keys_in_, const uint32_t* __restrict__ v
     unsigned m[RS_BATCH];
 #pragma unroll
     for (int u = 0; u < RS_BATCH; ++u) {
-      d[u] = digit_of<MODE>(key[h + u], val[h + u], shift, validity, vbit);
+      d[u] = digit_at(h + u);
       m[u] = match_digit_asm(d[u]);
     }
     uint32_t prev[RS_BATCH];
@@ -408,8 +443,8 @@ k_onesweep(const uint64_t* __restrict__ keys_in_, const uint32_t* __restrict__ v
   // ---- final in-tile ranks (both halves of a register at once: no carry, ranks < 65536) ----
 #pragma unroll
   for (int i = 0; i < RS_ITEMS; i += 2) {
-    const uint32_t d0 = digit_of<MODE>(key[i], val[i], shift, validity, vbit);
-    const uint32_t d1 = digit_of<MODE>(key[i + 1], val[i + 1], shift, validity, vbit);
+    const uint32_t d0 = digit_at(i);
+    const uint32_t d1 = digit_at(i + 1);
     rank2[i >> 1] += (myhist[d0] + sstart[d0]) + ((myhist[d1] + sstart[d1]) << 16);
   }
   __syncthreads();  // whist is dead from here: skeys may overwrite it
@@ -437,7 +472,10 @@ k_onesweep(const uint64_t* __restrict__ keys_in_, const uint32_t* __restrict__ v
       const uint32_t pos = i * RS_THREADS + tid;
       const uint64_t k = skeys[pos];
       const uint32_t v = svals[pos];
-      const uint32_t g = sbase[digit_of<MODE>(k, v, shift, validity, vbit)] + pos;
+      uint32_t dd;
+      if constexpr (MODE == 2) dd = dest_of(k, thr_s, strict_s, raw.nthr);
+      else dd = digit_of<MODE>(k, v, shift, validity, vbit);
+      const uint32_t g = sbase[dd] + pos;
       keys_out[g] = k;
       vals_out[g] = v;
     }
@@ -448,7 +486,10 @@ k_onesweep(const uint64_t* __restrict__ keys_in_, const uint32_t* __restrict__ v
       if (pos < tile_items) {
         const uint64_t k = skeys[pos];
         const uint32_t v = svals[pos];
-        const uint32_t g = sbase[digit_of<MODE>(k, v, shift, validity, vbit)] + pos;
+        uint32_t dd;
+        if constexpr (MODE == 2) dd = dest_of(k, thr_s, strict_s, raw.nthr);
+        else dd = digit_of<MODE>(k, v, shift, validity, vbit);
+        const uint32_t g = sbase[dd] + pos;
         keys_out[g] = k;
         vals_out[g] = v;
       }
@@ -972,30 +1013,36 @@ static void onesweep_shape(int* threads_out, int* items_out) {
 
 // One onesweep pass.  segs == NULL: over the whole array of n rows (mode 1 = validity
 // place).  segs != NULL: inside every segment of an MSD level, ntiles_seg tiles in all.
+// raw != NULL: a RAW pass (keys read in their own type, see RawKeys); mode 2 = partition
+// by destination (always RAW).  RAW passes use the default CTA shape.
 static int onesweep_pass(int mode, const uint64_t* kin, const uint32_t* vin, uint64_t* kout,
                          uint32_t* vout, uint32_t n, int shift, const uint32_t* gexcl,
                          uint32_t* status, uint32_t* tile_counter, const uint8_t* validity,
                          int64_t vbit, const Seg* segs, const uint32_t* tile_seg,
-                         uint32_t ntiles_seg, cudaStream_t s) {
+                         uint32_t ntiles_seg, cudaStream_t s, const RawKeys* raw = nullptr) {
   int threads, items;
   onesweep_shape(&threads, &items);
-#define XCHG_ONESWEEP_CASE(MODE, SEG, THREADS, ITEMS, SLOT)                                             \
+  const RawKeys no_raw = {nullptr, 0, 0, nullptr, nullptr, 0};
+#define XCHG_ONESWEEP_CASE(MODE, SEG, THREADS, ITEMS, RAW, EXTRA)                                       \
   {                                                                                                    \
-    XCHG_ONCE_PER_DEVICE(XCHG_CUDA_TRY(cudaFuncSetAttribute(k_onesweep<MODE, THREADS, ITEMS, SEG>,     \
+    XCHG_ONCE_PER_DEVICE(XCHG_CUDA_TRY(cudaFuncSetAttribute(k_onesweep<MODE, THREADS, ITEMS, SEG, RAW>, \
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,                  \
-                                         (int)rs_smem(THREADS, ITEMS))));                              \
+                                         (int)(rs_smem(THREADS, ITEMS) + (EXTRA)))));                  \
     const uint32_t ntiles = (SEG) ? ntiles_seg : (n + THREADS * ITEMS - 1) / (THREADS * ITEMS);        \
     XCHG_LAUNCH(XK_ONESWEEP, s,                                                                        \
-                k_onesweep<MODE, THREADS, ITEMS, SEG><<<ntiles, THREADS, rs_smem(THREADS, ITEMS), s>>>( \
+                k_onesweep<MODE, THREADS, ITEMS, SEG, RAW>                                             \
+                <<<ntiles, THREADS, rs_smem(THREADS, ITEMS) + (EXTRA), s>>>(                           \
                     kin, vin, kout, vout, n, shift, gexcl, status, tile_counter, validity, vbit, segs,  \
-                    tile_seg));                                                                        \
+                    tile_seg, raw ? *raw : no_raw));                                                   \
   }
 #define XCHG_ONESWEEP_MODE(MODE, SEG)                                          \
-  if (threads == 512) XCHG_ONESWEEP_CASE(MODE, SEG, 512, 16, 0)                \
-  else if (items == 16) XCHG_ONESWEEP_CASE(MODE, SEG, 256, 16, 1)              \
-  else if (items == 12) XCHG_ONESWEEP_CASE(MODE, SEG, 256, 12, 2)              \
-  else XCHG_ONESWEEP_CASE(MODE, SEG, 256, 8, 3)
-  if (segs) { XCHG_ONESWEEP_MODE(0, true) }
+  if (threads == 512) XCHG_ONESWEEP_CASE(MODE, SEG, 512, 16, false, 0)         \
+  else if (items == 16) XCHG_ONESWEEP_CASE(MODE, SEG, 256, 16, false, 0)       \
+  else if (items == 12) XCHG_ONESWEEP_CASE(MODE, SEG, 256, 12, false, 0)       \
+  else XCHG_ONESWEEP_CASE(MODE, SEG, 256, 8, false, 0)
+  if (raw && mode == 2) { XCHG_ONESWEEP_CASE(2, false, RS_DEFAULT_THREADS, RS_DEFAULT_ITEMS, true, RS_RULE_SMEM) }
+  else if (raw) { XCHG_ONESWEEP_CASE(0, false, RS_DEFAULT_THREADS, RS_DEFAULT_ITEMS, true, 0) }
+  else if (segs) { XCHG_ONESWEEP_MODE(0, true) }
   else if (mode == 0) { XCHG_ONESWEEP_MODE(0, false) }
   else { XCHG_ONESWEEP_MODE(1, false) }
 #undef XCHG_ONESWEEP_MODE
@@ -1236,6 +1283,109 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
     if (nbig == 0) break;
   }
   return XCHG_OK;
+}
+
+// ---- stable partition of a block's rows by destination (the exchange's map side) ----
+
+int xchg_internal_fill_rule(DestRule* rule, const uint32_t* pick_host, const uint8_t* strict_host, int nthr);
+
+namespace {
+struct PartitionWorkspace {
+  uint32_t* gexcl;         // BINS
+  uint32_t* tile_counter;  // 16
+  uint64_t* thr;           // BINS
+  uint8_t* strict;         // BINS
+  uint32_t* status;        // ntiles * BINS
+  uint64_t total;
+};
+PartitionWorkspace carve_partition(void* base, uint64_t n) {
+  PartitionWorkspace w;
+  uint64_t off = 0;
+  auto take = [&](uint64_t bytes) {
+    uint64_t o = off;
+    off = xchg_align_up(off + bytes, 256);
+    return (uint8_t*)base + o;
+  };
+  const uint64_t ntiles = n / (RS_DEFAULT_THREADS * RS_DEFAULT_ITEMS) + 1;
+  w.gexcl = (uint32_t*)take(BINS * 4);
+  w.tile_counter = (uint32_t*)take(64);
+  w.thr = (uint64_t*)take(BINS * 8);
+  w.strict = (uint8_t*)take(BINS);
+  w.status = (uint32_t*)take(ntiles * BINS * 4);
+  w.total = off;
+  return w;
+}
+
+// thresholds picked from the boundary list, and the exclusive scan of the destination counts
+__global__ void __launch_bounds__(BINS)
+k_partition_prepare(const uint64_t* __restrict__ bounds, DestRule rule, const unsigned long long* __restrict__ counts,
+                    uint64_t* __restrict__ thr, uint8_t* __restrict__ strict, uint32_t* __restrict__ gexcl) {
+  __shared__ uint32_t wsum[BINS / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid < rule.nthr) {
+    thr[tid] = bounds[rule.pick[tid]];
+    strict[tid] = rule.strict[tid];
+  }
+  const uint32_t c = tid <= rule.nthr ? (uint32_t)counts[tid] : 0u;
+  uint32_t x = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= o) x += y;
+  }
+  if (lane == 31) wsum[warp] = x;
+  __syncthreads();
+  uint32_t base = 0;
+  for (int w = 0; w < warp; ++w) base += wsum[w];
+  gexcl[tid] = base + x - c;
+}
+}  // namespace
+
+extern "C" int xchg_partition_workspace_bytes(uint64_t n, uint64_t* bytes_out) {
+  XCHG_REQUIRE(bytes_out != nullptr, "bytes_out is NULL");
+  if (n > XCHG_MAX_ROWS) {
+    xchg_set_error("n=%llu exceeds XCHG_MAX_ROWS", (unsigned long long)n);
+    return XCHG_ERR_LIMIT;
+  }
+  *bytes_out = carve_partition(nullptr, n).total + 256;
+  return XCHG_OK;
+}
+
+extern "C" int xchg_partition_rows(const void* keys, int key_type, int descending, uint64_t n,
+                                   const uint64_t* bounds, const uint32_t* pick_host,
+                                   const uint8_t* strict_host, int nthr, const uint64_t* counts,
+                                   uint64_t* keys_out, uint32_t* rows_out, void* workspace,
+                                   uint64_t workspace_bytes, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  if (n == 0) return XCHG_OK;
+  XCHG_REQUIRE(keys && counts && keys_out && rows_out && workspace, "NULL argument");
+  XCHG_REQUIRE(key_type >= XCHG_I8 && key_type <= XCHG_F64, "unknown key_type %d", key_type);
+  XCHG_REQUIRE(nthr == 0 || bounds, "NULL bounds");
+  if (n > XCHG_MAX_ROWS) {
+    xchg_set_error("n=%llu exceeds XCHG_MAX_ROWS", (unsigned long long)n);
+    return XCHG_ERR_LIMIT;
+  }
+  DestRule rule;
+  int rc = xchg_internal_fill_rule(&rule, pick_host, strict_host, nthr);
+  if (rc) return rc;
+  uint8_t* base = (uint8_t*)xchg_align_up((uint64_t)(uintptr_t)workspace, 256);
+  PartitionWorkspace w = carve_partition(base, n);
+  if ((uint64_t)(base - (uint8_t*)workspace) + w.total > workspace_bytes) {
+    xchg_set_error("partition workspace too small: have %llu, need %llu",
+                   (unsigned long long)workspace_bytes, (unsigned long long)(w.total + 256));
+    return XCHG_ERR_WORKSPACE;
+  }
+  const uint32_t n32 = (uint32_t)n;
+  const uint32_t ntiles = (n32 + RS_DEFAULT_THREADS * RS_DEFAULT_ITEMS - 1) / (RS_DEFAULT_THREADS * RS_DEFAULT_ITEMS);
+  XCHG_CUDA_TRY(cudaMemsetAsync(w.tile_counter, 0, 64, s));
+  XCHG_CUDA_TRY(cudaMemsetAsync(w.status, 0, (size_t)ntiles * BINS * 4, s));
+  XCHG_LAUNCH(XK_PARTITION, s,
+              k_partition_prepare<<<1, BINS, 0, s>>>(bounds, rule, (const unsigned long long*)counts, w.thr,
+                                                    w.strict, w.gexcl));
+  XCHG_LAUNCH_CHECK();
+  const RawKeys raw = {keys, key_type, descending, w.thr, w.strict, nthr};
+  return onesweep_pass(2, nullptr, nullptr, keys_out, rows_out, n32, 0, w.gexcl, w.status, w.tile_counter,
+                       nullptr, 0, nullptr, nullptr, 0, s, &raw);
 }
 
 extern "C" int xchg_denormalize_keys(const uint64_t* norm, int key_type, int descending, uint64_t n,

@@ -44,9 +44,24 @@ def _trace(rt, name):
     _t_last[0] = now
 
 
+def _unwrap(group):
+    """-> (comm or None, torch process group).  ``group`` may be a torch process group
+    (None = the default one) or one of exchange/comm.py's communicators."""
+    from .comm import ThreadComm, TorchComm
+
+    if isinstance(group, ThreadComm):
+        return group, None
+    if isinstance(group, TorchComm):
+        return None, group.group
+    return None, group
+
+
 def world(group=None):
+    comm, pg = _unwrap(group)
+    if comm is not None:
+        return comm.rank, comm.world
     if dist.is_available() and dist.is_initialized():
-        return dist.get_rank(group), dist.get_world_size(group)
+        return dist.get_rank(pg), dist.get_world_size(pg)
     return 0, 1
 
 
@@ -54,8 +69,11 @@ def all_gather_object(obj, group=None) -> list:
     rank, size = world(group)
     if size == 1:
         return [obj]
+    comm, pg = _unwrap(group)
+    if comm is not None:
+        return comm.all_gather_object(obj)
     out = [None] * size
-    dist.all_gather_object(out, obj, group=group)
+    dist.all_gather_object(out, obj, group=pg)
     return out
 
 
@@ -74,9 +92,13 @@ def gather_dataset_info(rt: dev.Runtime, num_blocks: int, num_rows: int, schema,
     if schema is not None:
         fp = int.from_bytes(hashlib.blake2b(schema.serialize().to_pybytes(), digest_size=7).digest(), "little") | 1
     mine = torch.tensor([int(num_blocks), int(num_rows), fp], dtype=torch.int64, device=rt.device)
-    parts = [torch.empty_like(mine) for _ in range(size)]
-    dist.all_gather(parts, mine, group=group)
-    rows = torch.stack(parts).cpu().numpy()
+    comm, pg = _unwrap(group)
+    if comm is not None:
+        rows = comm.all_gather(mine).cpu().numpy()
+    else:
+        parts = [torch.empty_like(mine) for _ in range(size)]
+        dist.all_gather(parts, mine, group=pg)
+        rows = torch.stack(parts).cpu().numpy()
     fps = set(int(x) for x in rows[:, 2])
     if len(fps) == 1 and fp != 0:
         return [(int(r[0]), int(r[1]), schema) for r in rows]
@@ -109,6 +131,7 @@ def exchange_table(rt: dev.Runtime, table: DeviceTable, send_counts: Sequence[in
     to rank ``d``.  Returns the rows this rank receives, in (source rank, position)
     order.  Every rank must call this with the same schema."""
     rank, G = world(group)
+    group = _unwrap(group)[1]
     assert len(send_counts) == G
     n_send = table.num_rows
     assert sum(send_counts) == n_send

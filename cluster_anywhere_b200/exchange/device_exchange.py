@@ -111,7 +111,7 @@ class DeviceExchange:
         from . import peer
 
         rt = self.rt
-        if peer.enabled(rt) and not getattr(self, "_p2p_unavailable", False):
+        if peer.enabled(rt, group) and not getattr(self, "_p2p_unavailable", False):
             try:
                 recv = peer.gather_exchange(rt, self, table, perm, send_counts, group)
                 self._phase("dist.gather_exchange_p2p")
@@ -281,13 +281,30 @@ class DeviceExchange:
                   boundary search for this rank's block cuts (K4), one gather (K5).
         """
         from . import collective as coll
+        from . import chunked_sort, peer
+        from .comm import as_comm
 
-        rank, G = coll.world(group)
+        group = as_comm(group)
+        rank, G = group.rank, group.world
         if G == 1 and not force_exchange:  # force_exchange: run the map/exchange/reduce path anyway
             return self.sort(ds, sort_key, boundaries=boundaries, seed=seed)
         rt = self.rt
         self._phase(None)
         self._stamp(None)
+        # chunked fast path (one fixed-width key column, fixed / uniform-width payload); the
+        # ranks decide together, a None means "not eligible somewhere": general path below
+        if (peer.enabled(rt, group) and not self.trace and not getattr(self, "_p2p_unavailable", False)
+                and os.environ.get("XCHG_CHUNKED", "1") != "0"):
+            try:
+                out = chunked_sort.try_sort(self, ds, sort_key, boundaries, seed, group)
+            except (ImportError, AttributeError, NotImplementedError) as e:  # no symmetric memory here
+                import warnings
+
+                warnings.warn(f"NVLink peer-memory exchange unavailable ({e!r}); using NCCL all-to-all")
+                self._p2p_unavailable = True
+                out = None
+            if out is not None:
+                return out
         self._gpu_mark("step_begin")
         schema = None if ds.table is None else ds.table.schema
         info = coll.gather_dataset_info(rt, ds.num_blocks, ds.num_rows, schema, group)
@@ -345,10 +362,8 @@ class DeviceExchange:
             self._gpu_mark("g.assigned")
         lo_b, hi_b = int(ob[rank]), int(ob[rank + 1])
         local_bounds = list(boundaries[lo_b:max(lo_b, hi_b - 1)])
-        from . import peer
-
-        if (peer.enabled(rt) and not getattr(self, "_p2p_unavailable", False) and not self.trace
-                and os.environ.get("XCHG_OVERLAP", "1") != "0"):
+        if (peer.enabled(rt, group) and not getattr(self, "_p2p_unavailable", False) and not self.trace
+                and os.environ.get("XCHG_OVERLAP", "1") != "0" and rt.is_cuda):
             try:
                 return self._exchange_and_reduce_overlapped(table, perm, send_counts, sort_key,
                                                             local_bounds, my_blocks, group)

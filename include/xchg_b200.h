@@ -206,6 +206,88 @@ int xchg_assign_partitions(const uint64_t* const* norm_cols_host, const uint8_t*
                            int nb, int first_descending, uint32_t* dest_out,
                            uint64_t* counts_out, void* stream);
 
+/* ------------------------------------- multi-GPU exchange: control path ---- */
+/*
+ * K1, boundary sampling.  Replaces SortTaskSpec._sample_block -> ArrowBlockAccessor._sample
+ * (python/ray/data/_internal/planner/exchange/sort_task_spec.py:229,
+ * _internal/arrow_block.py:341-344: `random.sample` of min(n_samples, rows) rows of every
+ * block and a take of the key column).  Block b = rows [block_start_host[b],
+ * +block_rows_host[b]) of the key column; min(per_block, rows) DISTINCT rows of it are
+ * drawn (the first values of a Philox-keyed bijection of [0, rows), keyed by seed and the
+ * block's global index first_block_index + b; the reference's draw is unseeded) and their
+ * radix keys (xchg_normalize_keys' transform) are written back to back to samples_out.
+ * *count_out_host = number of samples (known without a read-back).  XCHG_ERR_LIMIT if
+ * they exceed `capacity`.
+ */
+int xchg_sample_keys(const void* keys, int key_type, int descending, const uint8_t* validity,
+                     int64_t validity_bit_offset, const uint64_t* block_start_host,
+                     const uint64_t* block_rows_host, int nblocks, uint32_t per_block,
+                     uint64_t seed, uint64_t first_block_index, uint64_t* samples_out,
+                     uint64_t capacity, uint64_t* count_out_host, void* stream);
+/*
+ * The driver half of SortTaskSpec.sample_boundaries (sort_task_spec.py:200-226) on the
+ * device: sort all samples, pick the num_partitions - 1 boundaries at
+ * int(q * (len - 1)), q in linspace(0, 1, num_partitions + 1)[1:-1] (float64, as numpy).
+ * `gathered` = nmsgs (<= 64) messages of msg_words uint64 each, as one all-gather of the
+ * ranks' sample buffers delivers them: word count_word of a message = its number of
+ * samples, samples from word hdr_words on.  More than 16384 samples in total are thinned
+ * out evenly first.  bounds_out: num_partitions - 1 radix keys in sort order (untouched
+ * when there is no sample); info_out (may be NULL): {samples received, samples used}.
+ * One CTA; every rank computes identical boundaries from identical input.
+ */
+int xchg_select_boundaries(const uint64_t* gathered, int nmsgs, uint64_t msg_words,
+                           uint32_t count_word, uint32_t hdr_words, uint32_t num_partitions,
+                           uint64_t* bounds_out, uint64_t* info_out, void* stream);
+/*
+ * Map side of the exchange for ONE fixed-width key column without nulls, boundaries
+ * resident on the device: destination of every row = the range partition
+ * find_partitions (python/ray/data/_internal/util.py:806-828) slices it into, for the
+ * nthr (<= 255) thresholds bounds[pick_host[i]] (in sort order).  strict_host[i] != 0: rows
+ * equal to threshold i stay left of it (descending keys, util.py:803); NULL = none strict.
+ * Same rule as xchg_assign_partitions, without materialising radix keys or a destination
+ * array.
+ *
+ * xchg_partition_hist   counts_out[d] (nthr + 1 uint64, device, zeroed here) = rows of
+ *                       destination d.
+ * xchg_partition_rows   stable partition: keys_out / rows_out (n entries each) = radix key
+ *                       and row id of every row, ordered by destination, input order kept
+ *                       inside a destination (SortTaskSpec.map without the sort,
+ *                       sort_task_spec.py:127-138).  counts = xchg_partition_hist's output
+ *                       for the same arguments.  One RAW onesweep pass: 8 B read + 12 B
+ *                       written per row.
+ */
+int xchg_partition_hist(const void* keys, int key_type, int descending, uint64_t n,
+                        const uint64_t* bounds, const uint32_t* pick_host, const uint8_t* strict_host,
+                        int nthr, uint64_t* counts_out, void* stream);
+int xchg_partition_workspace_bytes(uint64_t n, uint64_t* bytes_out);
+int xchg_partition_rows(const void* keys, int key_type, int descending, uint64_t n,
+                        const uint64_t* bounds, const uint32_t* pick_host, const uint8_t* strict_host,
+                        int nthr, const uint64_t* counts, uint64_t* keys_out, uint32_t* rows_out,
+                        void* workspace, uint64_t workspace_bytes, void* stream);
+/*
+ * dst_host[i][0 .. bytes_host[i]) = src_host[i][...] for nseg segments in one launch, the
+ * segments' tiles interleaved; destinations may be peer memory (the key runs of the
+ * exchange).  Replaces the object-store transfer of a map task's outputs
+ * (pull_based_shuffle_task_scheduler.py:84-120) for contiguous runs.
+ */
+int xchg_copy_segments(int nseg, const void* const* src_host, void* const* dst_host,
+                       const uint64_t* bytes_host, void* stream);
+/*
+ * Arrival flags between GPUs.  The reference orders map, merge and reduce rounds by task
+ * dependencies on object references (push_based_shuffle_task_scheduler.py:548-561,
+ * :696-730); here a sender announces that a chunk has been stored by writing `value` to a
+ * 4-byte flag in the receiver's memory, and the receiver's stream waits for it.
+ * xchg_signal_flags  every flag_ptrs_host[i] (device pointers, peer memory allowed) := value,
+ *                    released at system scope after all earlier work of the stream.
+ * xchg_wait_flags    blocks the stream until flags[0..n) (local memory) have all reached
+ *                    `value` (wrap-around compare).  After timeout_ns without it,
+ *                    *error_flag (device uint32) := 1 + index of a missing flag and the
+ *                    stream continues: check it before trusting what follows.
+ */
+int xchg_signal_flags(uint32_t* const* flag_ptrs_host, int n, uint32_t value, void* stream);
+int xchg_wait_flags(const uint32_t* flags, int n, uint32_t value, uint64_t timeout_ns,
+                    uint32_t* error_flag, void* stream);
+
 /* ------------------------------------------------- string / binary keys ---- */
 /*
  * Sort keys of variable-width columns (Arrow binary / string, int64 byte offsets as this

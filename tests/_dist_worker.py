@@ -77,6 +77,34 @@ def main():
                 assert g.num_rows == e.num_rows
                 if e.num_rows:
                     assert tables_equal(g, e)
+    # the chunked fast path (one fixed-width key without nulls, fixed / uniform payload): taken on
+    # real GPUs (peer memory); under gloo the same input goes through the all-to-all path
+    rng2 = np.random.default_rng(21)
+
+    def plain_block(n):
+        pay = rng2.integers(0, 256, n * 90, dtype=np.uint8)
+        offs = np.arange(n + 1, dtype=np.int32) * 90
+        return pa.table({"k": pa.array(rng2.integers(-10 ** 9, 10 ** 9, n), pa.int64()),
+                         "v": pa.array(rng2.integers(0, 100, n), pa.int32()),
+                         "p": pa.Array.from_buffers(pa.binary(), n, [None, pa.py_buffer(offs), pa.py_buffer(pay)])})
+
+    plain = [plain_block(n) for n in ((30000, 5, 20000, 41000, 9000, 100) if w == 2 else (3000, 5, 2000, 4100, 900, 100, 77))]
+    pcut = [len(plain) * g // w for g in range(w + 1)]
+    pmine = plain[pcut[r]:pcut[r + 1]]
+    pfull = pa.concat_tables(plain)
+    for desc, bounds in ((False, None), (True, None), (False, [(-5 * 10 ** 8,), (0,), (123456789,)])):
+        before = getattr(ex, "chunked_steps", 0)
+        out = ex.sort_blocks_distributed(pmine, SortKey("k", desc), boundaries=bounds, seed=5)
+        if "--gpu" in sys.argv:
+            assert getattr(ex, "chunked_steps", 0) == before + 1, "chunked path not taken on the GPU"
+        outs = [None] * w
+        dist.all_gather_object(outs, out)
+        got = [b for part in outs for b in part]
+        exp = O.sort_table(pfull, ["k"], [desc])
+        assert tables_equal(pa.concat_tables([g for g in got if g.num_rows]), exp), ("plain", desc, bounds)
+        if bounds is not None:
+            parts = O.find_partitions(exp, bounds, ["k"], [desc])
+            assert [g.num_rows for g in got] == [e.num_rows for e in parts]
     # random_shuffle: the G-rank result is the single-process result, take(P^-1(0..N))
     for seed, nout in ((42, None), (7, 3)):
         out = ex.random_shuffle_blocks(mine, seed, num_outputs=nout)

@@ -298,6 +298,126 @@ class FakeLib:
             _arr(flag, np.uint32, 1)[0] |= 1
         return 0
 
+    # -- multi-GPU exchange: control path ---------------------------------------
+    @staticmethod
+    def _splitmix64(x):
+        m = (1 << 64) - 1
+        x = (x + 0x9E3779B97F4A7C15) & m
+        x = ((x ^ (x >> 30)) * 0xBF58476D1CE4E5B9) & m
+        x = ((x ^ (x >> 27)) * 0x94D049BB133111EB) & m
+        return x ^ (x >> 31)
+
+    def xchg_sample_keys(self, keys, kt, desc, validity, vbit, starts, rows, nblocks, per_block, seed,
+                         first_block, out, capacity, count_out, stream):
+        ks = [min(int(per_block), int(rows[b])) for b in range(nblocks)]
+        total = sum(ks)
+        count_out._obj.value = total
+        if total == 0:
+            return 0
+        if total > capacity:
+            self.err = b"xchg_sample_keys: samples exceed the capacity"
+            return -4
+        pos = 0
+        for b in range(nblocks):
+            k, r = ks[b], int(rows[b])
+            if k == 0:
+                continue
+            sd = self._splitmix64(int(seed) ^ self._splitmix64(int(first_block) + b))
+            j = np.arange(k, dtype=np.uint64)
+            loc = j if k == r else self._feistel(sd, r, j, False)
+            ridx = (int(starts[b]) + loc.astype(np.int64)).astype(np.uint32)
+            tmp = np.ascontiguousarray(ridx)
+            _, nk, _ = self._norm_col(keys, kt, desc, validity, vbit, ctypes.c_void_p(tmp.ctypes.data), k)
+            _arr(out, np.uint64, total)[pos:pos + k] = nk
+            pos += k
+        return 0
+
+    def xchg_select_boundaries(self, gathered, nmsgs, msg_words, count_word, hdr_words, R, bounds, info, stream):
+        g = _arr(gathered, np.uint64, nmsgs * msg_words).reshape(nmsgs, msg_words)
+        allv = np.concatenate([g[i, hdr_words:hdr_words + int(g[i, count_word])] for i in range(nmsgs)])
+        total = len(allv)
+        stride = (total + 16383) // 16384 if total > 16384 else 1
+        used = np.sort(allv[::stride], kind="stable")
+        m = len(used)
+        if m and R > 1:
+            step = 1.0 / float(R)
+            idx = [min(m - 1, int((i * step) * float(m - 1))) for i in range(1, R)]
+            _arr(bounds, np.uint64, R - 1)[:] = used[idx]
+        if _addr(info):
+            _arr(info, np.uint64, 2)[:] = (total, m)
+        return 0
+
+    @staticmethod
+    def _dest(nk, thr, strict):
+        """number of thresholds t with t < k, or t == k and not strict (thresholds sorted)"""
+        if len(thr) == 0:
+            return np.zeros(len(nk), dtype=np.int64)
+        lt = np.searchsorted(thr, nk, side="left")       # thresholds < k
+        d = lt.copy()
+        # thresholds equal to k follow; the leading non-strict ones count (the rule is a prefix)
+        for i in range(len(nk)):
+            j = int(lt[i])
+            while j < len(thr) and thr[j] == nk[i] and not strict[j]:
+                j += 1
+            d[i] = j
+        return d
+
+    def _dest_rows(self, keys, kt, desc, n, bounds, pick, strict_p, nthr):
+        _, nk, _ = self._norm_col(keys, kt, desc, None, 0, None, n)
+        picks = [int(pick[i]) for i in range(nthr)]
+        b = _arr(bounds, np.uint64, max(picks) + 1) if nthr else np.zeros(0, np.uint64)
+        thr = b[picks] if nthr else np.zeros(0, np.uint64)
+        strict = np.array([int(strict_p[i]) if strict_p else 0 for i in range(nthr)], dtype=np.uint8)
+        return nk, self._dest(nk, thr, strict)
+
+    def xchg_partition_hist(self, keys, kt, desc, n, bounds, pick, strict, nthr, counts, stream):
+        _arr(counts, np.uint64, nthr + 1)[:] = 0
+        if n == 0:
+            return 0
+        _, d = self._dest_rows(keys, kt, desc, n, bounds, pick, strict, nthr)
+        _arr(counts, np.uint64, nthr + 1)[:] = np.bincount(d, minlength=nthr + 1).astype(np.uint64)
+        return 0
+
+    def xchg_partition_workspace_bytes(self, n, out):
+        out._obj.value = 64
+        return 0
+
+    def xchg_partition_rows(self, keys, kt, desc, n, bounds, pick, strict, nthr, counts, keys_out, rows_out,
+                            ws, wsb, stream):
+        if n == 0:
+            return 0
+        nk, d = self._dest_rows(keys, kt, desc, n, bounds, pick, strict, nthr)
+        order = np.argsort(d, kind="stable")
+        _arr(keys_out, np.uint64, n)[:] = nk[order]
+        _arr(rows_out, np.uint32, n)[:] = order.astype(np.uint32)
+        return 0
+
+    def xchg_copy_segments(self, nseg, src, dst, nbytes, stream):
+        for i in range(nseg):
+            b = int(nbytes[i])
+            if b:
+                _arr(ctypes.c_void_p(dst[i]), np.uint8, b)[:] = _arr(ctypes.c_void_p(src[i]), np.uint8, b)
+        return 0
+
+    def xchg_signal_flags(self, ptrs, n, value, stream):
+        for i in range(n):
+            _arr(ctypes.c_void_p(ptrs[i]), np.uint32, 1)[0] = value
+        return 0
+
+    def xchg_wait_flags(self, flags, n, value, timeout_ns, error, stream):
+        import time
+
+        f = _arr(flags, np.uint32, n)
+        t0 = time.monotonic()
+        while True:
+            late = [i for i in range(n) if ((int(f[i]) - int(value)) & 0xFFFFFFFF) >= 0x80000000]
+            if not late:
+                return 0
+            if (time.monotonic() - t0) * 1e9 > timeout_ns:
+                _arr(error, np.uint32, 1)[0] = 1 + late[0]
+                return 0
+            time.sleep(0.0005)
+
     # -- exchange-side entry points ------------------------------------------
     def xchg_assign_partitions(self, cols, col_desc, ncols, n, lower, upper, flags, nb, first_desc, dest, counts,
                                stream):

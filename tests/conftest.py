@@ -3,6 +3,11 @@ import sys
 
 import pytest
 
+# the virtual-world tests run several ranks' streams on one GPU, some of them parked in a
+# wait-for-flag kernel: give every stream its own hardware queue so that none of them ends
+# up queued behind another rank's wait (must be set before the CUDA context exists)
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
