@@ -49,6 +49,8 @@ _SIGNATURES = {
                                    ctypes.POINTER(c_uint64), _P]),
     "xchg_signal_flags": (c_int, [ctypes.POINTER(c_void_p), c_int, c_uint32, _P]),
     "xchg_wait_flags": (c_int, [_P, c_int, c_uint32, c_uint64, _P, _P]),
+    "xchg_merge_workspace_bytes": (c_int, [c_uint64, ctypes.POINTER(c_uint64)]),
+    "xchg_merge_sorted_runs": (c_int, [_P, _P, ctypes.POINTER(c_uint64), c_int, _P, _P, _P, c_uint64, _P, _P]),
     "xchg_shuffle_positions": (c_int, [c_uint64, c_uint64, c_uint64, c_uint64, c_int, _P, _P]),
     "xchg_invert_permutation": (c_int, [_P, c_uint64, c_uint64, _P, _P]),
     "xchg_even_split_dest": (c_int, [_P, c_uint64, c_uint64, c_uint32, _P, _P, _P]),

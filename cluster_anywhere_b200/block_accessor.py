@@ -11,6 +11,8 @@ back per call); the device-resident, multi-block path is
 """
 from __future__ import annotations
 
+import os
+
 from typing import List, Optional, Sequence, Tuple
 
 import numpy as np
@@ -207,8 +209,59 @@ class B200ArrowBlockAccessor:
             ret = empty_table()
         else:
             t = pa.concat_tables(blocks, promote_options="permissive")
-            ret = B200ArrowBlockAccessor(t, runtime).sort(sort_key)
+            acc = B200ArrowBlockAccessor(t, runtime)
+            # the runs arrive sorted (SortTaskSpec.map made them): a stable merge (K6) gives
+            # the reference's concat + stable re-sort; anything the merge kernel does not
+            # take -- several key columns, string keys, 64-bit keys with nulls, a run that
+            # turns out not to be sorted -- is sorted from scratch like the reference does
+            ret = acc._merge_runs([b.num_rows for b in blocks], sort_key)
+            if ret is None:
+                ret = acc.sort(sort_key)
         return ret, B200ArrowBlockAccessor(ret, runtime).get_metadata(exec_stats=stats.build())
+
+    def _merge_runs(self, run_rows: List[int], sort_key: SortKey) -> Optional[pa.Table]:
+        """K6 on this table seen as consecutive sorted runs of ``run_rows`` rows; None when
+        the merge kernel does not apply (see merge_sorted_blocks)."""
+        import ctypes
+
+        import torch
+
+        cols, desc = sort_key.get_columns(), sort_key.get_descending()
+        if len(cols) != 1 or len(run_rows) > 128 or os.environ.get("XCHG_MERGE", "1") == "0":
+            return None
+        sort_key.validate_schema(self._table.schema)
+        rt = self.rt
+        dt = dev.stage_table(rt, self._table)
+        col = dt.column(cols[0])
+        if col.kind != "fixed":
+            return None
+        try:
+            kt = dev.key_type_of(col.type)
+        except NotImplementedError:
+            return None
+        if col.validity is not None and kt in (dev._cabi.I64, dev._cabi.U64):
+            return None  # nulls of 64-bit keys need the validity place of the full sort
+        n = dt.num_rows
+        if n > (1 << 30) - 1:
+            return None
+        norm = rt.empty(n, torch.int64)
+        rt.call("xchg_normalize_keys", dev._vp(col.data), kt, int(bool(desc[0])), dev._vp(col.validity), 0, None, n,
+                dev._vp(norm), rt.stream)
+        starts = np.concatenate([[0], np.cumsum(np.asarray(run_rows, dtype=np.int64))])
+        a_starts = (ctypes.c_uint64 * len(starts))(*[int(x) for x in starts])
+        wsb = ctypes.c_uint64()
+        dev._cabi.check(dev._cabi.load().xchg_merge_workspace_bytes(n, ctypes.byref(wsb)))
+        ws = rt.empty(wsb.value)
+        keys_out = rt.empty(n, torch.int64)
+        perm = rt.empty(n, torch.int32)
+        flag = rt.zeros(1, torch.int32)
+        rt.call("xchg_merge_sorted_runs", dev._vp(norm), None, a_starts, len(run_rows), dev._vp(keys_out),
+                dev._vp(perm), dev._vp(ws), wsb.value, dev._vp(flag), rt.stream,
+                launches=max(1, (len(run_rows) - 1).bit_length()) + 1)
+        if int(flag.item()):  # sync: a run was not sorted
+            return None
+        out = dev.take_table(rt, dt, perm, n, {cols[0]: (keys_out, bool(desc[0]))})
+        return dev.export_table(rt, out)
 
     # -- aggregate -------------------------------------------------------------
     def _reduce(self, kind: int, on: str, ignore_nulls: bool, ddof: int = 1):

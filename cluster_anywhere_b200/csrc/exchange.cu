@@ -13,6 +13,7 @@
 // keeps them in HBM for the partition kernels, and a chunk's arrival is a 4-byte flag in
 // the receiver's memory instead of a task dependency.
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "feistel.cuh"
@@ -208,6 +209,75 @@ k_copy_segments(CopySegs cs, uint64_t max_tiles) {
   }
 }
 
+// The same copy by the TMA unit: one warp per CTA, lane 0 moves 32 KB stages global ->
+// shared (cp.async.bulk + mbarrier) -> global (cp.async.bulk, bulk group), two stages so
+// that the store of one stage drains while the next one loads.  No thread touches the data;
+// towards a peer GPU the stores leave the SM as the TMA unit's large bursts instead of
+// per-thread 16-byte stores.  Needs 16-byte aligned segments; tails (< 16 bytes) go bytewise.
+constexpr uint32_t CB_STAGE = 32768;
+constexpr int CB_STAGES = 2;
+
+__device__ __forceinline__ void mbar_init(uint32_t mbar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t mbar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@!p bra WAIT_%=;\n\t}"
+      ::"r"(mbar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_load(uint32_t smem_dst, const void* gsrc, uint32_t bytes, uint32_t mbar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_dst), "l"(gsrc), "r"(bytes), "r"(mbar) : "memory");
+}
+__device__ __forceinline__ void bulk_store(void* gdst, uint32_t smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+               ::"l"(gdst), "r"(smem_src), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+
+__global__ void __launch_bounds__(32)
+k_copy_segments_bulk(CopySegs cs, uint64_t max_tiles) {
+  extern __shared__ __align__(128) uint8_t cb_smem[];
+  __shared__ __align__(8) uint64_t mbar_mem[CB_STAGES];
+  const uint32_t stage_s = (uint32_t)__cvta_generic_to_shared(cb_smem);
+  const uint32_t mbar_s = (uint32_t)__cvta_generic_to_shared(mbar_mem);
+  const int lane = threadIdx.x;
+  if (lane == 0) {
+    for (int i = 0; i < CB_STAGES; ++i) mbar_init(mbar_s + 8 * i, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+  const uint64_t nwork = max_tiles * (uint64_t)cs.nseg;
+  uint32_t it = 0;
+  for (uint64_t work = blockIdx.x; work < nwork; work += gridDim.x) {
+    const int sg = (int)(work % (uint64_t)cs.nseg);
+    const uint64_t off = (work / (uint64_t)cs.nseg) * CB_STAGE;
+    if (off >= cs.bytes[sg]) continue;
+    const uint32_t len = (uint32_t)min((uint64_t)CB_STAGE, cs.bytes[sg] - off);
+    const uint32_t body = len & ~15u;
+    const uint8_t* src = cs.src[sg] + off;
+    uint8_t* dst = cs.dst[sg] + off;
+    if (lane == 0 && body) {
+      const uint32_t st = it % CB_STAGES;
+      // the store issued from this stage two items ago must have read its bytes
+      asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(CB_STAGES - 1) : "memory");
+      mbar_expect_tx(mbar_s + 8 * st, body);
+      bulk_load(stage_s + st * CB_STAGE, src, body, mbar_s + 8 * st);
+      mbar_wait(mbar_s + 8 * st, (it / CB_STAGES) & 1u);
+      bulk_store(dst, stage_s + st * CB_STAGE, body);
+      ++it;
+    }
+    for (uint32_t q = body + lane; q < len; q += 32) dst[q] = src[q];
+  }
+  if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
 // -------------------------------------------------------- arrival flags -----
 
 constexpr int FLAG_MAX = 64;
@@ -386,8 +456,22 @@ extern "C" int xchg_copy_segments(int nseg, const void* const* src_host, void* c
       ++cs.nseg;
     }
     if (cs.nseg == 0) continue;
-    const int grid = (int)std::min<uint64_t>(max_tiles * cs.nseg, (uint64_t)xchg_sm_count() * 8);
-    XCHG_LAUNCH(XK_MISC, s, k_copy_segments<<<grid, 256, 0, s>>>(cs, max_tiles));
+    // XCHG_COPY_BULK=1: the TMA variant (16-byte aligned segments only)
+    const char* bulk_env = getenv("XCHG_COPY_BULK");  // read per call: a profiling switch
+    const int bulk_mode = bulk_env ? atoi(bulk_env) : 0;
+    bool aligned = true;
+    for (int i = 0; i < cs.nseg; ++i) aligned = aligned && ((((uintptr_t)cs.src[i] | (uintptr_t)cs.dst[i]) & 15) == 0);
+    if (bulk_mode && aligned) {
+      constexpr int smem = CB_STAGE * CB_STAGES;
+      XCHG_ONCE_PER_DEVICE(XCHG_CUDA_TRY(cudaFuncSetAttribute(k_copy_segments_bulk,
+                                                              cudaFuncAttributeMaxDynamicSharedMemorySize, smem)));
+      const uint64_t tiles = ((max_tiles * CS_TILE + CB_STAGE - 1) / CB_STAGE);
+      const int grid = (int)std::min<uint64_t>(tiles * cs.nseg, (uint64_t)xchg_sm_count() * 3);
+      XCHG_LAUNCH(XK_MISC, s, k_copy_segments_bulk<<<grid, 32, smem, s>>>(cs, tiles));
+    } else {
+      const int grid = (int)std::min<uint64_t>(max_tiles * cs.nseg, (uint64_t)xchg_sm_count() * 8);
+      XCHG_LAUNCH(XK_MISC, s, k_copy_segments<<<grid, 256, 0, s>>>(cs, max_tiles));
+    }
     XCHG_LAUNCH_CHECK();
   }
   return XCHG_OK;

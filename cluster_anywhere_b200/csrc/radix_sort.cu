@@ -125,6 +125,74 @@ k_scan_hist(const uint32_t* __restrict__ ghist, uint32_t* __restrict__ gexcl,
   }
 }
 
+// First look at a key column that is sorted straight from its raw values (no nulls, no
+// incoming permutation): OR and AND of all radix keys -- a digit place is trivial exactly
+// when every key has the same byte there, i.e. (OR ^ AND) has a zero byte -- and the
+// histograms of the places in place_mask (the one place the first pass runs on, guessed
+// as the type's top byte; all active places for an all-LSD sort).  Nothing is written per
+// row: the passes read the raw column again and normalise in registers (RAW passes).
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_key_scan(const T* __restrict__ keys, uint32_t n, int desc, uint32_t place_mask, int want_orand,
+           unsigned long long* __restrict__ orand, uint32_t* __restrict__ ghist) {
+  __shared__ uint32_t sh[KEY_PLACES * BINS];
+  __shared__ unsigned long long s_or[8], s_and[8];
+  for (int j = threadIdx.x; j < KEY_PLACES * BINS; j += blockDim.x) sh[j] = 0;
+  __syncthreads();
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t stride = gridDim.x * blockDim.x;
+  const uint32_t n_up = (n + 31u) & ~31u;
+  uint64_t acc_or = 0, acc_and = ~0ull;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_up; i += stride) {
+    const bool active = i < n;
+    uint64_t key = 0;
+    if (active) {
+      key = norm_value<T>(keys[i], desc != 0);
+      acc_or |= key;
+      acc_and &= key;
+    }
+    const unsigned act = __ballot_sync(0xffffffffu, active);
+    const int first = __ffs(act) - 1;
+    for (uint32_t pm = place_mask; pm; pm &= pm - 1) {
+      const int p = __ffs(pm) - 1;
+      const uint32_t d = (uint32_t)(key >> (8 * p)) & 255u;
+      const uint32_t d0 = __shfl_sync(0xffffffffu, d, first);
+      const bool uni = __all_sync(0xffffffffu, !active || d == d0);
+      if (uni) {
+        if ((int)lane == first) atomicAdd(&sh[p * BINS + d0], (uint32_t)__popc(act));
+      } else if (active) {
+        atomicAdd(&sh[p * BINS + d], 1u);
+      }
+    }
+  }
+  if (want_orand) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      acc_or |= __shfl_xor_sync(0xffffffffu, acc_or, o);
+      acc_and &= __shfl_xor_sync(0xffffffffu, acc_and, o);
+    }
+    if (lane == 0) {
+      s_or[warp] = acc_or;
+      s_and[warp] = acc_and;
+    }
+  }
+  __syncthreads();
+  if (want_orand && threadIdx.x == 0) {
+    uint64_t o = 0, a = ~0ull;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) {
+      o |= s_or[w];
+      a &= s_and[w];
+    }
+    atomicOr(&orand[0], (unsigned long long)o);
+    atomicAnd(&orand[1], (unsigned long long)a);
+  }
+  for (uint32_t pm = place_mask; pm; pm &= pm - 1) {
+    const int p = __ffs(pm) - 1;
+    for (int j = threadIdx.x; j < BINS; j += blockDim.x)
+      if (sh[p * BINS + j]) atomicAdd(&ghist[p * BINS + j], sh[p * BINS + j]);
+  }
+}
+
 // ------------------------------------------------------------------ K3 -----
 
 template <int MODE>
@@ -992,6 +1060,28 @@ int dispatch_normalize(const void* keys, int key_type, const uint32_t* perm, con
   return XCHG_OK;
 }
 
+int dispatch_key_scan(const void* keys, int key_type, uint32_t n, int desc, uint32_t place_mask,
+                      int want_orand, unsigned long long* orand, uint32_t* ghist, cudaStream_t s) {
+  const int blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)xchg_sm_count() * 8);
+  const bool ok = xchg_dispatch_key_type(key_type, [&](auto tag) {
+    using T = typename decltype(tag)::type;
+    XCHG_LAUNCH(XK_NORMALIZE, s,
+                k_key_scan<T><<<blocks, 256, 0, s>>>((const T*)keys, n, desc, place_mask, want_orand, orand, ghist));
+  });
+  XCHG_REQUIRE(ok, "unknown key_type %d", key_type);
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+int key_type_bytes(int key_type) {
+  switch (key_type) {
+    case XCHG_I8: case XCHG_U8: return 1;
+    case XCHG_I16: case XCHG_U16: return 2;
+    case XCHG_I32: case XCHG_U32: case XCHG_F32: return 4;
+    default: return 8;
+  }
+}
+
 }  // namespace
 
 // CTA shape of the onesweep pass: XCHG_ONESWEEP_THREADS=256|512 and
@@ -1175,21 +1265,62 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
   const uint32_t ntiles = (n32 + RS_MIN_TILE - 1) / RS_MIN_TILE;  // status rows cleared per pass
 
   XCHG_CUDA_TRY(cudaMemsetAsync(w.ghist, 0, NUM_PLACES * BINS * 4, s));
-  int rc = dispatch_normalize(keys, key_type, perm_in, validity, validity_bit_offset, n32, descending,
-                              w.norm, w.ghist, s);
-  if (rc) return rc;
-  XCHG_LAUNCH(XK_SCAN_HIST, s, k_scan_hist<<<1, BINS, 0, s>>>(w.ghist, w.gexcl, w.active, n32));
-  XCHG_LAUNCH_CHECK();
-  uint32_t active[NUM_PLACES];
-  XCHG_CUDA_TRY(cudaMemcpyAsync(active, w.active, sizeof(active), cudaMemcpyDeviceToHost, s));
-  XCHG_CUDA_TRY(cudaStreamSynchronize(s));
-
+  int rc;
   int places[NUM_PLACES];
   int np = 0;
-  for (int p = 0; p < KEY_PLACES; ++p)
-    if (active[p]) places[np++] = p;
-  const bool wide_int = key_type == XCHG_I64 || key_type == XCHG_U64;
-  if (wide_int && validity && active[KEY_PLACES]) places[np++] = KEY_PLACES;
+  // A column without nulls that is sorted in its stored order needs no materialised radix
+  // keys: one scan tells which digit places matter (and builds the first pass's histogram),
+  // the first pass reads the raw values (RAW).  XCHG_SORT_RAW=0 keeps the normalise pass.
+  static const bool raw_enabled = [] {
+    const char* e = getenv("XCHG_SORT_RAW");
+    return !(e && atoi(e) == 0);
+  }();
+  const bool raw_able = raw_enabled && perm_in == nullptr && validity == nullptr;
+  const RawKeys raw0 = {keys, key_type, descending, nullptr, nullptr, 0};
+  const RawKeys* raw = raw_able ? &raw0 : nullptr;
+  if (raw_able) {
+    XCHG_REQUIRE(key_type >= XCHG_I8 && key_type <= XCHG_F64, "unknown key_type %d", key_type);
+    unsigned long long* orand = (unsigned long long*)w.active;  // 64 bytes: {OR, AND}
+    XCHG_CUDA_TRY(cudaMemsetAsync(orand, 0, 8, s));
+    XCHG_CUDA_TRY(cudaMemsetAsync(orand + 1, 0xFF, 8, s));
+    const int guess = key_type_bytes(key_type) - 1;  // the type's top byte
+    rc = dispatch_key_scan(keys, key_type, n32, descending, 1u << guess, 1, orand, w.ghist, s);
+    if (rc) return rc;
+    unsigned long long oa[2];
+    XCHG_CUDA_TRY(cudaMemcpyAsync(oa, orand, sizeof(oa), cudaMemcpyDeviceToHost, s));
+    XCHG_CUDA_TRY(cudaStreamSynchronize(s));
+    const uint64_t diff = oa[0] ^ oa[1];
+    uint32_t need = 0;
+    for (int p = 0; p < KEY_PLACES; ++p)
+      if ((diff >> (8 * p)) & 0xFF) places[np++] = p;
+    if (np > 0) {
+      if (sort_algorithm() == 1 || np <= 2) {
+        for (int j = 0; j < np; ++j) need |= 1u << places[j];
+      } else {
+        need = 1u << places[np - 1];
+      }
+      need &= ~(1u << guess);
+      if (need) {
+        rc = dispatch_key_scan(keys, key_type, n32, descending, need, 0, orand, w.ghist, s);
+        if (rc) return rc;
+      }
+      XCHG_LAUNCH(XK_SCAN_HIST, s, k_scan_hist<<<1, BINS, 0, s>>>(w.ghist, w.gexcl, w.active, n32));
+      XCHG_LAUNCH_CHECK();
+    }
+  } else {
+    rc = dispatch_normalize(keys, key_type, perm_in, validity, validity_bit_offset, n32, descending,
+                            w.norm, w.ghist, s);
+    if (rc) return rc;
+    XCHG_LAUNCH(XK_SCAN_HIST, s, k_scan_hist<<<1, BINS, 0, s>>>(w.ghist, w.gexcl, w.active, n32));
+    XCHG_LAUNCH_CHECK();
+    uint32_t active[NUM_PLACES];
+    XCHG_CUDA_TRY(cudaMemcpyAsync(active, w.active, sizeof(active), cudaMemcpyDeviceToHost, s));
+    XCHG_CUDA_TRY(cudaStreamSynchronize(s));
+    for (int p = 0; p < KEY_PLACES; ++p)
+      if (active[p]) places[np++] = p;
+    const bool wide_int = key_type == XCHG_I64 || key_type == XCHG_U64;
+    if (wide_int && validity && active[KEY_PLACES]) places[np++] = KEY_PLACES;
+  }
 
   uint64_t* keys_a = norm_keys_out ? norm_keys_out : w.keys_a;
   if (np == 0) {
@@ -1197,8 +1328,14 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
     int blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)xchg_sm_count() * 8);
     XCHG_LAUNCH(XK_MISC, s, k_iota_or_copy<<<blocks, 256, 0, s>>>(perm_in, perm_out, n32));
     XCHG_LAUNCH_CHECK();
-    if (norm_keys_out)
-      XCHG_CUDA_TRY(cudaMemcpyAsync(norm_keys_out, w.norm, n * 8, cudaMemcpyDeviceToDevice, s));
+    if (norm_keys_out) {
+      if (raw_able) {
+        rc = dispatch_normalize(keys, key_type, nullptr, nullptr, 0, n32, descending, norm_keys_out, nullptr, s);
+        if (rc) return rc;
+      } else {
+        XCHG_CUDA_TRY(cudaMemcpyAsync(norm_keys_out, w.norm, n * 8, cudaMemcpyDeviceToDevice, s));
+      }
+    }
     return XCHG_OK;
   }
   // XCHG_SORT_ALGO=lsd keeps every pass global (A/B runs); the default finishes small
@@ -1214,7 +1351,8 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
       XCHG_CUDA_TRY(cudaMemsetAsync(w.tile_counter, 0, 64, s));
       XCHG_CUDA_TRY(cudaMemsetAsync(w.status, 0, (size_t)ntiles * BINS * 4, s));
       rc = onesweep_pass(p == KEY_PLACES ? 1 : 0, kin, vin, kout, vout, n32, 8 * p, w.gexcl + p * BINS,
-                         w.status, w.tile_counter, validity, validity_bit_offset, nullptr, nullptr, 0, s);
+                         w.status, w.tile_counter, validity, validity_bit_offset, nullptr, nullptr, 0, s,
+                         j == 0 ? raw : nullptr);
       if (rc) return rc;
       kin = kout;
       vin = vout;
@@ -1242,7 +1380,7 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
       XCHG_CUDA_TRY(cudaMemsetAsync(w.status, 0, (size_t)((n32 + tile_rows - 1) / tile_rows) * BINS * 4, s));
       rc = onesweep_pass(p == KEY_PLACES ? 1 : 0, w.norm, perm_in, side_keys(0), side_vals(0), n32, 8 * p,
                          w.gexcl + p * BINS, w.status, w.tile_counter, validity, validity_bit_offset,
-                         nullptr, nullptr, 0, s);
+                         nullptr, nullptr, 0, s, raw);
       if (rc) return rc;
       hist = w.ghist + p * BINS;
       excl = w.gexcl + p * BINS;

@@ -262,7 +262,9 @@ def try_sort(ex, ds, sort_key: SortKey, boundaries: Optional[list], seed: int, c
     pay_cols = list(range(ncw - 1))
 
     def push_payload():
-        cap = int(os.environ.get("XCHG_SIDE_CTAS_PER_SM", "0"))
+        # the stores are link-bound: a CTA or two per SM keep NVLink busy and leave the rest of
+        # every SM (shared memory above all) to the receive-side sorts and gathers
+        cap = int(os.environ.get("XCHG_SIDE_CTAS_PER_SM", "1"))
         if cap:
             rt.call("xchg_set_gather_ctas_per_sm", cap, launches=0)
         try:
@@ -276,13 +278,13 @@ def try_sort(ex, ds, sort_key: SortKey, boundaries: Optional[list], seed: int, c
             if cap:
                 rt.call("xchg_set_gather_ctas_per_sm", 0, launches=0)
 
-    if side is not None:
-        side.wait_stream(main)
-        with torch.cuda.stream(side):
-            push_payload()
-            ex._gpu_mark("g.side_payload_stored")
+    partitioned = None
+    if main is not None:
+        partitioned = torch.cuda.Event()
+        partitioned.record(main)
 
-    # ---- key runs: contiguous copies into the owners' arenas, flag per chunk ----
+    # ---- key runs: contiguous copies into the owners' arenas, flag per chunk (queued
+    # before the payload so that their CTAs are placed first) ----
     for c in range(nchunks):
         srcs, dsts, nbs = [], [], []
         for g in owners:
@@ -300,7 +302,14 @@ def try_sort(ex, ds, sort_key: SortKey, boundaries: Optional[list], seed: int, c
         fp, k = flag_ptrs(KIND_KEYS, c)
         rt.call("xchg_signal_flags", fp, k, epoch, rt.stream)
     ex._gpu_mark("g.keys_stored")
-    if side is None:  # host double: no streams, everything in program order
+
+    # ---- payload: side stream, chunk after chunk ----
+    if side is not None:
+        with torch.cuda.stream(side):
+            side.wait_event(partitioned)
+            push_payload()
+            ex._gpu_mark("g.side_payload_stored")
+    else:  # host double: no streams, everything in program order
         push_payload()
 
     # ---- receive: chunk by chunk ----

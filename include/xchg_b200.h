@@ -288,6 +288,30 @@ int xchg_signal_flags(uint32_t* const* flag_ptrs_host, int n, uint32_t value, vo
 int xchg_wait_flags(const uint32_t* flags, int n, uint32_t value, uint64_t timeout_ns,
                     uint32_t* error_flag, void* stream);
 
+/* ---------------------------------------------------------------- merge ---- */
+/*
+ * K6: stable k-way merge of sorted runs.  Replaces the reduce side of the reference's
+ * sort -- ArrowBlockAccessor.merge_sorted_blocks -> concat_and_sort
+ * (python/ray/data/_internal/arrow_block.py:529-541, _internal/arrow_ops/
+ * transform_pyarrow.py:540-547: concatenate the runs, sort everything again) -- by a merge:
+ * the result is identical (ties keep (run index, position in run) order), every key is
+ * read ceil(log2(nruns)) times instead of being re-sorted.
+ *
+ *  keys_in    radix keys (xchg_normalize_keys) of all runs back to back; run r =
+ *             [run_start_host[r], run_start_host[r+1]), ascending inside every run
+ *  vals_in    row ids travelling with the keys, or NULL = positions 0..n-1
+ *  run_start_host  HOST array, nruns + 1 entries, run_start_host[0] = 0 (<= 128 runs)
+ *  keys_out / vals_out  n merged entries each (must not alias the inputs)
+ *  workspace  xchg_merge_workspace_bytes(n) bytes
+ *  unsorted_flag_out  optional device uint32: set to 1 when some run is NOT ascending (the
+ *             output is then meaningless; callers fall back to xchg_sort_column)
+ */
+int xchg_merge_workspace_bytes(uint64_t n, uint64_t* bytes_out);
+int xchg_merge_sorted_runs(const uint64_t* keys_in, const uint32_t* vals_in,
+                           const uint64_t* run_start_host, int nruns, uint64_t* keys_out,
+                           uint32_t* vals_out, void* workspace, uint64_t workspace_bytes,
+                           uint32_t* unsorted_flag_out, void* stream);
+
 /* ------------------------------------------------- string / binary keys ---- */
 /*
  * Sort keys of variable-width columns (Arrow binary / string, int64 byte offsets as this

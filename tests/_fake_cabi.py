@@ -418,6 +418,37 @@ class FakeLib:
                 return 0
             time.sleep(0.0005)
 
+    # -- merge ---------------------------------------------------------------------
+    def xchg_merge_workspace_bytes(self, n, out):
+        out._obj.value = n * 12 + 1024
+        return 0
+
+    def xchg_merge_sorted_runs(self, keys_in, vals_in, run_start, nruns, keys_out, vals_out, ws, wsb, flag, stream):
+        """Contract: the stable sort of the concatenation (what merging sorted runs with ties
+        resolved by (run, position) gives); the flag reports a run that is not ascending."""
+        if _addr(flag):
+            _arr(flag, np.uint32, 1)[0] = 0
+        if nruns == 0:
+            return 0
+        n = int(run_start[nruns])
+        if n == 0:
+            return 0
+        if nruns > 128:
+            self.err = b"at most 128 runs per call"
+            return -1
+        k = _arr(keys_in, np.uint64, n)
+        v = _arr(vals_in, np.uint32, n) if _addr(vals_in) else np.arange(n, dtype=np.uint32)
+        if _addr(flag):
+            bad = False
+            for r in range(nruns):
+                seg = k[int(run_start[r]):int(run_start[r + 1])]
+                bad = bad or bool((seg[1:] < seg[:-1]).any())
+            _arr(flag, np.uint32, 1)[0] = int(bad)
+        order = np.argsort(k, kind="stable")
+        _arr(keys_out, np.uint64, n)[:] = k[order]
+        _arr(vals_out, np.uint32, n)[:] = v[order]
+        return 0
+
     # -- exchange-side entry points ------------------------------------------
     def xchg_assign_partitions(self, cols, col_desc, ncols, n, lower, upper, flags, nb, first_desc, dest, counts,
                                stream):
