@@ -90,7 +90,7 @@ def _table(rng, n, ktype, nulls):
         k = rng.standard_normal(n).round(1)
         k[rng.random(n) < 0.1] = np.nan
     else:
-        k = rng.integers(-5, 6, n)
+        k = rng.integers(0 if pa.types.is_unsigned_integer(ktype) else -5, 6, n)
     mask = rng.random(n) < 0.15 if nulls else None
     return pa.table({"k": pa.array(k, ktype, mask=mask), "i": pa.array(np.arange(n), pa.int64()),
                      "s": pa.array([None if rng.random() < 0.2 else "x" * int(rng.integers(0, 5)) for _ in range(n)])})
