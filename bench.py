@@ -566,7 +566,23 @@ def run_b200(args):
         blocks, keep = host_blocks_from_device(rt, keys, data, ds.block_ranges)
         h2d = sum(b.nbytes for b in blocks)
 
+        breakdown = {} if os.environ.get("XCHG_E2E_BREAKDOWN", "0") == "1" else None
+
         def e2e_step(i):
+            if breakdown is not None:
+                # diagnostics: the three phases one after the other, a synchronise between them
+                t = [time.perf_counter()]
+                dsx = ex.stage(blocks)
+                torch.cuda.synchronize()
+                t.append(time.perf_counter())
+                outx = ex.sort_distributed(dsx, sk, seed=i) if world > 1 else ex.sort(dsx, sk, seed=i)
+                torch.cuda.synchronize()
+                t.append(time.perf_counter())
+                res = ex.export(outx)
+                t.append(time.perf_counter())
+                for nm, a, b in (("stage_h2d", 0, 1), ("sort", 1, 2), ("export_d2h", 2, 3)):
+                    breakdown.setdefault(nm, []).append(round((t[b] - t[a]) * 1e3, 1))
+                return res
             if world > 1:
                 return ex.sort_blocks_distributed(blocks, sk, seed=i)
             return ex.sort_blocks(blocks, sk, seed=i)
@@ -594,16 +610,33 @@ def run_b200(args):
             dist.all_reduce(sums)
             dt, rows, h2d, d2h = float(tm.item()), int(sums[0].item()), int(sums[1].item()), int(sums[2].item())
         assert rows == total_rows
+        if breakdown is not None:
+            print(f"[e2e breakdown rank {rank}] ms per call (warm-up calls first): {json.dumps(breakdown)}",
+                  file=sys.stderr, flush=True)
         e2e = {"value": total_rows / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                "ms_per_step": dt * 1e3, "steps": e_steps,
                "api": ("DeviceExchange.sort_blocks_distributed" if world > 1 else "DeviceExchange.sort_blocks")
                       + "(pinned host Arrow blocks) -> host Arrow blocks; wall clock, max over ranks"}
         del blocks, keep
 
+    # ---- the path's other operators (N=1 only): random_shuffle, groupby.aggregate, string-key
+    # sort and configs[0], same event / per-kernel bookkeeping (scripts/bench_ops.py) ----
+    ops = None
+    if world == 1 and not args.no_ops:
+        del ds, keys, data
+        ds = keys = data = None
+        torch.cuda.empty_cache()
+        import importlib.util
+
+        spec = importlib.util.spec_from_file_location("bench_ops", os.path.join(ROOT, "scripts", "bench_ops.py"))
+        bench_ops = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(bench_ops)
+        ops = bench_ops.run_ops(rt, ex, lib, peak, steps=5, warmup=3)
+
     # ---- CPU baseline (rank 0, N=1 only): bounded sample of the same workload ----
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        del ds, keys, data
+        ds = keys = data = None
         torch.cuda.empty_cache()
         cores = len(os.sched_getaffinity(0))
         ref = CpuReference(cores, args.cpu_rows_per_block, args.cpu_blocks or cores)
@@ -662,6 +695,7 @@ def run_b200(args):
             "kernels": kernels,
             "e2e": e2e,
             "cpu_baseline": cpu,
+            "ops": ops,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -679,6 +713,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-ops", action="store_true", help="skip the secondary operators' lines (ops key)")
     ap.add_argument("--trace", action="store_true",
                     help="diagnostics: synchronise after every phase of the distributed sort and print "
                          "per-phase wall-clock ms (serialises the pipeline; not a bench number)")

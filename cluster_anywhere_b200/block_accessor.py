@@ -63,15 +63,15 @@ class B200ArrowBlockAccessor:
     # -- plumbing ------------------------------------------------------------
     @staticmethod
     def for_block(block, runtime: Optional[dev.Runtime] = None) -> "B200ArrowBlockAccessor":
-        """python/ray/data/block.py:446-473 (Arrow branch only; pandas blocks are
-        converted by the caller)."""
+        """python/ray/data/block.py:446-473: Arrow tables and pandas DataFrames (a DataFrame
+        gets the accessor whose outputs are DataFrames again)."""
         if isinstance(block, B200ArrowBlockAccessor):
             return block
         try:
             import pandas as pd
 
             if isinstance(block, pd.DataFrame):
-                block = pa.Table.from_pandas(block, preserve_index=False)
+                return B200PandasBlockAccessor(block, runtime)
         except ImportError:
             pass
         return B200ArrowBlockAccessor(block, runtime)
@@ -374,3 +374,95 @@ class B200ArrowBlockAccessor:
             if finalize:
                 ret = agg.null_typed_like_reference(ret)
         return ret, B200ArrowBlockAccessor(ret, runtime).get_metadata(exec_stats=stats.build())
+
+
+def is_pandas_block(block) -> bool:
+    try:
+        import pandas as pd
+    except ImportError:
+        return False
+    return isinstance(block, pd.DataFrame)
+
+
+def want_pandas_output(blocks, batch_format: str = "default") -> bool:
+    """Block type of a reduce task's output (TableBlockAccessor.normalize_block_types,
+    python/ray/data/_internal/table_block.py:266-316): all inputs of one type -> that type;
+    mixed -> ``batch_format`` decides."""
+    kinds = {is_pandas_block(b) for b in blocks if b is not None}
+    if len(kinds) == 1:
+        return kinds.pop()
+    return batch_format == "pandas"
+
+
+def _to_pandas(table):
+    import pandas as pd
+
+    if isinstance(table, pd.DataFrame):
+        return table
+    if table.num_columns == 0:
+        return pd.DataFrame()  # pandas_block.py: _empty_table()
+    return table.to_pandas()
+
+
+class B200PandasBlockAccessor(B200ArrowBlockAccessor):
+    """Pandas twin (python/ray/data/_internal/pandas_block.py:503-746): DataFrame in,
+    DataFrame out.  The rows go through the same kernels as Arrow blocks (the frame is
+    converted on the way in -- missing values, NaN included, become nulls, which sort last
+    in both directions like pandas' ``na_position='last'`` -- and back on the way out).
+    The reference's single-key ``sort_values`` is not stable; this one is, which is one of
+    the orders it may produce."""
+
+    def __init__(self, frame, runtime: Optional[dev.Runtime] = None):
+        super().__init__(pa.Table.from_pandas(frame, preserve_index=False), runtime)
+        self._frame = frame
+
+    def to_block(self):
+        return self._frame
+
+    def to_pandas(self):
+        return self._frame
+
+    @staticmethod
+    def _empty_table():
+        import pandas as pd
+
+        return pd.DataFrame()
+
+    def slice(self, start: int, end: int, copy: bool = False):
+        # pandas_block.py:219-224: a re-indexed view, deep-copied on request
+        view = self._frame.iloc[start:end].reset_index(drop=True)
+        return view.copy(deep=True) if copy else view
+
+    def select(self, columns: List[str]):
+        return _to_pandas(super().select(columns))
+
+    def take(self, indices):
+        return _to_pandas(super().take(indices))
+
+    def sample(self, n_samples: int, sort_key: SortKey):
+        return _to_pandas(super().sample(n_samples, sort_key))
+
+    def random_shuffle(self, random_seed: Optional[int]):
+        return _to_pandas(super().random_shuffle(random_seed))
+
+    def sort(self, sort_key: SortKey):
+        return _to_pandas(super().sort(sort_key))
+
+    def sort_and_partition(self, boundaries: List[tuple], sort_key: SortKey) -> list:
+        return [_to_pandas(t) for t in super().sort_and_partition(boundaries, sort_key)]
+
+    def combine(self, sort_key: SortKey, aggs):
+        return _to_pandas(super().combine(sort_key, aggs))
+
+    @staticmethod
+    def merge_sorted_blocks(blocks: list, sort_key: SortKey, runtime: Optional[dev.Runtime] = None):
+        tables = [B200ArrowBlockAccessor.for_block(b).to_arrow() for b in blocks]
+        ret, meta = B200ArrowBlockAccessor.merge_sorted_blocks(tables, sort_key, runtime)
+        return _to_pandas(ret), meta
+
+    @staticmethod
+    def aggregate_combined_blocks(blocks: list, sort_key: SortKey, aggs, finalize: bool = True,
+                                  runtime: Optional[dev.Runtime] = None):
+        tables = [B200ArrowBlockAccessor.for_block(b).to_arrow() for b in blocks]
+        ret, meta = B200ArrowBlockAccessor.aggregate_combined_blocks(tables, sort_key, aggs, finalize, runtime)
+        return _to_pandas(ret), meta

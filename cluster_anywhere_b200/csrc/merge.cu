@@ -143,7 +143,7 @@ extern "C" int xchg_merge_workspace_bytes(uint64_t n, uint64_t* bytes_out) {
     xchg_set_error("n=%llu exceeds XCHG_MAX_ROWS", (unsigned long long)n);
     return XCHG_ERR_LIMIT;
   }
-  *bytes_out = xchg_align_up(n * 8, 256) + xchg_align_up(n * 4, 256) + 512;
+  *bytes_out = xchg_align_up(n * 8, 256) + xchg_align_up(n * 4, 256) + 256 + (2 * MG_MAX_PAIRS + 2) * 8;
   return XCHG_OK;
 }
 
@@ -183,8 +183,7 @@ extern "C" int xchg_merge_sorted_runs(const uint64_t* keys_in, const uint32_t* v
   for (int kk = k; kk > 1; kk = (kk + 1) / 2) ++rounds;
 
   if (unsorted_flag_out) {
-    // run starts to the device: the tail of the workspace (512 bytes are reserved; more runs
-    // than fit there are checked pair by pair through the merge's own reads instead)
+    // run starts to the device: the tail of the workspace
     XCHG_REQUIRE(workspace != nullptr, "the sortedness check needs the workspace");
     uint64_t need = xchg_align_up(n * 8, 256) + xchg_align_up(n * 4, 256);
     XCHG_REQUIRE((uint64_t)(base - (uint8_t*)workspace) + need + (uint64_t)(k + 1) * 8 <= workspace_bytes,

@@ -126,14 +126,20 @@ k_scan_hist(const uint32_t* __restrict__ ghist, uint32_t* __restrict__ gexcl,
 }
 
 // First look at a key column that is sorted straight from its raw values (no nulls, no
-// incoming permutation): OR and AND of all radix keys -- a digit place is trivial exactly
-// when every key has the same byte there, i.e. (OR ^ AND) has a zero byte -- and the
-// histograms of the places in place_mask (the one place the first pass runs on, guessed
-// as the type's top byte; all active places for an all-LSD sort).  Nothing is written per
-// row: the passes read the raw column again and normalise in registers (RAW passes).
+// incoming permutation): OR and AND of all radix keys -- the keys differ exactly in the bits
+// of OR ^ AND, so the digit places are laid over [lowest differing bit, highest differing
+// bit] instead of over fixed bytes -- and the histograms of the digit places in `ks` (the
+// place the first pass runs on, guessed from the previous sort of this key type; all places
+// for an all-LSD sort).  Nothing is written per row: the passes read the raw column again
+// and normalise in registers (RAW passes).
+struct KeyShifts {
+  int n;                  // digit places to build histograms for (slot h -> ghist + h * BINS)
+  int shift[KEY_PLACES];  // any bit position: a digit is (key >> shift) & 255
+};
+
 template <typename T>
 __global__ void __launch_bounds__(256)
-k_key_scan(const T* __restrict__ keys, uint32_t n, int desc, uint32_t place_mask, int want_orand,
+k_key_scan(const T* __restrict__ keys, uint32_t n, int desc, KeyShifts ks, int want_orand,
            unsigned long long* __restrict__ orand, uint32_t* __restrict__ ghist) {
   __shared__ uint32_t sh[KEY_PLACES * BINS];
   __shared__ unsigned long long s_or[8], s_and[8];
@@ -153,9 +159,8 @@ k_key_scan(const T* __restrict__ keys, uint32_t n, int desc, uint32_t place_mask
     }
     const unsigned act = __ballot_sync(0xffffffffu, active);
     const int first = __ffs(act) - 1;
-    for (uint32_t pm = place_mask; pm; pm &= pm - 1) {
-      const int p = __ffs(pm) - 1;
-      const uint32_t d = (uint32_t)(key >> (8 * p)) & 255u;
+    for (int p = 0; p < ks.n; ++p) {
+      const uint32_t d = (uint32_t)(key >> ks.shift[p]) & 255u;
       const uint32_t d0 = __shfl_sync(0xffffffffu, d, first);
       const bool uni = __all_sync(0xffffffffu, !active || d == d0);
       if (uni) {
@@ -186,8 +191,7 @@ k_key_scan(const T* __restrict__ keys, uint32_t n, int desc, uint32_t place_mask
     atomicOr(&orand[0], (unsigned long long)o);
     atomicAnd(&orand[1], (unsigned long long)a);
   }
-  for (uint32_t pm = place_mask; pm; pm &= pm - 1) {
-    const int p = __ffs(pm) - 1;
+  for (int p = 0; p < ks.n; ++p) {
     for (int j = threadIdx.x; j < BINS; j += blockDim.x)
       if (sh[p * BINS + j]) atomicAdd(&ghist[p * BINS + j], sh[p * BINS + j]);
   }
@@ -1060,7 +1064,7 @@ int dispatch_normalize(const void* keys, int key_type, const uint32_t* perm, con
   return XCHG_OK;
 }
 
-int dispatch_key_scan(const void* keys, int key_type, uint32_t n, int desc, uint32_t place_mask,
+int dispatch_key_scan(const void* keys, int key_type, uint32_t n, int desc, const KeyShifts& place_mask,
                       int want_orand, unsigned long long* orand, uint32_t* ghist, cudaStream_t s) {
   const int blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)xchg_sm_count() * 8);
   const bool ok = xchg_dispatch_key_type(key_type, [&](auto tag) {
@@ -1266,11 +1270,16 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
 
   XCHG_CUDA_TRY(cudaMemsetAsync(w.ghist, 0, NUM_PLACES * BINS * 4, s));
   int rc;
-  int places[NUM_PLACES];
+  // digit places in ascending significance: shift, histogram slot (ghist / gexcl row)
+  struct Place {
+    int shift, slot;
+    bool validity;
+  };
+  Place places[NUM_PLACES];
   int np = 0;
   // A column without nulls that is sorted in its stored order needs no materialised radix
-  // keys: one scan tells which digit places matter (and builds the first pass's histogram),
-  // the first pass reads the raw values (RAW).  XCHG_SORT_RAW=0 keeps the normalise pass.
+  // keys: one scan tells which bits matter (and builds the first pass's histogram), the
+  // first pass reads the raw values (RAW).  XCHG_SORT_RAW=0 keeps the normalise pass.
   static const bool raw_enabled = [] {
     const char* e = getenv("XCHG_SORT_RAW");
     return !(e && atoi(e) == 0);
@@ -1283,24 +1292,48 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
     unsigned long long* orand = (unsigned long long*)w.active;  // 64 bytes: {OR, AND}
     XCHG_CUDA_TRY(cudaMemsetAsync(orand, 0, 8, s));
     XCHG_CUDA_TRY(cudaMemsetAsync(orand + 1, 0xFF, 8, s));
-    const int guess = key_type_bytes(key_type) - 1;  // the type's top byte
-    rc = dispatch_key_scan(keys, key_type, n32, descending, 1u << guess, 1, orand, w.ghist, s);
+    // the top place's shift is only known after the scan: guess it (what the last sort of
+    // this key type used; the type's top byte the first time) and scan again on a miss
+    static std::atomic<int> last_top_shift[XCHG_F64 + 1];
+    static std::atomic<bool> last_init{false};
+    if (!last_init.exchange(true))
+      for (int t = 0; t <= XCHG_F64; ++t) last_top_shift[t].store(8 * (key_type_bytes(t) - 1));
+    KeyShifts ks;
+    ks.n = 1;
+    ks.shift[0] = last_top_shift[key_type].load();
+    rc = dispatch_key_scan(keys, key_type, n32, descending, ks, 1, orand, w.ghist, s);
     if (rc) return rc;
     unsigned long long oa[2];
     XCHG_CUDA_TRY(cudaMemcpyAsync(oa, orand, sizeof(oa), cudaMemcpyDeviceToHost, s));
     XCHG_CUDA_TRY(cudaStreamSynchronize(s));
     const uint64_t diff = oa[0] ^ oa[1];
-    uint32_t need = 0;
-    for (int p = 0; p < KEY_PLACES; ++p)
-      if ((diff >> (8 * p)) & 0xFF) places[np++] = p;
-    if (np > 0) {
-      if (sort_algorithm() == 1 || np <= 2) {
-        for (int j = 0; j < np; ++j) need |= 1u << places[j];
-      } else {
-        need = 1u << places[np - 1];
+    if (diff) {
+      const int top = 63 - __builtin_clzll(diff), low = __builtin_ctzll(diff);
+      // places from the top bit down, 8 bits each, the lowest one clamped to `low` (it may
+      // then share bits with its neighbour: harmless for a stable pass in either direction)
+      int shifts[KEY_PLACES];
+      int cnt = 0;
+      for (int sh = std::max(low, top - 7);; sh = std::max(low, sh - 8)) {
+        shifts[cnt++] = sh;
+        if (sh == low) break;
       }
-      need &= ~(1u << guess);
-      if (need) {
+      np = cnt;
+      for (int j = 0; j < np; ++j) places[j] = Place{shifts[np - 1 - j], 0, false};
+      last_top_shift[key_type].store(places[np - 1].shift);
+      const bool all_places = sort_algorithm() == 1 || np <= 2;
+      const bool hit = ks.shift[0] == places[np - 1].shift;
+      if (all_places ? !(hit && np == 1) : !hit) {
+        KeyShifts need;
+        need.n = 0;
+        if (all_places) {
+          for (int j = 0; j < np; ++j) {
+            places[j].slot = need.n;
+            need.shift[need.n++] = places[j].shift;
+          }
+        } else {
+          need.shift[need.n++] = places[np - 1].shift;
+        }
+        XCHG_CUDA_TRY(cudaMemsetAsync(w.ghist, 0, NUM_PLACES * BINS * 4, s));
         rc = dispatch_key_scan(keys, key_type, n32, descending, need, 0, orand, w.ghist, s);
         if (rc) return rc;
       }
@@ -1317,9 +1350,9 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
     XCHG_CUDA_TRY(cudaMemcpyAsync(active, w.active, sizeof(active), cudaMemcpyDeviceToHost, s));
     XCHG_CUDA_TRY(cudaStreamSynchronize(s));
     for (int p = 0; p < KEY_PLACES; ++p)
-      if (active[p]) places[np++] = p;
+      if (active[p]) places[np++] = Place{8 * p, p, false};
     const bool wide_int = key_type == XCHG_I64 || key_type == XCHG_U64;
-    if (wide_int && validity && active[KEY_PLACES]) places[np++] = KEY_PLACES;
+    if (wide_int && validity && active[KEY_PLACES]) places[np++] = Place{0, KEY_PLACES, true};
   }
 
   uint64_t* keys_a = norm_keys_out ? norm_keys_out : w.keys_a;
@@ -1347,10 +1380,10 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
       const bool to_a = ((np - 1 - j) % 2) == 0;  // the last pass lands on side A
       uint64_t* kout = to_a ? keys_a : w.keys_b;
       uint32_t* vout = to_a ? perm_out : w.vals_b;
-      const int p = places[j];
+      const Place p = places[j];
       XCHG_CUDA_TRY(cudaMemsetAsync(w.tile_counter, 0, 64, s));
       XCHG_CUDA_TRY(cudaMemsetAsync(w.status, 0, (size_t)ntiles * BINS * 4, s));
-      rc = onesweep_pass(p == KEY_PLACES ? 1 : 0, kin, vin, kout, vout, n32, 8 * p, w.gexcl + p * BINS,
+      rc = onesweep_pass(p.validity ? 1 : 0, kin, vin, kout, vout, n32, p.shift, w.gexcl + p.slot * BINS,
                          w.status, w.tile_counter, validity, validity_bit_offset, nullptr, nullptr, 0, s,
                          j == 0 ? raw : nullptr);
       if (rc) return rc;
@@ -1369,7 +1402,7 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
   MsdCounters h;
   uint32_t nbig = 1, ntiles_l = 0;
   for (int l = 0; l < np; ++l) {
-    const int p = places[np - 1 - l];
+    const Place p = places[np - 1 - l];
     const bool last = l == np - 1;
     Seg* cur = w.big[l & 1];
     Seg* nxt = w.big[(l + 1) & 1];
@@ -1378,21 +1411,21 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
     XCHG_CUDA_TRY(cudaMemsetAsync(w.tile_counter, 0, 64, s));
     if (l == 0) {
       XCHG_CUDA_TRY(cudaMemsetAsync(w.status, 0, (size_t)((n32 + tile_rows - 1) / tile_rows) * BINS * 4, s));
-      rc = onesweep_pass(p == KEY_PLACES ? 1 : 0, w.norm, perm_in, side_keys(0), side_vals(0), n32, 8 * p,
-                         w.gexcl + p * BINS, w.status, w.tile_counter, validity, validity_bit_offset,
+      rc = onesweep_pass(p.validity ? 1 : 0, w.norm, perm_in, side_keys(0), side_vals(0), n32, p.shift,
+                         w.gexcl + p.slot * BINS, w.status, w.tile_counter, validity, validity_bit_offset,
                          nullptr, nullptr, 0, s, raw);
       if (rc) return rc;
-      hist = w.ghist + p * BINS;
-      excl = w.gexcl + p * BINS;
+      hist = w.ghist + p.slot * BINS;
+      excl = w.gexcl + p.slot * BINS;
     } else {
       XCHG_LAUNCH(XK_MSD_AUX, s, k_fill_tile_map<<<nbig, 128, 0, s>>>(cur, tile_rows, w.tile_seg));
       XCHG_CUDA_TRY(cudaMemsetAsync(w.seg_hist, 0, (size_t)nbig * BINS * 4, s));
       XCHG_CUDA_TRY(cudaMemsetAsync(w.status, 0, (size_t)ntiles_l * BINS * 4, s));
-      rc = seg_hist_pass(side_keys(l - 1), 8 * p, cur, w.tile_seg, ntiles_l, w.seg_hist, s);
+      rc = seg_hist_pass(side_keys(l - 1), p.shift, cur, w.tile_seg, ntiles_l, w.seg_hist, s);
       if (rc) return rc;
       XCHG_LAUNCH(XK_MSD_AUX, s, k_seg_scan<<<nbig, BINS, 0, s>>>(w.seg_hist, w.seg_excl));
       XCHG_LAUNCH_CHECK();
-      rc = onesweep_pass(0, side_keys(l - 1), side_vals(l - 1), side_keys(l), side_vals(l), 0, 8 * p,
+      rc = onesweep_pass(0, side_keys(l - 1), side_vals(l - 1), side_keys(l), side_vals(l), 0, p.shift,
                          w.seg_excl, w.status, w.tile_counter, nullptr, 0, cur, w.tile_seg, ntiles_l, s);
       if (rc) return rc;
       hist = w.seg_hist;
@@ -1400,7 +1433,7 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
     }
     if (last) break;  // every row now sits at its final position on side A
     XCHG_CUDA_TRY(cudaMemsetAsync(w.ctr, 0, sizeof(MsdCounters), s));
-    const int can_group = p != KEY_PLACES;
+    const int can_group = !p.validity;
     SmallLists lists;
     for (int c = 0; c < LS_CLASSES; ++c) lists.p[c] = w.small[c];
     XCHG_LAUNCH(XK_MSD_AUX, s,
@@ -1412,8 +1445,8 @@ extern "C" int xchg_sort_column(const void* keys, int key_type, int descending,
     // small children of this level: finish them now, by the places below this one
     LocalPlaces lp;
     lp.n = np - 1 - l;
-    for (int j = 0; j < lp.n; ++j) lp.shift[j] = 8 * places[j];
-    lp.shift[lp.n] = can_group ? 8 * p : 0;
+    for (int j = 0; j < lp.n; ++j) lp.shift[j] = places[j].shift;
+    lp.shift[lp.n] = can_group ? p.shift : 0;
     rc = local_sort_level(side_keys(l), side_vals(l), keys_a, perm_out, w.small, h.nsmall, lp, s);
     if (rc) return rc;
     nbig = h.nbig;

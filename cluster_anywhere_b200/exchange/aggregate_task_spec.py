@@ -54,9 +54,12 @@ class SortAggregateTaskSpec(ExchangeTaskSpec):
     def reduce(key: SortKey, aggs: list, batch_format: str, *mapper_outputs,
                partial_reduce: bool = False) -> Tuple[pa.Table, BlockMetadata]:
         """aggregate_task_spec.py:61-74."""
+        from ..block_accessor import B200PandasBlockAccessor
+
         blocks = [B200ArrowBlockAccessor.for_block(b).to_arrow() for b in mapper_outputs]
-        return B200ArrowBlockAccessor.aggregate_combined_blocks(blocks, key, aggs,
-                                                                finalize=not partial_reduce)
+        # partial blocks are the engine's own format; only a FINAL block follows batch_format
+        cls = B200PandasBlockAccessor if (batch_format == "pandas" and not partial_reduce) else B200ArrowBlockAccessor
+        return cls.aggregate_combined_blocks(blocks, key, aggs, finalize=not partial_reduce)
 
     @staticmethod
     def _prune_unused_columns(block, sort_key: SortKey, aggs):

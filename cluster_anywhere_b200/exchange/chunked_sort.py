@@ -9,9 +9,11 @@ merge with ``partial_reduce=True`` :696-730), and the final reduce of partition 
 when partition j's merge outputs exist (:330-397).  Here a "round" is a CHUNK: rank g's
 key range (its run of output blocks) is cut at block boundaries into up to
 ``XCHG_CHUNKS`` sub-ranges; every rank partitions its rows by (destination rank, chunk)
-in one stable pass, stores chunk after chunk into the owners' arenas and raises one
-4-byte arrival flag per (owner, chunk); the owner waits for the G flags of chunk c on
-the stream that sorts it, never for the whole exchange.
+in one stable pass, stores the payload chunk after chunk into the owners' arenas and
+raises one 4-byte arrival flag per (owner, chunk); the owner's final gather of chunk c
+waits for the G flags of chunk c, never for the whole exchange.  The radix keys (8 % of
+the bytes) go first, in one piece: the owner sorts them once while the payload is still
+crossing NVLink.
 
 Per rank and step (device-resident input):
 
@@ -19,11 +21,12 @@ Per rank and step (device-resident input):
                 boundary selection (one CTA) -> destination histogram -> all-gather of
                 the counts -> stable partition (radix key, row id) by destination
                 [D2H of the count matrix] -> key runs copied to the owners, flag per chunk
-                for every own chunk c: wait(keys, c) -> stable sort of the chunk's radix
-                keys -> block cuts (K4) -> key column from the sorted radix keys
   side stream   for every chunk c: payload rows gathered straight into the owners'
-                arenas (K5 storing over NVLink), flag per chunk
-  gather stream for every own chunk c: wait(payload, c) -> final payload gather (K5)
+                arenas (K5 storing over NVLink, a CTA or two per SM), flag per chunk
+  receive stream  wait(keys) -> ONE stable sort of all received radix keys -> block cuts
+                (K4) -> key column from the sorted radix keys; then for every own chunk c:
+                wait(payload, c) -> final payload gather (K5) of the chunk's slice of the
+                sorted order
 
 Eligible: ONE fixed-width key column without nulls (any of the ten key types;
 descending floats excepted), payload columns fixed-width or uniform-width without
@@ -258,13 +261,13 @@ def try_sort(ex, ds, sort_key: SortKey, boundaries: Optional[list], seed: int, c
 
     # ---- payload: side stream, chunk after chunk ----
     side = _stream(ex, "_side_stream")
-    gat = _stream(ex, "_gather_stream")
+    srt = _stream(ex, "_sort_stream")
     pay_cols = list(range(ncw - 1))
 
     def push_payload():
         # the stores are link-bound: a CTA or two per SM keep NVLink busy and leave the rest of
         # every SM (shared memory above all) to the receive-side sorts and gathers
-        cap = int(os.environ.get("XCHG_SIDE_CTAS_PER_SM", "1"))
+        cap = int(os.environ.get("XCHG_SIDE_CTAS_PER_SM", "2"))
         if cap:
             rt.call("xchg_set_gather_ctas_per_sm", cap, launches=0)
         try:
@@ -283,10 +286,11 @@ def try_sort(ex, ds, sort_key: SortKey, boundaries: Optional[list], seed: int, c
         partitioned = torch.cuda.Event()
         partitioned.record(main)
 
-    # ---- key runs: contiguous copies into the owners' arenas, flag per chunk (queued
-    # before the payload so that their CTAs are placed first) ----
+    # ---- key runs: contiguous copies into the owners' arenas, ONE flag per owner (queued
+    # before the payload so that their CTAs are placed first; the keys are 8 % of the bytes
+    # and the receive-side sort wants all of them at once) ----
+    srcs, dsts, nbs = [], [], []
     for c in range(nchunks):
-        srcs, dsts, nbs = [], [], []
         for g in owners:
             if c >= len(chunks_of[g]):
                 continue
@@ -296,11 +300,12 @@ def try_sort(ex, ds, sort_key: SortKey, boundaries: Optional[list], seed: int, c
                 srcs.append(pk.data_ptr() + int(pl.cuts[v]) * 8)
                 dsts.append(arena.ptrs[g] + pl.offsets_of[g][(kj, "data")] + int(pl.prefix_rows[rank, v]) * 8)
                 nbs.append(k * 8)
-        if srcs:
-            rt.call("xchg_copy_segments", len(srcs), (ctypes.c_void_p * len(srcs))(*srcs),
-                    (ctypes.c_void_p * len(srcs))(*dsts), (ctypes.c_uint64 * len(srcs))(*nbs), rt.stream)
-        fp, k = flag_ptrs(KIND_KEYS, c)
-        rt.call("xchg_signal_flags", fp, k, epoch, rt.stream)
+    if srcs:
+        rt.call("xchg_copy_segments", len(srcs), (ctypes.c_void_p * len(srcs))(*srcs),
+                (ctypes.c_void_p * len(srcs))(*dsts), (ctypes.c_uint64 * len(srcs))(*nbs), rt.stream,
+                launches=(len(srcs) + 15) // 16)
+    fp, k = flag_ptrs(KIND_KEYS, 0)
+    rt.call("xchg_signal_flags", fp, k, epoch, rt.stream)
     ex._gpu_mark("g.keys_stored")
 
     # ---- payload: side stream, chunk after chunk ----
@@ -328,59 +333,61 @@ def try_sort(ex, ds, sort_key: SortKey, boundaries: Optional[list], seed: int, c
             w = c.width if c.kind == "fixed" else c.uniform
             out_cols[j] = (c, w, rt.empty(m * w))
         out_key = rt.empty(m * keycol.width) if int_key else None
-        max_rows = max(int(pl.vrows[v]) for v in mine)
-        ws_bytes = dev.sort_workspace_bytes(max_rows)
+        ws_bytes = dev.sort_workspace_bytes(m)
         ws = rt.empty(ws_bytes)
         if nb_local:
-            cuts_d = rt.zeros(len(mine) * nb_local, torch.int64)
+            cuts_d = rt.zeros(nb_local, torch.int64)
             thr_last, has_last = keymod.last_class_threshold(kt, 0)
-        perms = []
-        for ci, v in enumerate(mine):
-            mc, base = int(pl.vrows[v]), int(pl.vstart[v])
-            rt.call("xchg_wait_flags", local_flags(KIND_KEYS, ci), G, epoch, WAIT_TIMEOUT_NS, err_ptr, rt.stream)
-            perm_c = None
-            if mc:
-                kin = _ptr(arena.buf.data_ptr(), my_off[(kj, "data")] + base * 8)
-                nout = _ptr(norm_sorted.data_ptr(), base * 8)
-                perm_c = rt.empty(mc, torch.int32)
-                rt.call("xchg_sort_column", kin, _cabi.U64, 0, None, 0, None, mc, _vp(perm_c), nout, _vp(ws),
-                        ws_bytes, rt.stream, launches=8)
-                if nb_local:
-                    ptrs = (ctypes.c_void_p * 1)(nout.value)
-                    rt.call("xchg_partition_bounds", ptrs, (ctypes.c_uint8 * 1)(int(desc)),
-                            (ctypes.c_uint64 * 1)(int(thr_last)), (ctypes.c_uint8 * 1)(int(has_last)), 1, mc,
-                            _ptr(bounds_d.data_ptr(), lo_b * 8), _ptr(bounds_d.data_ptr(), lo_b * 8),
-                            _ptr(bflags_d.data_ptr(), lo_b) if bflags_d is not None else None,
-                            nb_local, int(desc), _ptr(cuts_d.data_ptr(), ci * nb_local * 8), rt.stream)
-                if int_key:
-                    rt.call("xchg_denormalize_keys", nout, kt, int(desc), mc,
-                            _ptr(out_key.data_ptr(), base * keycol.width), rt.stream)
-            perms.append(perm_c)
-            ex._gpu_mark(f"g.keys_sorted_{ci}")
+        perm = rt.empty(m, torch.int32)
 
-            def gather_chunk(ci=ci, v=v, mc=mc, base=base, perm_c=perm_c):
-                rt.call("xchg_wait_flags", local_flags(KIND_PAYLOAD, ci), G, epoch, WAIT_TIMEOUT_NS, err_ptr,
-                        rt.stream)
-                if not mc:
-                    return
+        def sort_keys():
+            """ONE stable sort of all received radix keys (positions in arena order as the
+            values): the chunks are consecutive key ranges, so chunk c's rows end up in the
+            sorted positions [vstart_c, vstart_c + rows_c) and its final gather needs nothing
+            but that slice of the permutation."""
+            rt.call("xchg_wait_flags", local_flags(KIND_KEYS, 0), G, epoch, WAIT_TIMEOUT_NS, err_ptr, rt.stream)
+            kin = _ptr(arena.buf.data_ptr(), my_off[(kj, "data")])
+            rt.call("xchg_sort_column", kin, _cabi.U64, 0, None, 0, None, m, _vp(perm), _vp(norm_sorted), _vp(ws),
+                    ws_bytes, rt.stream, launches=8)
+            if nb_local:
+                ptrs = (ctypes.c_void_p * 1)(norm_sorted.data_ptr())
+                rt.call("xchg_partition_bounds", ptrs, (ctypes.c_uint8 * 1)(int(desc)),
+                        (ctypes.c_uint64 * 1)(int(thr_last)), (ctypes.c_uint8 * 1)(int(has_last)), 1, m,
+                        _ptr(bounds_d.data_ptr(), lo_b * 8), _ptr(bounds_d.data_ptr(), lo_b * 8),
+                        _ptr(bflags_d.data_ptr(), lo_b) if bflags_d is not None else None,
+                        nb_local, int(desc), _vp(cuts_d), rt.stream)
+            if int_key:
+                rt.call("xchg_denormalize_keys", _vp(norm_sorted), kt, int(desc), m, _vp(out_key), rt.stream)
+            ex._gpu_mark("g.keys_sorted")
+
+        def gather_chunk(ci):
+            v = mine[ci]
+            mc, base = int(pl.vrows[v]), int(pl.vstart[v])
+            rt.call("xchg_wait_flags", local_flags(KIND_PAYLOAD, ci), G, epoch, WAIT_TIMEOUT_NS, err_ptr, rt.stream)
+            if mc:
+                idx = _ptr(perm.data_ptr(), base * 4)
                 for jj, j in enumerate(pay_j):
                     c, w, out = out_cols[j]
-                    src = _ptr(arena.buf.data_ptr(), my_off[(jj, "data")] + base * w)
+                    src = _ptr(arena.buf.data_ptr(), my_off[(jj, "data")])
                     dst = _ptr(out.data_ptr(), base * w)
                     if c.kind == "fixed":
-                        rt.call("xchg_gather_fixed", src, w, _vp(perm_c), mc, dst, rt.stream)
+                        rt.call("xchg_gather_fixed", src, w, idx, mc, dst, rt.stream)
                     else:
-                        rt.call("xchg_gather_rows", src, w, _vp(perm_c), mc, dst, rt.stream)
+                        rt.call("xchg_gather_rows", src, w, idx, mc, dst, rt.stream)
+            ex._gpu_mark(f"g.taken_{ci}")
 
-            if gat is not None:
-                ev = torch.cuda.Event()
-                ev.record(main)
-                with torch.cuda.stream(gat):
-                    gat.wait_event(ev)
-                    gather_chunk()
-                    ex._gpu_mark(f"g.taken_{ci}")
-            else:
-                gather_chunk()
+        # ONE receive stream: the sort and the final gathers each want the whole SM (shared
+        # memory), so they take turns; the payload stores keep their few resident CTAs per SM
+        # throughout.  The keys (8 % of the bytes) are all there long before the payload, so
+        # the sort runs under the payload's transfer and the gathers follow the chunks in.
+        import contextlib
+
+        if srt is not None:
+            srt.wait_stream(main)
+        with (torch.cuda.stream(srt) if srt is not None else contextlib.nullcontext()):
+            sort_keys()
+            for ci in range(len(mine)):
+                gather_chunk(ci)
         cols = []
         for j in range(len(names)):
             src = table.columns[j]
@@ -394,7 +401,7 @@ def try_sort(ex, ds, sort_key: SortKey, boundaries: Optional[list], seed: int, c
                     cols.append(DeviceColumn(src.type, m, "var", src.width, out, None, None, 0, uniform=w))
         out_ds = DeviceTable(names, cols, m, table.schema)
     if main is not None:
-        main.wait_stream(gat)
+        main.wait_stream(srt)
         main.wait_stream(side)
     ex._gpu_mark("g.taken")
 
@@ -411,8 +418,7 @@ def try_sort(ex, ds, sort_key: SortKey, boundaries: Optional[list], seed: int, c
         return DeviceDataset(None, [(0, 0)] * my_blocks)
     cuts: List[int] = []
     if nb_local:
-        per_chunk = cuts_d.cpu().numpy().reshape(len(mine), nb_local)
-        cuts = [int(x) for x in per_chunk.sum(axis=0)]
+        cuts = [int(x) for x in cuts_d.cpu().numpy()]
     ranges, last = [], 0
     for c in cuts:
         ranges.append((last, c))
@@ -426,6 +432,13 @@ def _stream(ex, attr: str):
         return None
     s = getattr(ex, attr, None)
     if s is None:
-        s = torch.cuda.Stream(device=ex.rt.device)
+        # CTAs of a later kernel are placed only when the earlier kernels have none left to
+        # place, unless its stream has priority: the short receive-side sorts (which the final
+        # gathers wait for) go first, then the payload stores (the long pole whenever NVLink
+        # binds), the final gathers take what is left.  XCHG_STREAM_PRIORITIES=0: all equal.
+        prio = {"_sort_stream": -2, "_side_stream": -1}.get(attr, 0)
+        if os.environ.get("XCHG_STREAM_PRIORITIES", "1") == "0":
+            prio = 0
+        s = torch.cuda.Stream(device=ex.rt.device, priority=prio)
         setattr(ex, attr, s)
     return s

@@ -59,7 +59,7 @@ class ShuffleTaskSpec(ExchangeTaskSpec):
             # does (a list of R table handles, :97-99) -- so reducer j receives the
             # same slice sizes as under the reference
             np.random.RandomState(seed_i).shuffle(slices)
-        num_rows = sum(s.num_rows for s in slices)
+        num_rows = sum(B200ArrowBlockAccessor.for_block(s).num_rows() for s in slices)
         assert num_rows == acc.num_rows(), (num_rows, acc.num_rows())
         return slices + [acc.get_metadata(exec_stats=stats.build())]
 
@@ -79,4 +79,8 @@ class ShuffleTaskSpec(ExchangeTaskSpec):
             new_block = acc.random_shuffle(random_seed if random_seed is not None else None)
             acc = B200ArrowBlockAccessor.for_block(new_block)
         meta = BlockMetadata(acc.num_rows(), acc.size_bytes(), acc.schema(), None, stats.build())
+        from ..block_accessor import want_pandas_output
+
+        if want_pandas_output(mapper_outputs):  # DataFrame blocks in, a DataFrame out
+            new_block = B200ArrowBlockAccessor.for_block(new_block).to_arrow().to_pandas()
         return new_block, meta

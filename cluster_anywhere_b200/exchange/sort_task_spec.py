@@ -68,8 +68,11 @@ class SortTaskSpec(ExchangeTaskSpec):
     def reduce(sort_key: SortKey, batch_format: str, *mapper_outputs,
                partial_reduce: bool = False) -> Tuple[pa.Table, BlockMetadata]:
         """sort_task_spec.py:140-152: merge one partition from every mapper."""
+        from ..block_accessor import B200PandasBlockAccessor, want_pandas_output
+
+        cls = B200PandasBlockAccessor if want_pandas_output(mapper_outputs, batch_format) else B200ArrowBlockAccessor
         blocks = [B200ArrowBlockAccessor.for_block(b).to_arrow() for b in mapper_outputs]
-        return B200ArrowBlockAccessor.merge_sorted_blocks(blocks, sort_key)
+        return cls.merge_sorted_blocks(blocks, sort_key)
 
     @staticmethod
     def boundaries_from_samples(samples: List[tuple], sort_key: SortKey, num_reducers: int) -> list:

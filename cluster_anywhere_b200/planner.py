@@ -287,7 +287,9 @@ class Sort(AbstractAllToAll):
 
 class Aggregate(AbstractAllToAll):
     def __init__(self, input_op: LogicalOperator, key: Optional[str], aggs: list,
-                 batch_format: Optional[str] = "default"):
+                 num_partitions: Optional[int] = None, batch_format: Optional[str] = "default"):
+        # num_partitions is carried like the reference carries it (logical/operators/
+        # all_to_all_operator.py:140-165); its planner does not read it either
         from .exchange.sort_task_spec import SortTaskSpec
 
         super().__init__("Aggregate", input_op,
@@ -295,6 +297,7 @@ class Aggregate(AbstractAllToAll):
                          + _exchange_bar_names())
         self._key = key
         self._aggs = aggs
+        self._num_partitions = num_partitions
         self._batch_format = batch_format
 
 

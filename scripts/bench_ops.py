@@ -71,9 +71,9 @@ def range_sort(args, rt, ex, lib, peak):
         sk = SortKey("id", descending=True)
         ms, ks = timed(lambda i: ex.sort(ds, sk, seed=i), args.steps, args.warmup, lib)
         gbs = 2 * n * 8 / ms / 1e6
-        print(json.dumps({"op": "sort(range)", "workload": f"range({n}).sort('id', descending=True), {blocks} blocks, "
-                          f"{name}: BASELINE configs[0]", "ms_per_step": ms, "rows_per_s": n / ms * 1e3,
-                          "gb_per_s_algorithmic": gbs, "frac_of_measured_hbm": gbs / peak, "kernels": ks}), flush=True)
+        yield {"op": "sort(range)", "workload": f"range({n}).sort('id', descending=True), {blocks} blocks, "
+               f"{name}: BASELINE configs[0]", "ms_per_step": ms, "rows_per_s": n / ms * 1e3,
+               "gb_per_s_algorithmic": gbs, "frac_of_measured_hbm": gbs / peak, "kernels": ks}
 
 
 def string_sort(args, rt, ex, lib, peak):
@@ -116,51 +116,24 @@ def string_sort(args, rt, ex, lib, peak):
     kbytes = int(keycol.data.numel())
     ms, ks = timed(lambda i: ex.sort(ds, sk, seed=i), args.steps, args.warmup, lib)
     gbs = 2 * (kbytes + pbytes + 16 * (n + 1)) / ms / 1e6
-    print(json.dumps({"op": "sort(string key)", "workload": f"{n} rows, string key Zipf(1.2) over {V} distinct strings of "
-                      f"8-31 bytes ({kbytes / 1e9:.2f} GB), binary payload 16-256 bytes ({pbytes / 1e9:.2f} GB), {blocks} "
-                      "blocks: BASELINE configs[4] (500 M rows, 10 M distinct) at a sub-scale that fits one run's time",
-                      "ms_per_step": ms, "rows_per_s": n / ms * 1e3, "gb_per_s_algorithmic": gbs,
-                      "frac_of_measured_hbm": gbs / peak, "kernels": ks}), flush=True)
+    res = {"op": "sort(string key)", "workload": f"{n} rows, string key Zipf(1.2) over {V} distinct strings of "
+           f"8-31 bytes ({kbytes / 1e9:.2f} GB), binary payload 16-256 bytes ({pbytes / 1e9:.2f} GB), {blocks} "
+           "blocks: BASELINE configs[4] (500 M rows, 10 M distinct) at a sub-scale that fits one run's time",
+           "ms_per_step": ms, "rows_per_s": n / ms * 1e3, "gb_per_s_algorithmic": gbs,
+           "frac_of_measured_hbm": gbs / peak, "kernels": ks}
     del ds, table, keycol, paycol, pdata, poff, vocab
     torch.cuda.empty_cache()
+    return res
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--shuffle-rows", type=int, default=25_000_000)
-    ap.add_argument("--agg-rows", type=int, default=250_000_000)
-    ap.add_argument("--agg-groups", type=int, default=10_000_000)
-    ap.add_argument("--string-rows", type=int, default=40_000_000)
-    ap.add_argument("--string-vocab", type=int, default=800_000)
-    ap.add_argument("--only", default="", help="comma list of ops to run: shuffle,aggregate,strings")
-    args = ap.parse_args()
+def shuffle_op(args, rt, ex, lib, peak):
+    """configs[2] shard: random_shuffle(seed=42) of 1 KiB tensor rows."""
     import pyarrow as pa
     import torch
 
-    import __graft_entry__ as ge
-
-    ge.build()
-    from cluster_anywhere_b200 import Count, Mean, Sum, _cabi
     from cluster_anywhere_b200 import device as dev
-    from cluster_anywhere_b200.exchange import DeviceDataset, DeviceExchange
+    from cluster_anywhere_b200.exchange import DeviceDataset
 
-    lib = _cabi.load()
-    rt = dev.Runtime()
-    ex = DeviceExchange(rt)
-    peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(
-        os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
-
-    only = set(x for x in args.only.split(",") if x)
-    if not only or "c1" in only:
-        range_sort(args, rt, ex, lib, peak)
-    if not only or "strings" in only:
-        string_sort(args, rt, ex, lib, peak)
-    if only and "shuffle" not in only and "aggregate" not in only:
-        return
-
-    # ---- configs[2] shard: random_shuffle(seed=42) of 1 KiB tensor rows ----
     n, w = args.shuffle_rows, 1024
     data = torch.empty(n * w + 64, dtype=torch.uint8, device=rt.device)[: n * w]
     data.view(torch.int64)[:] = torch.arange(n * w // 8, device=rt.device, dtype=torch.int64)  # row-id derived
@@ -171,14 +144,24 @@ def main():
     ds = DeviceDataset(table, [(i * n // blocks, (i + 1) * n // blocks) for i in range(blocks)])
     ms, ks = timed(lambda i: ex.random_shuffle(ds, 42), args.steps, args.warmup, lib)
     gbs = 2 * n * w / ms / 1e6
-    print(json.dumps({"op": "random_shuffle", "workload": f"{n} rows x 1 KiB tensor rows (25.6 GB), seed 42, "
-                      f"{blocks} blocks: the per-GPU shard of BASELINE configs[2] (200 M rows at 8 GPUs)",
-                      "ms_per_step": ms, "rows_per_s": n / ms * 1e3, "gb_per_s_algorithmic": gbs,
-                      "frac_of_measured_hbm": gbs / peak, "kernels": ks}), flush=True)
+    res = {"op": "random_shuffle", "workload": f"{n} rows x 1 KiB tensor rows ({n * w / 1e9:.1f} GB), seed 42, "
+           f"{blocks} blocks: the per-GPU shard of BASELINE configs[2] (200 M rows at 8 GPUs)",
+           "ms_per_step": ms, "rows_per_s": n / ms * 1e3, "gb_per_s_algorithmic": gbs,
+           "frac_of_measured_hbm": gbs / peak, "kernels": ks}
     del ds, table, col, data
     torch.cuda.empty_cache()
+    return res
 
-    # ---- configs[3] shard: groupby(int32 key).aggregate(Sum, Mean, Count) over float32 rows ----
+
+def aggregate_op(args, rt, ex, lib, peak):
+    """configs[3] shard: groupby(int32 key).aggregate(Sum, Mean, Count) over float32 rows."""
+    import pyarrow as pa
+    import torch
+
+    from cluster_anywhere_b200 import Count, Mean, Sum
+    from cluster_anywhere_b200 import device as dev
+    from cluster_anywhere_b200.exchange import DeviceDataset
+
     n, g = args.agg_rows, args.agg_groups
     gen = torch.Generator(device=rt.device)
     gen.manual_seed(4)
@@ -194,10 +177,75 @@ def main():
     out = ex.aggregate(ds, "k", aggs)
     groups = out.num_rows
     gbs = (8 * n + 32 * groups) / ms / 1e6
-    print(json.dumps({"op": "groupby.aggregate", "workload": f"{n} rows (int32 key, float32 value), {groups} groups, "
-                      f"Sum/Mean/Count, {blocks} blocks: the per-GPU shard of BASELINE configs[3] (2 B rows at 8 GPUs)",
-                      "ms_per_step": ms, "rows_per_s": n / ms * 1e3, "gb_per_s_algorithmic": gbs,
-                      "frac_of_measured_hbm": gbs / peak, "kernels": ks}), flush=True)
+    res = {"op": "groupby.aggregate", "workload": f"{n} rows (int32 key, float32 value), {groups} groups, "
+           f"Sum/Mean/Count, {blocks} blocks: the per-GPU shard of BASELINE configs[3] (2 B rows at 8 GPUs)",
+           "ms_per_step": ms, "rows_per_s": n / ms * 1e3, "gb_per_s_algorithmic": gbs,
+           "frac_of_measured_hbm": gbs / peak, "kernels": ks}
+    del ds, table, kc, vc, k, v, out
+    torch.cuda.empty_cache()
+    return res
+
+
+class OpArgs:
+    """Default sizes of the secondary measurements (bench.py's ``ops`` key uses these)."""
+
+    def __init__(self, steps=5, warmup=3):
+        self.steps, self.warmup = steps, warmup
+        self.shuffle_rows = 25_000_000
+        self.agg_rows = 250_000_000
+        self.agg_groups = 10_000_000
+        self.string_rows = 40_000_000
+        self.string_vocab = 800_000
+
+
+def run_ops(rt, ex, lib, peak, steps=5, warmup=3, only=()):
+    """The secondary operators on one GPU -> list of result dicts."""
+    args = OpArgs(steps, warmup)
+    out = []
+    if not only or "shuffle" in only:
+        out.append(shuffle_op(args, rt, ex, lib, peak))
+    if not only or "aggregate" in only:
+        out.append(aggregate_op(args, rt, ex, lib, peak))
+    if not only or "strings" in only:
+        out.append(string_sort(args, rt, ex, lib, peak))
+    if not only or "c1" in only:
+        out.extend(range_sort(args, rt, ex, lib, peak))
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--shuffle-rows", type=int, default=25_000_000)
+    ap.add_argument("--agg-rows", type=int, default=250_000_000)
+    ap.add_argument("--agg-groups", type=int, default=10_000_000)
+    ap.add_argument("--string-rows", type=int, default=40_000_000)
+    ap.add_argument("--string-vocab", type=int, default=800_000)
+    ap.add_argument("--only", default="", help="comma list of ops to run: c1,shuffle,aggregate,strings")
+    args = ap.parse_args()
+    import __graft_entry__ as ge
+
+    ge.build()
+    from cluster_anywhere_b200 import _cabi
+    from cluster_anywhere_b200 import device as dev
+    from cluster_anywhere_b200.exchange import DeviceExchange
+
+    lib = _cabi.load()
+    rt = dev.Runtime()
+    ex = DeviceExchange(rt)
+    peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(
+        os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+    only = set(x for x in args.only.split(",") if x)
+    if not only or "c1" in only:
+        for r in range_sort(args, rt, ex, lib, peak):
+            print(json.dumps(r), flush=True)
+    if not only or "strings" in only:
+        print(json.dumps(string_sort(args, rt, ex, lib, peak)), flush=True)
+    if not only or "shuffle" in only:
+        print(json.dumps(shuffle_op(args, rt, ex, lib, peak)), flush=True)
+    if not only or "aggregate" in only:
+        print(json.dumps(aggregate_op(args, rt, ex, lib, peak)), flush=True)
 
 
 if __name__ == "__main__":

@@ -88,41 +88,73 @@ def main():
     def gather(in_ptr, out_ptr):
         _cabi.check(lib.xchg_gather_rows(vp(in_ptr), W, vp(perm.data_ptr()), n, vp(out_ptr), stream))
 
-    for cap in (0, 1, 2, 3, 6):
-        lib.xchg_set_gather_ctas_per_sm(cap)
-        timed(f"push_gather cap={cap}", lambda: gather(table.data_ptr(), ptrs[peer] + land_off), nbytes)
-        timed(f"pull_gather cap={cap}", lambda: gather(ptrs[peer], local_out.data_ptr()), nbytes)
-    lib.xchg_set_gather_ctas_per_sm(0)
-    timed("local_gather", lambda: gather(table.data_ptr(), local_out.data_ptr()), nbytes)
+    if os.environ.get("PROBE_PAIR", "1" if world <= 2 else "0") == "1":
+        for cap in (0, 1, 2, 3, 6):
+            lib.xchg_set_gather_ctas_per_sm(cap)
+            timed(f"push_gather cap={cap}", lambda: gather(table.data_ptr(), ptrs[peer] + land_off), nbytes)
+            timed(f"pull_gather cap={cap}", lambda: gather(ptrs[peer], local_out.data_ptr()), nbytes)
+        lib.xchg_set_gather_ctas_per_sm(0)
+        timed("local_gather", lambda: gather(table.data_ptr(), local_out.data_ptr()), nbytes)
 
-    def copy_seg(dst):
-        src = (ctypes.c_void_p * 1)(table.data_ptr())
-        d = (ctypes.c_void_p * 1)(dst)
-        nb = (ctypes.c_uint64 * 1)(nbytes)
-        _cabi.check(lib.xchg_copy_segments(1, src, d, nb, stream))
+        def copy_seg(dst):
+            src = (ctypes.c_void_p * 1)(table.data_ptr())
+            d = (ctypes.c_void_p * 1)(dst)
+            nb = (ctypes.c_uint64 * 1)(nbytes)
+            _cabi.check(lib.xchg_copy_segments(1, src, d, nb, stream))
 
-    timed("push_copy", lambda: copy_seg(ptrs[peer] + land_off), nbytes)
-    timed("local_copy", lambda: copy_seg(local_out.data_ptr()), nbytes)
-    # ctypes' getenv sees the C environment, not os.environ's copy: set it there
-    libc = ctypes.CDLL(None)
-    libc.setenv(b"XCHG_COPY_BULK", b"1", 1)
-    timed("push_copy_tma", lambda: copy_seg(ptrs[peer] + land_off), nbytes)
-    timed("local_copy_tma", lambda: copy_seg(local_out.data_ptr()), nbytes)
-    libc.setenv(b"XCHG_COPY_BULK", b"0", 1)
-    peer_view = hdl.get_buffer(peer, (nbytes,), torch.uint8, land_off)
-    timed("push_ce", lambda: peer_view.copy_(table, non_blocking=True), nbytes)
+        timed("push_copy", lambda: copy_seg(ptrs[peer] + land_off), nbytes)
+        timed("local_copy", lambda: copy_seg(local_out.data_ptr()), nbytes)
+        # ctypes' getenv sees the C environment, not os.environ's copy: set it there
+        libc = ctypes.CDLL(None)
+        libc.setenv(b"XCHG_COPY_BULK", b"1", 1)
+        timed("push_copy_tma", lambda: copy_seg(ptrs[peer] + land_off), nbytes)
+        timed("local_copy_tma", lambda: copy_seg(local_out.data_ptr()), nbytes)
+        libc.setenv(b"XCHG_COPY_BULK", b"0", 1)
+        peer_view = hdl.get_buffer(peer, (nbytes,), torch.uint8, land_off)
+        timed("push_ce", lambda: peer_view.copy_(table, non_blocking=True), nbytes)
 
-    # mixed: half local, half remote in one multi-destination launch
-    half = n // 2
-    row0 = (ctypes.c_uint64 * 2)(0, half)
-    rows = (ctypes.c_uint64 * 2)(half, n - half)
-    outs = (ctypes.c_void_p * 2)(ptrs[rank] + land_off, ptrs[peer] + land_off + half * W)
-    for cap in (0, 1, 2, 3):
-        lib.xchg_set_gather_ctas_per_sm(cap)
-        timed(f"mixed_multi cap={cap} (remote half counted)",
-              lambda: _cabi.check(lib.xchg_gather_rows_multi(vp(table.data_ptr()), W, vp(perm.data_ptr()), 2, row0, rows,
-                                                             outs, stream)), (n - half) * W)
-    lib.xchg_set_gather_ctas_per_sm(0)
+        # mixed: half local, half remote in one multi-destination launch
+        half = n // 2
+        row0 = (ctypes.c_uint64 * 2)(0, half)
+        rows = (ctypes.c_uint64 * 2)(half, n - half)
+        outs = (ctypes.c_void_p * 2)(ptrs[rank] + land_off, ptrs[peer] + land_off + half * W)
+        for cap in (0, 1, 2, 3):
+            lib.xchg_set_gather_ctas_per_sm(cap)
+            timed(f"mixed_multi cap={cap} (remote half counted)",
+                  lambda: _cabi.check(lib.xchg_gather_rows_multi(vp(table.data_ptr()), W, vp(perm.data_ptr()), 2, row0, rows,
+                                                                 outs, stream)), (n - half) * W)
+        lib.xchg_set_gather_ctas_per_sm(0)
+
+    # all-to-all: every rank stores an equal share of its rows into EVERY rank (itself
+    # included) at the same time -- the exchange's real traffic pattern at world > 2
+    if world > 2 or os.environ.get("PROBE_A2A", "0") == "1":
+        share = n // world
+        remote_bytes = share * W * (world - 1)
+        order = [(rank + 1 + i) % world for i in range(world)]
+        row0 = (ctypes.c_uint64 * world)(*[i * share for i in range(world)])
+        rows = (ctypes.c_uint64 * world)(*[share] * world)
+        outs = (ctypes.c_void_p * world)(*[ptrs[d] + land_off + rank * share * W for d in order])
+        for cap in (0, 1, 2, 3, 6):
+            lib.xchg_set_gather_ctas_per_sm(cap)
+            timed(f"a2a_gather_multi cap={cap} (remote bytes counted)",
+                  lambda: _cabi.check(lib.xchg_gather_rows_multi(vp(table.data_ptr()), W, vp(perm.data_ptr()), world,
+                                                                 row0, rows, outs, stream)), remote_bytes)
+        lib.xchg_set_gather_ctas_per_sm(0)
+
+        def one_by_one():
+            for i, d in enumerate(order):
+                _cabi.check(lib.xchg_gather_rows(vp(table.data_ptr()), W, vp(perm.data_ptr() + 4 * i * share), share,
+                                                 vp(ptrs[d] + land_off + rank * share * W), stream))
+
+        timed("a2a_gather one launch per destination, rotated order (remote bytes counted)", one_by_one, remote_bytes)
+        srcs = (ctypes.c_void_p * world)(*[table.data_ptr() + i * share * W for i in range(world)])
+        nbs = (ctypes.c_uint64 * world)(*[share * W] * world)
+        timed("a2a_copy (contiguous, interleaved segments; remote bytes counted)",
+              lambda: _cabi.check(lib.xchg_copy_segments(world, srcs, outs, nbs, stream)), remote_bytes)
+        send = table[: share * W * world]
+        recv = local_out[: share * W * world]
+        timed("a2a_nccl all_to_all_single (remote bytes counted)",
+              lambda: dist.all_to_all_single(recv, send), remote_bytes)
     dist.barrier()
     dist.destroy_process_group()
 

@@ -124,8 +124,6 @@ def main():
     aggs = [Count(), Sum("f"), Mean("f"), Min("k"), Max("f"), Std("f", ddof=1)]
     exp = O.groupby_aggregate(all_blocks, "k", [("count",), ("sum", "f"), ("mean", "f"), ("min", "k"),
                                                  ("max", "f"), ("std", "f", 1)])
-    i = exp.schema.get_field_index("min(k)")
-    exp = exp.set_column(i, "min(k)", exp["min(k)"].cast(pa.int64()))
     for bounds in (None, [(-20,), (0,), (31,)]):
         out = ex.aggregate_blocks(mine, "k", aggs, boundaries=bounds, seed=1)
         outs = [None] * w
