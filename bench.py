@@ -507,7 +507,9 @@ def run_b200(args):
     total_rows = n * world
     verified = verify_output(out, input_fingerprint(keys, data, n), world)
     del out
-    if not (verified["order"] and verified["rank_boundaries"] and verified["checksum"]
+    if args.no_verify:
+        verified["skipped"] = "--no-verify (a timing experiment; this line is not a bench value)"
+    elif not (verified["order"] and verified["rank_boundaries"] and verified["checksum"]
             and verified["payload_keys"] and verified["rows"] == total_rows):
         if rank == 0:
             print(json.dumps({"metric": METRIC, "error": "output verification failed", "verified": verified,
@@ -713,6 +715,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-verify", action="store_true",
+                    help="timing experiments with XCHG_DEBUG_SKIP: do not abort on a wrong output")
     ap.add_argument("--no-ops", action="store_true", help="skip the secondary operators' lines (ops key)")
     ap.add_argument("--trace", action="store_true",
                     help="diagnostics: synchronise after every phase of the distributed sort and print "

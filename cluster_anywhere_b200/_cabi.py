@@ -34,6 +34,7 @@ _SIGNATURES = {
     "xchg_denormalize_keys": (c_int, [_P, c_int, c_int, c_uint64, _P, _P]),
     "xchg_set_l2_fetch_granularity": (c_int, [c_int]),
     "xchg_set_gather_ctas_per_sm": (c_int, [c_int]),
+    "xchg_set_gather_stage_kb": (c_int, [c_int]),
     "xchg_set_sort_algorithm": (c_int, [c_int]),
     "xchg_partition_bounds": (c_int, [ctypes.POINTER(c_void_p), _P, _P, _P, c_int, c_uint64, _P, _P, _P, c_int, c_int, _P, _P]),
     "xchg_assign_partitions": (c_int, [ctypes.POINTER(c_void_p), _P, c_int, c_uint64, _P, _P, _P, c_int, c_int, _P, _P, _P]),
@@ -82,6 +83,11 @@ _SIGNATURES = {
     "xchg_offsets_rebase": (c_int, [_P, c_uint64, c_int64, _P, _P]),
     "xchg_string_lengths": (c_int, [_P, c_uint64, _P, _P, _P]),
     "xchg_string_chunk_keys": (c_int, [_P, _P, c_uint64, c_uint32, _P, _P]),
+    "xchg_string_tie_flags": (c_int, [_P, _P, _P, _P, _P, _P, c_uint64, c_uint64, _P, _P, _P]),
+    "xchg_string_active_rows": (c_int, [_P, _P, _P, c_uint64, c_uint64, _P, _P, _P]),
+    "xchg_scatter_flagged": (c_int, [_P, _P, c_uint64, _P, _P]),
+    "xchg_string_chunk_keys_rows": (c_int, [_P, _P, _P, c_uint64, c_uint32, _P, _P]),
+    "xchg_scatter_u32": (c_int, [_P, _P, c_uint64, _P, _P]),
     "xchg_partition_bounds_bytes": (c_int, [_P, _P, _P, c_uint64, _P, _P, _P, c_int, c_int, _P, _P]),
     "xchg_assign_partitions_bytes": (c_int, [_P, _P, _P, c_uint64, _P, _P, _P, c_int, c_int, _P, _P, _P]),
     "xchg_gather_fixed": (c_int, [_P, c_uint32, _P, c_uint64, _P, _P]),

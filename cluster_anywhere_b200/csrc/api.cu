@@ -143,6 +143,17 @@ std::atomic<int> g_gather_ctas_per_sm{0};
 }
 int xchg_gather_ctas_per_sm() { return g_gather_ctas_per_sm.load(std::memory_order_relaxed); }
 
+namespace {
+std::atomic<int> g_gather_stage_kb{0};
+}
+int xchg_gather_stage_kb() { return g_gather_stage_kb.load(std::memory_order_relaxed); }
+
+extern "C" int xchg_set_gather_stage_kb(int kb) {
+  XCHG_REQUIRE(kb == 0 || (kb >= 4 && kb <= 56), "kb must be 0 or in [4, 56]");
+  g_gather_stage_kb.store(kb);
+  return XCHG_OK;
+}
+
 extern "C" int xchg_set_gather_ctas_per_sm(int ctas_per_sm) {
   XCHG_REQUIRE(ctas_per_sm >= 0 && ctas_per_sm <= 32, "ctas_per_sm must be in [0, 32]");
   g_gather_ctas_per_sm.store(ctas_per_sm);

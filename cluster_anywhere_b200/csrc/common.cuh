@@ -51,6 +51,9 @@ int xchg_sm_count();
 // CTAs per SM the gather kernels may use (0 = each kernel's own default); see
 // xchg_set_gather_ctas_per_sm.
 int xchg_gather_ctas_per_sm();
+// Staging bytes per CTA (KB) of the uniform-row gather for the launches that follow (0 = the
+// default); see xchg_set_gather_stage_kb.
+int xchg_gather_stage_kb();
 
 __device__ __forceinline__ bool bit_is_set(const uint8_t* bm, int64_t i) {
   return (bm[i >> 3] >> (i & 7)) & 1;

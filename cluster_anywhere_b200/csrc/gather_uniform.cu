@@ -29,19 +29,25 @@ constexpr int GU_THREADS = 256;
 constexpr int GU_STAGE_DEFAULT_KB = 56;
 constexpr int GU_STAGE_MAX = 56 * 1024;
 constexpr int GU_MAX_ROWS = 1024;
-// int64 src[GU_MAX_ROWS] | uint32 a0[GU_MAX_ROWS] | stage | pad
-constexpr size_t GU_META = (size_t)GU_MAX_ROWS * (8 + 4);
-constexpr size_t gu_smem(int stage_bytes) { return GU_META + (size_t)stage_bytes + 32; }
+// int64 src[rows_per_tile] | uint32 a0[rows_per_tile + 1] | stage | pad: the row tables are sized
+// by the tile's rows, so a small stage makes a small CTA (the peer-store gathers run with a
+// few KB per CTA beside kernels that need the SM's shared memory)
+__host__ __device__ constexpr size_t gu_meta(uint32_t rows_per_tile) { return (((size_t)rows_per_tile * 12 + 4) + 15) & ~(size_t)15; }
+constexpr size_t gu_smem(int stage_bytes, uint32_t rows_per_tile) {
+  return gu_meta(rows_per_tile) + (size_t)stage_bytes + 32;
+}
 
 // Bytes of row staging per CTA.  Smaller stages let more CTAs share an SM, so that more
 // of them are in their (latency-bound) load phase while others write out: XCHG_GATHER_STAGE_KB
 // (16..56) overrides the default.
 static int gu_stage_bytes() {
+  const int over = xchg_gather_stage_kb();  // per-launch override (xchg_set_gather_stage_kb)
+  if (over >= 4 && over <= 56) return over * 1024;
   static int v = 0;
   if (v == 0) {
     const char* e = getenv("XCHG_GATHER_STAGE_KB");
     int kb = e ? atoi(e) : 0;
-    if (kb < 16 || kb > 56) kb = GU_STAGE_DEFAULT_KB;
+    if (kb < 4 || kb > 56) kb = GU_STAGE_DEFAULT_KB;
     v = kb * 1024;
   }
   return v;
@@ -86,8 +92,8 @@ k_gather_rows_uniform(const uint8_t* __restrict__ in, uint32_t w, const uint32_t
                       uint64_t max_tiles) {
   extern __shared__ __align__(16) uint8_t smem[];
   int64_t* m_src = reinterpret_cast<int64_t*>(smem);
-  uint32_t* m_a0 = reinterpret_cast<uint32_t*>(m_src + GU_MAX_ROWS);
-  uint8_t* stage = smem + GU_META;
+  uint32_t* m_a0 = reinterpret_cast<uint32_t*>(m_src + rows_per_tile);
+  uint8_t* stage = smem + gu_meta(rows_per_tile);
   const uint32_t stage_s = (uint32_t)__cvta_generic_to_shared(stage);
   const int tid = threadIdx.x;
   const uint32_t cpr = slot >> 4;  // 16-byte chunks per slot
@@ -228,6 +234,64 @@ k_gather_rows_uniform(const uint8_t* __restrict__ in, uint32_t w, const uint32_t
   }
 }
 
+// ---- TMA variant for rows whose width and bases are multiples of 16 bytes ----
+// (1 KiB tensor rows of random_shuffle).  One warp per CTA, no thread touches the data:
+// the lanes issue one cp.async.bulk per row (global -> shared, completion counted in bytes
+// on an mbarrier), lane 0 then stores the tile -- contiguous in the output -- with ONE bulk
+// store; two stages, so a tile's store drains while the next tile's rows arrive.
+constexpr int GB_STAGES = 2;
+constexpr uint32_t GB_STAGE_BYTES = 40 * 1024;
+
+__global__ void __launch_bounds__(32)
+k_gather_rows_bulk(const uint8_t* __restrict__ in, uint32_t w, const uint32_t* __restrict__ idx, uint64_t n_out,
+                   uint8_t* __restrict__ out, uint32_t rows_per_tile) {
+  extern __shared__ __align__(128) uint8_t gb_smem[];
+  __shared__ __align__(8) uint64_t mbar_mem[GB_STAGES];
+  const uint32_t stage_s = (uint32_t)__cvta_generic_to_shared(gb_smem);
+  const uint32_t mbar_s = (uint32_t)__cvta_generic_to_shared(mbar_mem);
+  const int lane = threadIdx.x;
+  if (lane == 0) {
+    for (int i = 0; i < GB_STAGES; ++i)
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar_s + 8 * i) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+  const uint64_t ntiles = (n_out + rows_per_tile - 1) / rows_per_tile;
+  uint32_t it = 0;
+  for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+    const uint64_t r0 = tile * rows_per_tile;
+    const uint32_t T = (uint32_t)min((uint64_t)rows_per_tile, n_out - r0);
+    const uint32_t st = it % GB_STAGES;
+    const uint32_t sbase = stage_s + st * GB_STAGE_BYTES;
+    const uint32_t mb = mbar_s + 8 * st;
+    if (lane == 0) {
+      // the bulk store issued from this stage two tiles ago must have read its bytes
+      asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(GB_STAGES - 1) : "memory");
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mb), "r"(T * w) : "memory");
+    }
+    __syncwarp();
+    for (uint32_t j = lane; j < T; j += 32) {
+      const uint8_t* g = in + (uint64_t)idx[r0 + j] * w;
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(sbase + j * w), "l"(g), "r"(w), "r"(mb) : "memory");
+    }
+    if (lane == 0) {
+      const uint32_t parity = (it / GB_STAGES) & 1u;
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t"
+          "WAITB_%=:\n\t"
+          "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+          "@!p bra WAITB_%=;\n\t}"
+          ::"r"(mb), "r"(parity) : "memory");
+      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                   ::"l"(out + r0 * w), "r"(sbase), "r"(T * w) : "memory");
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    }
+    __syncwarp();
+  }
+  if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
 }  // namespace
 
 static GatherSegs no_segs() {
@@ -240,26 +304,40 @@ static int gather_uniform_launch(const uint8_t* in, uint32_t w, const uint32_t* 
                                  uint8_t* out, const GatherSegs* multi, cudaStream_t s) {
   XCHG_ONCE_PER_DEVICE({
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<false, false>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gu_smem(GU_STAGE_MAX)));
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gu_smem(GU_STAGE_MAX, GU_MAX_ROWS)));
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<true, false>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gu_smem(GU_STAGE_MAX)));
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gu_smem(GU_STAGE_MAX, GU_MAX_ROWS)));
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<false, true>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gu_smem(GU_STAGE_MAX)));
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gu_smem(GU_STAGE_MAX, GU_MAX_ROWS)));
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_uniform<true, true>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gu_smem(GU_STAGE_MAX)));
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gu_smem(GU_STAGE_MAX, GU_MAX_ROWS)));
   });
   uintptr_t align_bits = (uintptr_t)in | (uintptr_t)out;
   if (multi)
     for (int d = 0; d < multi->nseg; ++d) align_bits |= (uintptr_t)multi->out[d];
   const bool vec16 = (w % 16 == 0) && (align_bits % 16 == 0);
+  // XCHG_GATHER_BULK=1: aligned rows through the TMA unit (A/B switch, read per call)
+  const char* bulk_env = getenv("XCHG_GATHER_BULK");
+  if (bulk_env && atoi(bulk_env) == 1 && vec16 && !multi && w <= GB_STAGE_BYTES) {
+    constexpr int smem = GB_STAGES * GB_STAGE_BYTES;
+    XCHG_ONCE_PER_DEVICE(XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows_bulk,
+                                                            cudaFuncAttributeMaxDynamicSharedMemorySize, smem)));
+    const uint32_t rpt = GB_STAGE_BYTES / w;
+    const uint64_t ntiles = (n_out + rpt - 1) / rpt;
+    const int cap = xchg_gather_ctas_per_sm();
+    const int grid = (int)std::min<uint64_t>(ntiles, (uint64_t)xchg_sm_count() * (cap ? cap : 2 * 8));
+    XCHG_LAUNCH(XK_GATHER_ROWS, s, k_gather_rows_bulk<<<grid, 32, smem, s>>>(in, w, idx, n_out, out, rpt));
+    XCHG_LAUNCH_CHECK();
+    return XCHG_OK;
+  }
   const uint32_t slot = vec16 ? w : ((w + 15u + 15u) & ~15u);
   int stage_bytes = gu_stage_bytes();
   if (slot > (uint32_t)stage_bytes) stage_bytes = GU_STAGE_MAX;  // wide rows: the largest stage
-  const size_t smem_bytes = gu_smem(stage_bytes);
-  // CTAs of this shape an SM holds (227 KB of shared memory, 1 KB reserved per CTA)
-  const int resident = std::max(1, (int)((227 * 1024) / (smem_bytes + 1024)));
   const uint32_t rpt = std::min<uint32_t>(GU_MAX_ROWS, (uint32_t)stage_bytes / slot);
   if (rpt == 0) return 1;  // row wider than the stage: caller takes the generic path
+  const size_t smem_bytes = gu_smem(stage_bytes, rpt);
+  // CTAs of this shape an SM holds (227 KB of shared memory, 1 KB reserved per CTA)
+  const int resident = std::max(1, std::min(8, (int)((227 * 1024) / (smem_bytes + 1024))));
   const uint32_t cpr = slot >> 4;
   // exact for every dividend below 2^32 / divisor, which bounds all uses (tile bytes, chunks)
   const uint32_t magic_w = w == 1 ? 0u : (uint32_t)((0x100000000ull + w - 1) / w);

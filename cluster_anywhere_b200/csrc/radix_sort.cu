@@ -149,6 +149,9 @@ k_key_scan(const T* __restrict__ keys, uint32_t n, int desc, KeyShifts ks, int w
   const uint32_t stride = gridDim.x * blockDim.x;
   const uint32_t n_up = (n + 31u) & ~31u;
   uint64_t acc_or = 0, acc_and = ~0ull;
+  // one shared-memory atomic per key and place; a warp whose 32 keys share the digit (sorted
+  // or narrow inputs) adds once instead -- that test is only made while it keeps succeeding
+  bool try_uniform = true;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_up; i += stride) {
     const bool active = i < n;
     uint64_t key = 0;
@@ -157,17 +160,24 @@ k_key_scan(const T* __restrict__ keys, uint32_t n, int desc, KeyShifts ks, int w
       acc_or |= key;
       acc_and &= key;
     }
-    const unsigned act = __ballot_sync(0xffffffffu, active);
-    const int first = __ffs(act) - 1;
-    for (int p = 0; p < ks.n; ++p) {
-      const uint32_t d = (uint32_t)(key >> ks.shift[p]) & 255u;
-      const uint32_t d0 = __shfl_sync(0xffffffffu, d, first);
-      const bool uni = __all_sync(0xffffffffu, !active || d == d0);
-      if (uni) {
-        if ((int)lane == first) atomicAdd(&sh[p * BINS + d0], (uint32_t)__popc(act));
-      } else if (active) {
-        atomicAdd(&sh[p * BINS + d], 1u);
+    if (try_uniform) {
+      const unsigned act = __ballot_sync(0xffffffffu, active);
+      const int first = __ffs(act) - 1;
+      bool all_uni = true;
+      for (int p = 0; p < ks.n; ++p) {
+        const uint32_t d = (uint32_t)(key >> ks.shift[p]) & 255u;
+        const uint32_t d0 = __shfl_sync(0xffffffffu, d, first);
+        const bool uni = __all_sync(0xffffffffu, !active || d == d0);
+        if (uni) {
+          if ((int)lane == first) atomicAdd(&sh[p * BINS + d0], (uint32_t)__popc(act));
+        } else {
+          all_uni = false;
+          if (active) atomicAdd(&sh[p * BINS + d], 1u);
+        }
       }
+      try_uniform = all_uni;  // warp-uniform by construction
+    } else if (active) {
+      for (int p = 0; p < ks.n; ++p) atomicAdd(&sh[p * BINS + ((uint32_t)(key >> ks.shift[p]) & 255u)], 1u);
     }
   }
   if (want_orand) {

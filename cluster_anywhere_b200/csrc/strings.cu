@@ -167,6 +167,104 @@ k_assign_partitions_bytes(StrCol col, uint64_t n, const int64_t* __restrict__ bo
   }
 }
 
+// ---- MSD refinement of a string sort (levels after the first 8 bytes) ----
+//
+// After the rows have been sorted by chunk 0 only the rows that TIE there need another look,
+// and of those only the ones whose group holds at least two different strings: a Zipf head
+// of identical keys is final after one comparison with its neighbour.  The kernels below
+// work on a LIST of m rows in their current order (level 0: all rows in sorted order; later:
+// the rows still unresolved).
+
+// gflag[j] = row j starts a new tie group (different previous-level group, different key at
+// this level, or null against non-null); fflag[j] = gflag[j], or the two strings differ
+// somewhere from byte `from_byte` on (lengths included).
+__global__ void __launch_bounds__(ST_THREADS)
+k_string_tie_flags(StrCol col, const uint32_t* __restrict__ rows, const uint64_t* __restrict__ keys,
+                   const uint32_t* __restrict__ gid_prev, uint64_t m, int64_t from_byte,
+                   uint8_t* __restrict__ gflag, uint8_t* __restrict__ fflag) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < m; j += stride) {
+    bool g = j == 0, f = j == 0;
+    if (!g) {
+      const uint32_t a = rows[j - 1], b = rows[j];
+      const bool na = row_is_null(col, a), nb = row_is_null(col, b);
+      g = (gid_prev && gid_prev[j] != gid_prev[j - 1]) || keys[j] != keys[j - 1] || na != nb;
+      f = g;
+      if (!g && !nb) {
+        const int64_t a0 = col.off[a], a1 = col.off[a + 1], b0 = col.off[b], b1 = col.off[b + 1];
+        if (a1 - a0 != b1 - b0) {
+          f = true;
+        } else {
+          for (int64_t q = from_byte; q < a1 - a0; ++q)
+            if (col.data[a0 + q] != col.data[b0 + q]) {
+              f = true;
+              break;
+            }
+        }
+      }
+    }
+    gflag[j] = g ? 1 : 0;
+    fflag[j] = f ? 1 : 0;
+  }
+}
+
+// a group is unresolved when two neighbours inside it differ
+__global__ void __launch_bounds__(ST_THREADS)
+k_mark_unresolved(const uint8_t* __restrict__ gflag, const uint8_t* __restrict__ fflag,
+                  const uint32_t* __restrict__ gid, uint64_t m, uint8_t* __restrict__ unresolved) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < m; j += stride)
+    if (fflag[j] && !gflag[j]) unresolved[gid[j]] = 1;
+}
+
+__global__ void __launch_bounds__(ST_THREADS)
+k_flag_active(const uint8_t* __restrict__ unresolved, const uint32_t* __restrict__ gid, uint64_t m,
+              uint32_t* __restrict__ active) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < m; j += stride)
+    active[j] = unresolved[gid[j]] ? 1u : 0u;
+}
+
+// list[excl[j]] = j for every flagged j (excl = exclusive scan of the flags)
+__global__ void __launch_bounds__(ST_THREADS)
+k_scatter_flagged(const uint32_t* __restrict__ active, const int64_t* __restrict__ excl, uint64_t m,
+                  uint32_t* __restrict__ list) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < m; j += stride)
+    if (active[j]) list[excl[j]] = (uint32_t)j;
+}
+
+// chunk keys (or, chunk == UINT32_MAX, lengths) of the listed rows
+__global__ void __launch_bounds__(ST_THREADS)
+k_string_chunk_keys_rows(const int64_t* __restrict__ off, const uint8_t* __restrict__ data,
+                         const uint32_t* __restrict__ rows, uint64_t m, uint32_t chunk,
+                         uint64_t* __restrict__ out) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < m; j += stride) {
+    const uint32_t r = rows[j];
+    const int64_t b = off[r], e = off[r + 1];
+    uint64_t k = 0;
+    if (chunk == 0xFFFFFFFFu) {
+      k = (uint64_t)(e - b);
+    } else {
+      const int64_t p = b + (int64_t)chunk * 8;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const uint64_t byte = (p + q < e) ? (uint64_t)data[p + q] : 0ull;
+        k = (k << 8) | byte;
+      }
+    }
+    out[j] = k;
+  }
+}
+
+__global__ void __launch_bounds__(ST_THREADS)
+k_scatter_u32(const uint32_t* __restrict__ idx, const uint32_t* __restrict__ vals, uint64_t m,
+              uint32_t* __restrict__ out) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < m; j += stride) out[idx[j]] = vals[j];
+}
+
 }  // namespace
 
 extern "C" int xchg_string_lengths(const int64_t* offsets, uint64_t n, uint32_t* len_out,
@@ -221,6 +319,66 @@ extern "C" int xchg_assign_partitions_bytes(const int64_t* offsets, const uint8_
   XCHG_LAUNCH(XK_PARTITION, s, k_assign_partitions_bytes<<<st_grid(n), ST_THREADS, 0, s>>>(
       c, n, bound_offsets, bound_data, bound_flags, nb, descending, dest_out,
       (unsigned long long*)counts_out));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+extern "C" int xchg_string_tie_flags(const int64_t* offsets, const uint8_t* data, const uint8_t* validity,
+                                     const uint32_t* rows, const uint64_t* keys, const uint32_t* gid_prev,
+                                     uint64_t m, uint64_t from_byte, uint8_t* gflag_out, uint8_t* fflag_out,
+                                     void* stream) {
+  if (m == 0) return XCHG_OK;
+  XCHG_REQUIRE(offsets && rows && keys && gflag_out && fflag_out, "NULL argument");
+  StrCol c{offsets, data, validity};
+  XCHG_LAUNCH(XK_PARTITION, (cudaStream_t)stream,
+              k_string_tie_flags<<<st_grid(m), ST_THREADS, 0, (cudaStream_t)stream>>>(
+                  c, rows, keys, gid_prev, m, (int64_t)from_byte, gflag_out, fflag_out));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+extern "C" int xchg_string_active_rows(const uint8_t* gflag, const uint8_t* fflag, const uint32_t* gid,
+                                       uint64_t m, uint64_t num_groups, uint8_t* unresolved_scratch,
+                                       uint32_t* active_out, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  if (m == 0) return XCHG_OK;
+  XCHG_REQUIRE(gflag && fflag && gid && unresolved_scratch && active_out, "NULL argument");
+  XCHG_CUDA_TRY(cudaMemsetAsync(unresolved_scratch, 0, num_groups, s));
+  XCHG_LAUNCH(XK_PARTITION, s, k_mark_unresolved<<<st_grid(m), ST_THREADS, 0, s>>>(gflag, fflag, gid, m,
+                                                                                unresolved_scratch));
+  XCHG_LAUNCH(XK_PARTITION, s, k_flag_active<<<st_grid(m), ST_THREADS, 0, s>>>(unresolved_scratch, gid, m,
+                                                                            active_out));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+extern "C" int xchg_scatter_flagged(const uint32_t* flags, const int64_t* excl_scan, uint64_t m,
+                                    uint32_t* list_out, void* stream) {
+  if (m == 0) return XCHG_OK;
+  XCHG_REQUIRE(flags && excl_scan && list_out, "NULL argument");
+  XCHG_LAUNCH(XK_MISC, (cudaStream_t)stream,
+              k_scatter_flagged<<<st_grid(m), ST_THREADS, 0, (cudaStream_t)stream>>>(flags, excl_scan, m, list_out));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+extern "C" int xchg_string_chunk_keys_rows(const int64_t* offsets, const uint8_t* data, const uint32_t* rows,
+                                           uint64_t m, uint32_t chunk, uint64_t* keys_out, void* stream) {
+  if (m == 0) return XCHG_OK;
+  XCHG_REQUIRE(offsets && rows && keys_out, "NULL argument");
+  XCHG_LAUNCH(XK_NORMALIZE, (cudaStream_t)stream,
+              k_string_chunk_keys_rows<<<st_grid(m), ST_THREADS, 0, (cudaStream_t)stream>>>(offsets, data, rows, m,
+                                                                                          chunk, keys_out));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+extern "C" int xchg_scatter_u32(const uint32_t* idx, const uint32_t* vals, uint64_t m, uint32_t* out,
+                                void* stream) {
+  if (m == 0) return XCHG_OK;
+  XCHG_REQUIRE(idx && vals && out, "NULL argument");
+  XCHG_LAUNCH(XK_MISC, (cudaStream_t)stream,
+              k_scatter_u32<<<st_grid(m), ST_THREADS, 0, (cudaStream_t)stream>>>(idx, vals, m, out));
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
 }

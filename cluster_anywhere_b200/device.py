@@ -32,6 +32,7 @@ import torch
 from . import _cabi
 from ._cabi import XchgError
 
+_OFFSET_LIMIT = 0x7FFFFFFF  # largest int32 Arrow offset (tests lower it)
 _PAD = 64  # every device buffer is padded so 16-byte windows / 4-byte words stay in bounds
 
 
@@ -609,12 +610,16 @@ def export_blocks(rt: Runtime, table: DeviceTable, ranges: Sequence[tuple]) -> L
                 w = col.uniform
                 ent["data"] = d2h(col.data[: n * w])
                 # every block's offsets are a prefix of 0, w, 2w, ...
-                offs_d = rt.empty(max_rows + 1, torch.int32 if obits == 32 else torch.int64)
                 elem_w = w // col.width
+                off_rows = max_rows
+                if obits == 32 and elem_w and max_rows * elem_w > _OFFSET_LIMIT:
+                    off_rows = _OFFSET_LIMIT // elem_w  # larger blocks leave as several chunks
+                    ent["rows_per_chunk"] = off_rows
+                offs_d = rt.empty(off_rows + 1, torch.int32 if obits == 32 else torch.int64)
                 if obits == 32:
-                    rt.call("xchg_offsets_uniform32", max_rows + 1, elem_w, _vp(offs_d), rt.stream)
+                    rt.call("xchg_offsets_uniform32", off_rows + 1, elem_w, _vp(offs_d), rt.stream)
                 else:
-                    rt.call("xchg_offsets_uniform64", max_rows + 1, elem_w, 0, _vp(offs_d), rt.stream)
+                    rt.call("xchg_offsets_uniform64", off_rows + 1, elem_w, 0, _vp(offs_d), rt.stream)
                 ent["offsets"] = d2h(offs_d)
             else:
                 total = int(col.offsets[n].item()) if n else 0  # sync: byte count
@@ -679,17 +684,30 @@ def export_blocks(rt: Runtime, table: DeviceTable, ranges: Sequence[tuple]) -> L
                 is_list = pa.types.is_list(st) or pa.types.is_large_list(st)
                 if col.uniform is not None:
                     w = col.uniform
-                    dslice = ent["dbuf"].slice(lo * w, m * w)
-                    # offsets start at 0 for every block; validity still needs the row offset
-                    if vbuf is not None and lo:
-                        vb = _bitmap_window(ent["valid"], lo, m)
-                    else:
-                        vb = vbuf
-                    if is_list:
-                        child = pa.Array.from_buffers(st.value_type, m * (w // col.width), [None, dslice])
-                        arr = pa.Array.from_buffers(st, m, [vb, ent["obuf"]], null_count=nc, children=[child])
-                    else:
-                        arr = pa.Array.from_buffers(st, m, [vb, ent["obuf"], dslice], null_count=nc)
+                    # a block whose bytes do not fit the type's int32 offsets becomes several
+                    # chunks of one column (the reference chunks the same way,
+                    # transform_pyarrow.py:654-737); every chunk's offsets are a prefix of 0, w, 2w, ...
+                    per = ent.get("rows_per_chunk") or max(1, m)
+                    pieces = []
+                    for c0 in range(0, max(m, 1), per):
+                        mc = min(per, m - c0)
+                        dslice = ent["dbuf"].slice((lo + c0) * w, mc * w)
+                        if vbuf is not None and (lo + c0):
+                            vb = _bitmap_window(ent["valid"], lo + c0, mc)
+                        else:
+                            vb = vbuf
+                        if is_list:
+                            child = pa.Array.from_buffers(st.value_type, mc * (w // col.width), [None, dslice])
+                            piece = pa.Array.from_buffers(st, mc, [vb, ent["obuf"]], null_count=nc, children=[child])
+                        else:
+                            piece = pa.Array.from_buffers(st, mc, [vb, ent["obuf"], dslice], null_count=nc)
+                        if isinstance(col.type, pa.ExtensionType):
+                            piece = pa.ExtensionArray.from_storage(col.type, piece)
+                        pieces.append(piece)
+                        if m == 0:
+                            break
+                    arrays.append(pieces[0] if len(pieces) == 1 else pa.chunked_array(pieces))
+                    continue
                 elif ent.get("abs"):
                     arr = pa.Array.from_buffers(st, m, [vbuf, ent["obuf"], ent["dbuf"]], null_count=nc, offset=lo)
                 else:
@@ -762,9 +780,10 @@ def _string_offsets(rt: Runtime, col: DeviceColumn) -> torch.Tensor:
     return off
 
 
-def _sort_string_column(rt: Runtime, col: DeviceColumn, desc: bool, perm, n: int, ws, ws_bytes):
+def _sort_string_column_lsd(rt: Runtime, col: DeviceColumn, desc: bool, perm, n: int, ws, ws_bytes):
     """Stable sort by one string column: LSD over (length, last chunk, ..., chunk 0), every
-    step a stable K3 sort of a u32 / u64 key array (see csrc/strings.cu)."""
+    step a stable K3 sort of a u32 / u64 key array (see csrc/strings.cu).  Kept for A/B runs
+    (XCHG_STRING_ALGO=lsd); the default is the MSD walk below."""
     off = _string_offsets(rt, col)
     lens = rt.empty(n, torch.int32)
     mx = rt.zeros(1, torch.int64)
@@ -784,6 +803,119 @@ def _sort_string_column(rt: Runtime, col: DeviceColumn, desc: bool, perm, n: int
                 _vp(perm), n, _vp(out), None, _vp(ws), ws_bytes, rt.stream, launches=11)
         perm = out
     return perm
+
+
+def _exclusive_scan_flags(rt: Runtime, flags: torch.Tensor, m: int) -> torch.Tensor:
+    """int64[m + 1] exclusive scan of a uint32 0/1 array, by the offsets scan of the ragged
+    take (K5): a row of "length" flags[j] out of a two-row table with lengths 0 and 1."""
+    table = getattr(rt, "_scan_table", None)
+    if table is None:
+        table = rt.empty(3, torch.int64)
+        _h2d(table.view(torch.uint8), np.array([0, 0, 1], dtype=np.int64).view(np.uint8))
+        rt._scan_table = table
+    out = rt.empty(m + 1, torch.int64)
+    wsb = ctypes.c_uint64()
+    _cabi.check(_cabi.load().xchg_gather_offsets_workspace_bytes(m, ctypes.byref(wsb)))
+    ws = rt.empty(wsb.value)
+    rt.call("xchg_gather_offsets", _vp(table), _vp(flags), m, _vp(out), _vp(ws), wsb.value, rt.stream, launches=3)
+    return out
+
+
+def _sort_string_column(rt: Runtime, col: DeviceColumn, desc: bool, perm, n: int, ws, ws_bytes):
+    """Stable sort by one string column, most significant bytes first: ONE stable sort of
+    all rows by their first 8 bytes, then only the rows that still tie AND whose tie group
+    holds at least two different strings are looked at again, 8 bytes at a time (a heavy
+    hitter's run of identical keys is final after one comparison with its neighbour), the
+    length last (a proper prefix sorts first).  Same order as the LSD chain over every
+    chunk -- pyarrow's bytewise order, nulls last -- at a cost that follows the number of
+    rows whose order is still open instead of rows x chunks."""
+    if os.environ.get("XCHG_STRING_ALGO", "msd") == "lsd":
+        return _sort_string_column_lsd(rt, col, desc, perm, n, ws, ws_bytes)
+    off = _string_offsets(rt, col)
+    lib = _cabi.load()
+    # ---- level 0: every row, by (null-ness, chunk 0) ----
+    keys0 = rt.empty(n, torch.int64)
+    rt.call("xchg_string_chunk_keys", _vp(off), _vp(col.data), n, 0, _vp(keys0), rt.stream)
+    order = rt.empty(n, torch.int32)
+    sorted_keys = rt.empty(n, torch.int64)
+    rt.call("xchg_sort_column", _vp(keys0), _cabi.U64, int(desc), _vp(col.validity), 0, _vp(perm), n, _vp(order),
+            _vp(sorted_keys), _vp(ws), ws_bytes, rt.stream, launches=11)
+    del keys0
+
+    def open_positions(rows, keys, gid_prev, m, from_byte):
+        """-> (list of the positions of ``rows`` whose order is still open, their group ids)"""
+        gflag, fflag = rt.empty(m), rt.empty(m)
+        rt.call("xchg_string_tie_flags", _vp(off), _vp(col.data), _vp(col.validity), _vp(rows), _vp(keys),
+                _vp(gid_prev), m, from_byte, _vp(gflag), _vp(fflag), rt.stream)
+        wsb = ctypes.c_uint64()
+        _cabi.check(lib.xchg_groups_from_flags_bytes(m, ctypes.byref(wsb)))
+        gws = rt.empty(wsb.value)
+        gid = rt.empty(m, torch.int32)
+        first = rt.empty(m, torch.int32)
+        g_out = ctypes.c_uint64()
+        rt.call("xchg_groups_from_flags", _vp(gflag), None, m, _vp(gws), wsb.value, _vp(gid), _vp(first),
+                ctypes.byref(g_out), rt.stream, launches=3)  # sync: number of groups
+        ngroups = int(g_out.value)
+        if ngroups == m:
+            return None, None, 0
+        unresolved = rt.empty(ngroups)
+        active = rt.empty(m, torch.int32)
+        rt.call("xchg_string_active_rows", _vp(gflag), _vp(fflag), _vp(gid), m, ngroups, _vp(unresolved),
+                _vp(active), rt.stream, launches=2)
+        excl = _exclusive_scan_flags(rt, active, m)
+        a = int(excl[m].item())  # sync: rows still open
+        if a == 0:
+            return None, None, 0
+        lst = rt.empty(a, torch.int32)
+        rt.call("xchg_scatter_flagged", _vp(active), _vp(excl), m, _vp(lst), rt.stream)
+        gid_a = rt.empty(a, torch.int32)
+        rt.call("xchg_gather_fixed", _vp(gid), 4, _vp(lst), a, _vp(gid_a), rt.stream)
+        return lst, gid_a, a
+
+    lst, gid_a, a = open_positions(order, sorted_keys, None, n, 8)
+    del sorted_keys
+    if a == 0:
+        return order
+    mx = rt.zeros(1, torch.int64)
+    lens = rt.empty(n, torch.int32)
+    rt.call("xchg_string_lengths", _vp(off), n, _vp(lens), _vp(mx), rt.stream)
+    nchunks = (int(mx.item()) + 7) // 8  # sync
+    del lens
+    pos = lst  # positions (in `order`) of the open rows, ascending
+    level = 1
+    while a > 0:
+        last = level >= nchunks  # the chunks are used up: the length decides
+        rows_a = rt.empty(a, torch.int32)
+        rt.call("xchg_gather_fixed", _vp(order), 4, _vp(pos), a, _vp(rows_a), rt.stream)
+        keys = rt.empty(a, torch.int64)
+        rt.call("xchg_string_chunk_keys_rows", _vp(off), _vp(col.data), _vp(rows_a), a,
+                0xFFFFFFFF if last else level, _vp(keys), rt.stream)
+        # stable sort of the list by (group, key): by key first, then by group
+        ws_a_bytes = sort_workspace_bytes(a)
+        ws_a = ws if ws_a_bytes <= ws_bytes else rt.empty(ws_a_bytes)
+        o1 = rt.empty(a, torch.int32)
+        rt.call("xchg_sort_column", _vp(keys), _cabi.U64, int(desc), None, 0, None, a, _vp(o1), None, _vp(ws_a),
+                max(ws_bytes, ws_a_bytes), rt.stream, launches=8)
+        o2 = rt.empty(a, torch.int32)
+        rt.call("xchg_sort_column", _vp(gid_a), _cabi.U32, 0, None, 0, _vp(o1), a, _vp(o2), None, _vp(ws_a),
+                max(ws_bytes, ws_a_bytes), rt.stream, launches=8)
+        rows_new = rt.empty(a, torch.int32)
+        rt.call("xchg_gather_fixed", _vp(rows_a), 4, _vp(o2), a, _vp(rows_new), rt.stream)
+        rt.call("xchg_scatter_u32", _vp(pos), _vp(rows_new), a, _vp(order), rt.stream)
+        if last:
+            break
+        keys_new = rt.empty(a, torch.int64)
+        rt.call("xchg_gather_fixed", _vp(keys), 8, _vp(o2), a, _vp(keys_new), rt.stream)
+        gid_new = rt.empty(a, torch.int32)
+        rt.call("xchg_gather_fixed", _vp(gid_a), 4, _vp(o2), a, _vp(gid_new), rt.stream)
+        sub, gid_next, a_next = open_positions(rows_new, keys_new, gid_new, a, 8 * (level + 1))
+        if a_next == 0:
+            break
+        pos_next = rt.empty(a_next, torch.int32)
+        rt.call("xchg_gather_fixed", _vp(pos), 4, _vp(sub), a_next, _vp(pos_next), rt.stream)
+        pos, gid_a, a = pos_next, gid_next, a_next
+        level += 1
+    return order
 
 
 def _pack_string_boundaries(rt: Runtime, boundaries: Sequence[tuple]):

@@ -54,7 +54,12 @@ from . import peer
 
 HDR = 8            # int64 words: blocks, rows, schema fingerprint, samples, eligible, layout signature
 CAP = 4096         # sample slots per rank in the all-gathered message
-SAMPLES_PER_BLOCK = 10  # int(R * 10 / M) with R == M (sort_task_spec.py:167)
+# The reference draws int(R * 10 / M) = 10 rows per block when R == M (sort_task_spec.py:167);
+# with 10 the gap between two boundaries has a relative spread of 1 / sqrt(10): blocks up to
+# ~2.5x the mean, ranks +-10 %.  Sampling is a kernel here and costs nothing, so every block
+# gives up to 100 samples (cut points are unpinned by the reference; XCHG_SAMPLES_PER_BLOCK=10
+# restores its count).
+SAMPLES_PER_BLOCK = int(os.environ.get("XCHG_SAMPLES_PER_BLOCK", "100"))
 CMAX = 16          # chunks per rank the flag area has room for
 GMAX = 32
 FLAG_AREA = 4096   # 2 kinds x CMAX x GMAX uint32
@@ -62,6 +67,8 @@ HEADER_BYTES = peer.HEADER_BYTES
 ERR_OFF = FLAG_AREA
 KIND_KEYS, KIND_PAYLOAD = 0, 1
 WAIT_TIMEOUT_NS = int(float(os.environ.get("XCHG_WAIT_TIMEOUT_S", "20")) * 1e9)
+# timing experiments only (the output is then wrong): 1 = no payload stores, 2 = no receive side
+_DEBUG_SKIP = int(os.environ.get("XCHG_DEBUG_SKIP", "0"))
 
 
 def _ptr(base: int, off: int = 0):
@@ -100,7 +107,7 @@ def _eligible(ds, sort_key: SortKey, boundaries) -> bool:
             return False
         if not (c.kind == "fixed" or (c.kind == "var" and c.uniform is not None and c.uniform > 0)):
             return False
-    if ds.num_blocks * SAMPLES_PER_BLOCK > CAP:
+    if ds.num_blocks * 10 > CAP:
         return False
     if boundaries is not None:
         for b in boundaries:
@@ -138,8 +145,9 @@ def try_sort(ex, ds, sort_key: SortKey, boundaries: Optional[list], seed: int, c
             nb = ds.num_blocks
             starts = (ctypes.c_uint64 * nb)(*[lo for lo, hi in ds.block_ranges])
             rows = (ctypes.c_uint64 * nb)(*[max(0, hi - lo) for lo, hi in ds.block_ranges])
+            per_block = max(10, min(SAMPLES_PER_BLOCK, CAP // max(1, nb)))
             rt.call("xchg_sample_keys", _vp(keycol.data), kt, int(desc), None, 0, starts, rows, nb,
-                    SAMPLES_PER_BLOCK, int(seed) & 0xFFFFFFFFFFFFFFFF, rank << 32,
+                    per_block, int(seed) & 0xFFFFFFFFFFFFFFFF, rank << 32,
                     _ptr(msg.data_ptr(), HDR * 8), CAP, ctypes.byref(nsamp), rt.stream)
     hdr = [ds.num_blocks, n, _schema_fp(table.schema) if table is not None else 0, int(nsamp.value),
            int(ok), _layout_signature(table) if table is not None else 0, 0, 0]
@@ -268,18 +276,23 @@ def try_sort(ex, ds, sort_key: SortKey, boundaries: Optional[list], seed: int, c
         # the stores are link-bound: a CTA or two per SM keep NVLink busy and leave the rest of
         # every SM (shared memory above all) to the receive-side sorts and gathers
         cap = int(os.environ.get("XCHG_SIDE_CTAS_PER_SM", "2"))
+        stage_kb = int(os.environ.get("XCHG_SIDE_STAGE_KB", "0"))
         if cap:
             rt.call("xchg_set_gather_ctas_per_sm", cap, launches=0)
+        if stage_kb:
+            rt.call("xchg_set_gather_stage_kb", stage_kb, launches=0)
         try:
             for c in range(nchunks):
                 vs = [chunks_of[g][c] for g in owners if c < len(chunks_of[g])]
-                if n and pay_cols:
+                if n and pay_cols and not (_DEBUG_SKIP & 1):
                     peer.store_columns(rt, pl, pay_cols, vsel=vs)
                 fp, k = flag_ptrs(KIND_PAYLOAD, c)
                 rt.call("xchg_signal_flags", fp, k, epoch, rt.stream)
         finally:
             if cap:
                 rt.call("xchg_set_gather_ctas_per_sm", 0, launches=0)
+            if stage_kb:
+                rt.call("xchg_set_gather_stage_kb", 0, launches=0)
 
     partitioned = None
     if main is not None:
@@ -385,9 +398,10 @@ def try_sort(ex, ds, sort_key: SortKey, boundaries: Optional[list], seed: int, c
         if srt is not None:
             srt.wait_stream(main)
         with (torch.cuda.stream(srt) if srt is not None else contextlib.nullcontext()):
-            sort_keys()
-            for ci in range(len(mine)):
-                gather_chunk(ci)
+            if not (_DEBUG_SKIP & 2):
+                sort_keys()
+                for ci in range(len(mine)):
+                    gather_chunk(ci)
         cols = []
         for j in range(len(names)):
             src = table.columns[j]

@@ -86,6 +86,11 @@ int xchg_set_l2_fetch_granularity(int bytes);
  * key sort, so that they do not take the SMs' shared memory away from it.  Process
  * wide; no counterpart in the reference. */
 int xchg_set_gather_ctas_per_sm(int ctas_per_sm);
+/* Shared-memory staging per CTA (KB, 4..56; 0 = the default 56) of the uniform-row gather
+ * for the launches that follow: a gather that stores into peer memory is link-bound and runs
+ * with a few KB per CTA so that the receive-side sort and gathers keep the SM's shared
+ * memory.  Process wide; no counterpart in the reference. */
+int xchg_set_gather_stage_kb(int kb);
 
 /* ---------------------------------------------------------------- sort ---- */
 
@@ -349,6 +354,42 @@ int xchg_assign_partitions_bytes(const int64_t* offsets, const uint8_t* data, co
                                  uint64_t n, const int64_t* bound_offsets, const uint8_t* bound_data,
                                  const uint8_t* bound_flags, int nb, int descending,
                                  uint32_t* dest_out, uint64_t* counts_out, void* stream);
+
+/*
+ * MSD refinement of a string sort.  After a stable sort by chunk 0 only the rows that tie
+ * there can be out of order, and of those only the ones whose tie group holds at least two
+ * DIFFERENT strings (a heavy hitter's run of identical keys is final).  The entry points
+ * below work on a LIST of m rows in their current order -- level 0: every row, in the order
+ * xchg_sort_column produced; later levels: the rows still unresolved -- and let the caller
+ * re-sort only those by the next chunk (xchg_sort_column on the list's chunk keys, then on
+ * the list's group ids, both stable).  Same result as the LSD chain over every chunk: the
+ * order pyarrow.compute.sort_indices gives the reference (transform_pyarrow.py:41).
+ *
+ * xchg_string_tie_flags     gflag[j] = list entry j starts a new tie group (previous-level
+ *                           group id, this level's key or null-ness differs from entry j-1);
+ *                           fflag[j] = gflag[j], or the two rows' strings differ anywhere from
+ *                           byte from_byte on (lengths included).  rows = the list's row ids,
+ *                           keys = its keys at this level, gid_prev may be NULL (one group).
+ * xchg_string_active_rows   active_out[j] = 1 when entry j's group (gid from a scan of gflag,
+ *                           num_groups groups) contains two different strings, else 0.
+ *                           unresolved_scratch: num_groups bytes.
+ * xchg_scatter_flagged      list_out[excl_scan[j]] = j for every j with flags[j] != 0.
+ * xchg_string_chunk_keys_rows  xchg_string_chunk_keys for listed rows; chunk = UINT32_MAX
+ *                           gives the rows' lengths (the last level: a proper prefix first).
+ * xchg_scatter_u32          out[idx[j]] = vals[j].
+ */
+int xchg_string_tie_flags(const int64_t* offsets, const uint8_t* data, const uint8_t* validity,
+                          const uint32_t* rows, const uint64_t* keys, const uint32_t* gid_prev,
+                          uint64_t m, uint64_t from_byte, uint8_t* gflag_out, uint8_t* fflag_out,
+                          void* stream);
+int xchg_string_active_rows(const uint8_t* gflag, const uint8_t* fflag, const uint32_t* gid, uint64_t m,
+                            uint64_t num_groups, uint8_t* unresolved_scratch, uint32_t* active_out,
+                            void* stream);
+int xchg_scatter_flagged(const uint32_t* flags, const int64_t* excl_scan, uint64_t m, uint32_t* list_out,
+                         void* stream);
+int xchg_string_chunk_keys_rows(const int64_t* offsets, const uint8_t* data, const uint32_t* rows,
+                                uint64_t m, uint32_t chunk, uint64_t* keys_out, void* stream);
+int xchg_scatter_u32(const uint32_t* idx, const uint32_t* vals, uint64_t m, uint32_t* out, void* stream);
 
 /* -------------------------------------------------------------- gather ---- */
 

@@ -11,7 +11,7 @@ for CFG in "$@"; do
   PORT=$((PORT+1))
   echo "=== $CFG" >> $OUT
   env $CFG XCHG_TIMELINE=1 timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N \
-      --master-addr 127.0.0.1 --master-port $PORT bench.py --gpus $N --steps 10 --warmup 3 --no-e2e --no-cpu \
+      --master-addr 127.0.0.1 --master-port $PORT bench.py --gpus $N --steps 10 --warmup 3 --no-e2e --no-cpu $SWEEP_EXTRA \
       > gpurun_out/${TAG}_tmp.json 2> gpurun_out/${TAG}_tmp.err
   echo "rc=$?" >> $OUT
   grep -E "gpu timeline rank 0|Error|error" gpurun_out/${TAG}_tmp.err | tail -4 >> $OUT

@@ -928,6 +928,9 @@ class FakeLib:
         _arr(out, np.uint8, n)[:] = _bits(inp, bit_off, _arr(idx, np.uint32, n)).astype(np.uint8)
         return 0
 
+    def xchg_set_gather_stage_kb(self, kb):
+        return 0
+
     def xchg_set_gather_ctas_per_sm(self, n):
         return 0
 
@@ -965,6 +968,71 @@ class FakeLib:
         bounds = self._rows_bytes(boff, bdata, nb)
         fl = _arr(bflags, np.uint8, nb) if _addr(bflags) else np.zeros(nb, np.uint8)
         return rows, valid, bounds, fl
+
+    # -- MSD refinement of a string sort --------------------------------------------
+    def _row_bytes(self, off, data, r):
+        o = _arr(off, np.int64, r + 2)
+        return bytes(_arr(data, np.uint8, int(o[r + 1]))[int(o[r]):int(o[r + 1])]) if o[r + 1] > o[r] else b""
+
+    def xchg_string_tie_flags(self, off, data, validity, rows, keys, gid_prev, m, from_byte, gflag, fflag, stream):
+        if m == 0:
+            return 0
+        r = _arr(rows, np.uint32, m).astype(np.int64)
+        k = _arr(keys, np.uint64, m)
+        gp = _arr(gid_prev, np.uint32, m) if _addr(gid_prev) else None
+        valid = _bits(validity, 0, r) if _addr(validity) else np.ones(m, bool)
+        g = np.zeros(m, np.uint8)
+        f = np.zeros(m, np.uint8)
+        g[0] = f[0] = 1
+        for j in range(1, m):
+            gj = (gp is not None and gp[j] != gp[j - 1]) or k[j] != k[j - 1] or valid[j] != valid[j - 1]
+            fj = gj
+            if not gj and valid[j]:
+                a, b = self._row_bytes(off, data, int(r[j - 1])), self._row_bytes(off, data, int(r[j]))
+                fj = len(a) != len(b) or a[from_byte:] != b[from_byte:]
+            g[j], f[j] = int(gj), int(fj)
+        _arr(gflag, np.uint8, m)[:] = g
+        _arr(fflag, np.uint8, m)[:] = f
+        return 0
+
+    def xchg_string_active_rows(self, gflag, fflag, gid, m, ngroups, scratch, active, stream):
+        if m == 0:
+            return 0
+        g, f = _arr(gflag, np.uint8, m), _arr(fflag, np.uint8, m)
+        gi = _arr(gid, np.uint32, m).astype(np.int64)
+        unresolved = np.zeros(ngroups, bool)
+        unresolved[gi[(f != 0) & (g == 0)]] = True
+        _arr(active, np.uint32, m)[:] = unresolved[gi].astype(np.uint32)
+        return 0
+
+    def xchg_scatter_flagged(self, flags, excl, m, out, stream):
+        if m == 0:
+            return 0
+        fl = _arr(flags, np.uint32, m)
+        idx = np.nonzero(fl)[0].astype(np.uint32)
+        _arr(out, np.uint32, len(idx))[:] = idx
+        return 0
+
+    def xchg_string_chunk_keys_rows(self, off, data, rows, m, chunk, out, stream):
+        if m == 0:
+            return 0
+        r = _arr(rows, np.uint32, m).astype(np.int64)
+        res = np.zeros(m, np.uint64)
+        for j in range(m):
+            b = self._row_bytes(off, data, int(r[j]))
+            if chunk == 0xFFFFFFFF:
+                res[j] = len(b)
+            else:
+                res[j] = int.from_bytes(b[8 * chunk:8 * chunk + 8].ljust(8, b"\0"), "big")
+        _arr(out, np.uint64, m)[:] = res
+        return 0
+
+    def xchg_scatter_u32(self, idx, vals, m, out, stream):
+        if m == 0:
+            return 0
+        ix = _arr(idx, np.uint32, m).astype(np.int64)
+        _arr(out, np.uint32, int(ix.max()) + 1)[ix] = _arr(vals, np.uint32, m)
+        return 0
 
     def xchg_partition_bounds_bytes(self, off, data, validity, n, boff, bdata, bflags, nb, desc, cuts, stream):
         rows, valid, bounds, fl = self._str_inputs(off, data, validity, n, boff, bdata, bflags, nb)

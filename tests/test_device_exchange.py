@@ -109,3 +109,25 @@ def test_large_sort_properties():
     assert (data == payload[rid]).all()
     same = np.diff(k) == 0
     assert (np.diff(rid)[same] > 0).all()  # ties keep (block, row) order
+
+
+def test_export_chunks_a_block_beyond_int32_offsets(engine, monkeypatch):
+    """A uniform-width binary block whose bytes exceed the int32 offset range leaves as ONE
+    table whose column has several chunks (the reference chunks too,
+    _internal/arrow_ops/transform_pyarrow.py:654-737); the limit is lowered here so that a
+    small block crosses it."""
+    from cluster_anywhere_b200 import device as dev
+
+    monkeypatch.setattr(dev, "_OFFSET_LIMIT", 90 * 100 + 50)
+    rng = np.random.default_rng(12)
+    n = 1000
+    pay = rng.integers(0, 256, n * 90, dtype=np.uint8)
+    offs = np.arange(n + 1, dtype=np.int32) * 90
+    t = pa.table({"k": pa.array(rng.integers(0, 1000, n), pa.int64()),
+                  "p": pa.Array.from_buffers(pa.binary(), n, [None, pa.py_buffer(offs), pa.py_buffer(pay)])})
+    rt = dev.default_runtime()
+    dt = dev.stage_table(rt, t)
+    out = dev.export_blocks(rt, dt, [(0, 350), (350, 350), (350, 1000)])
+    assert [o.num_rows for o in out] == [350, 0, 650]
+    assert out[0]["p"].num_chunks == 4 and out[2]["p"].num_chunks == 7  # 100 rows per chunk
+    assert pa.concat_tables(out).equals(t) or pa.concat_tables(out).combine_chunks().equals(t.combine_chunks())

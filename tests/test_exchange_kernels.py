@@ -148,3 +148,32 @@ def test_single_rank_map_exchange_reduce(engine, cols, desc):
         assert G.tables_equal(pa.concat_tables([o for o in out if o.num_rows]), exp)
     finally:
         dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("w,n_in,n_out", [(1024, 5000, 7001), (16, 100, 3), (4096, 300, 299), (48, 70000, 100000)])
+def test_gather_rows_tma_variant_equals_the_default(w, n_in, n_out):
+    """XCHG_GATHER_BULK=1 sends 16-byte-aligned uniform rows through cp.async.bulk (global ->
+    shared -> global, no thread touches the data); same bytes as the default kernel."""
+    import ctypes
+
+    from cluster_anywhere_b200 import _cabi
+
+    _cabi._install_test_double(None)
+    dev.reset_default_runtime()
+    rt = dev.default_runtime()
+    rng = np.random.default_rng(w)
+    src = torch.from_numpy(rng.integers(0, 256, n_in * w, dtype=np.uint8)).to(rt.device)
+    idx = torch.from_numpy(rng.integers(0, n_in, n_out).astype(np.int32)).to(rt.device)
+    libc = ctypes.CDLL(None)
+    outs = []
+    for mode in (b"0", b"1"):
+        libc.setenv(b"XCHG_GATHER_BULK", mode, 1)
+        out = rt.zeros(n_out * w)
+        rt.call("xchg_gather_rows", ctypes.c_void_p(src.data_ptr()), w, ctypes.c_void_p(idx.data_ptr()), n_out,
+                ctypes.c_void_p(out.data_ptr()), rt.stream)
+        rt.synchronize()
+        outs.append(out.cpu().numpy())
+    libc.setenv(b"XCHG_GATHER_BULK", b"0", 1)
+    exp = src.cpu().numpy().reshape(n_in, w)[idx.cpu().numpy()].reshape(-1)
+    assert np.array_equal(outs[0], exp) and np.array_equal(outs[1], exp)
