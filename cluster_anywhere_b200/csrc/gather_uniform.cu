@@ -99,7 +99,6 @@ k_gather_rows_uniform(const uint8_t* __restrict__ in, uint32_t w, const uint32_t
   const uint32_t cpr = slot >> 4;  // 16-byte chunks per slot
   const uint64_t nwork = MULTI ? max_tiles * (uint64_t)segs.nseg
                                : (n_out_ + rows_per_tile - 1) / rows_per_tile;
-
   for (uint64_t work = blockIdx.x; work < nwork; work += gridDim.x) {
     const uint32_t* idx = idx_;
     uint64_t n_out = n_out_;

@@ -151,6 +151,28 @@ def main():
         nbs = (ctypes.c_uint64 * world)(*[share * W] * world)
         timed("a2a_copy (contiguous, interleaved segments; remote bytes counted)",
               lambda: _cabi.check(lib.xchg_copy_segments(world, srcs, outs, nbs, stream)), remote_bytes)
+        libc = ctypes.CDLL(None)
+        libc.setenv(b"XCHG_COPY_BULK", b"1", 1)
+        timed("a2a_copy_tma (cp.async.bulk, interleaved segments; remote bytes counted)",
+              lambda: _cabi.check(lib.xchg_copy_segments(world, srcs, outs, nbs, stream)), remote_bytes)
+        libc.setenv(b"XCHG_COPY_BULK", b"0", 1)
+        # copy engines: one cudaMemcpyAsync per peer, each on its own stream
+        ce_streams = [torch.cuda.Stream(device=rt.device) for _ in range(world)]
+        views = [hdl.get_buffer(d, (share * W,), torch.uint8, land_off + rank * share * W) for d in order]
+
+        def a2a_ce():
+            cur = torch.cuda.current_stream(rt.device)
+            for i, d in enumerate(order):
+                if d == rank:
+                    continue
+                ce_streams[i].wait_stream(cur)
+                with torch.cuda.stream(ce_streams[i]):
+                    views[i].copy_(table[i * share * W:(i + 1) * share * W], non_blocking=True)
+            for i, d in enumerate(order):
+                if d != rank:
+                    cur.wait_stream(ce_streams[i])
+
+        timed("a2a_ce (cudaMemcpyAsync per peer on its own stream; remote bytes counted)", a2a_ce, remote_bytes)
         send = table[: share * W * world]
         recv = local_out[: share * W * world]
         timed("a2a_nccl all_to_all_single (remote bytes counted)",
