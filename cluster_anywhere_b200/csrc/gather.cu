@@ -317,29 +317,77 @@ k_gather_rows(const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off
       }
       __syncthreads();
 
-      // ---- phase 2: stage -> global, one warp per row, words aligned to dst ----
-      for (int j = round_start + warp; j < round_end; j += GR_WARPS) {
-        const uint32_t len = m_len[j];
-        if (len == 0) continue;
-        const uint32_t mis = (uint32_t)(((uintptr_t)in + m_src[j]) & 15);
-        const uint32_t a0 = (m_slot[j] - base_slot) + mis;  // stage byte address of the row
-        uint8_t* d = out + m_dst[j];
-        const uint32_t head = min(len, (uint32_t)((4 - ((uintptr_t)d & 3)) & 3));
-        const uint32_t nfull = (len - head) >> 2;
-        const uint32_t tail = len - head - (nfull << 2);
-        const uint32_t aw = a0 + head;
-        uint32_t* dw = reinterpret_cast<uint32_t*>(d + head);
-        const uint32_t sh = (aw & 3) * 8;
-        const uint32_t* sw = reinterpret_cast<const uint32_t*>(stage + (aw & ~3u));
-        for (uint32_t k = lane; k < nfull; k += 32) {
-          const uint32_t lo = sw[k], hi = sw[k + 1];
-          dw[k] = __funnelshift_r(lo, hi, sh);
+      // ---- phase 2: stage -> global, FLAT over the round's output bytes ----
+      // The rows of a round are consecutive output rows, so their bytes are ONE contiguous
+      // range of `out`: thread q produces the q-th 16-byte-aligned unit of it (one 16-byte
+      // store; a warp writes 512 dense bytes).  The unit's row is found by binary search over
+      // the rows' output offsets; a unit inside one row is two unaligned 16-byte windows of the
+      // stage joined by funnel shifts, a unit that spans rows (every unit of short rows) is
+      // put together bytewise.  One warp per row cost ~150 thread instructions per 16 bytes on
+      // 136-byte rows (the round-1 kernel was issue-bound at a quarter of the uniform gather's
+      // rate); this mapping needs about a third of that.
+      {
+        const int64_t o0 = m_dst[round_start];
+        const int64_t o1 = round_end < T ? m_dst[round_end] : m_dst[T - 1] + (int64_t)m_len[T - 1];
+        uint8_t* ob = out + o0;
+        const uint32_t nbytes = (uint32_t)(o1 - o0);
+        const uint32_t head = min(nbytes, (uint32_t)((16 - ((uintptr_t)ob & 15)) & 15));
+        const uint32_t nunits = (nbytes - head) >> 4;
+        const uint32_t tail0 = head + (nunits << 4);
+        auto row_of = [&](int64_t o) -> int {  // last row of the round that starts at or before byte o
+          int lo = round_start, hi = round_end;
+          while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (m_dst[mid] <= o) lo = mid;
+            else hi = mid;
+          }
+          return lo;
+        };
+        auto stage_addr = [&](int j) -> uint32_t {  // stage byte address of row j's first byte
+          return (m_slot[j] - base_slot) + (uint32_t)(((uintptr_t)in + m_src[j]) & 15);
+        };
+        uint4* ov = reinterpret_cast<uint4*>(ob + head);
+        const uint32_t* sw = reinterpret_cast<const uint32_t*>(stage);
+        for (uint32_t q = tid; q < nunits; q += GR_THREADS) {
+          const int64_t o = o0 + head + ((int64_t)q << 4);
+          int j = row_of(o);
+          uint32_t r = (uint32_t)(o - m_dst[j]);
+          uint32_t len = m_len[j];
+          uint4 v;
+          if (r + 16 <= len) {
+            const uint32_t a = stage_addr(j) + r;
+            const uint32_t* pa = sw + (a >> 2);
+            const uint32_t sa = (a & 3) * 8;
+            const uint32_t w0 = pa[0], w1 = pa[1], w2 = pa[2], w3 = pa[3], w4 = pa[4];
+            v.x = __funnelshift_r(w0, w1, sa);
+            v.y = __funnelshift_r(w1, w2, sa);
+            v.z = __funnelshift_r(w2, w3, sa);
+            v.w = __funnelshift_r(w3, w4, sa);
+          } else {
+            uint32_t x[4] = {0u, 0u, 0u, 0u};
+            uint32_t a = stage_addr(j) + r;
+#pragma unroll
+            for (int bi = 0; bi < 16; ++bi) {
+              while (r >= len) {  // next non-empty row (the unit lies inside the round's bytes)
+                ++j;
+                r = 0;
+                len = m_len[j];
+                a = stage_addr(j);
+              }
+              x[bi >> 2] |= (uint32_t)stage[a] << (8 * (bi & 3));
+              ++a;
+              ++r;
+            }
+            v = make_uint4(x[0], x[1], x[2], x[3]);
+          }
+          ov[q] = v;
         }
-        if ((uint32_t)lane < head) {
-          d[lane] = stage[a0 + lane];
-        } else if ((uint32_t)lane < head + tail) {
-          const uint32_t t = lane - head;
-          d[head + (nfull << 2) + t] = stage[aw + (nfull << 2) + t];
+        // head and tail bytes of the round's range (at most 15 each)
+        if ((uint32_t)tid < head + (nbytes - tail0)) {
+          const uint32_t t = (uint32_t)tid < head ? (uint32_t)tid : tail0 + ((uint32_t)tid - head);
+          const int64_t o = o0 + t;
+          const int j = row_of(o);
+          ob[t] = stage[stage_addr(j) + (uint32_t)(o - m_dst[j])];
         }
       }
       __syncthreads();
