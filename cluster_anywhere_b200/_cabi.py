@@ -21,6 +21,17 @@ class XchgError(RuntimeError):
 
 
 _P = c_void_p
+
+
+class MixedCol(ctypes.Structure):
+    """xchg_mixed_col (include/xchg_b200.h): one key column of a tuple that mixes numeric
+    and string columns."""
+    _fields_ = [("kind", ctypes.c_int32), ("descending", ctypes.c_int32), ("norm", c_void_p),
+                ("last_threshold", c_uint64), ("has_last", ctypes.c_int32), ("reserved", ctypes.c_int32),
+                ("offsets", c_void_p), ("data", c_void_p), ("validity", c_void_p),
+                ("bound_offsets", c_void_p), ("bound_data", c_void_p)]
+
+
 _SIGNATURES = {
     "xchg_abi_version": (c_int, []),
     "xchg_last_error": (c_char_p, []),
@@ -38,6 +49,9 @@ _SIGNATURES = {
     "xchg_set_sort_algorithm": (c_int, [c_int]),
     "xchg_partition_bounds": (c_int, [ctypes.POINTER(c_void_p), _P, _P, _P, c_int, c_uint64, _P, _P, _P, c_int, c_int, _P, _P]),
     "xchg_assign_partitions": (c_int, [ctypes.POINTER(c_void_p), _P, c_int, c_uint64, _P, _P, _P, c_int, c_int, _P, _P, _P]),
+    "xchg_partition_bounds_mixed": (c_int, [ctypes.POINTER(MixedCol), c_int, c_uint64, _P, _P, _P, c_int, c_int, _P, _P]),
+    "xchg_assign_partitions_mixed": (c_int, [ctypes.POINTER(MixedCol), c_int, c_uint64, _P, _P, _P, c_int, c_int, _P,
+                                             _P, _P]),
     "xchg_sample_keys": (c_int, [_P, c_int, c_int, _P, c_int64, ctypes.POINTER(c_uint64), ctypes.POINTER(c_uint64),
                                  c_int, c_uint32, c_uint64, c_uint64, _P, c_uint64, ctypes.POINTER(c_uint64), _P]),
     "xchg_select_boundaries": (c_int, [_P, c_int, c_uint64, c_uint32, c_uint32, c_uint32, _P, _P, _P]),

@@ -38,13 +38,13 @@ def _presorted(sort_key: SortKey, norms):
 
 def _cuts_for(rt: dev.Runtime, dt: dev.DeviceTable, norms, boundaries, sort_key: SortKey,
               sorted_dt: Optional[dev.DeviceTable] = None) -> List[int]:
-    """K4.  Numeric keys: search on the sorted radix keys.  A string key (single key
-    column only) is searched on the sorted column itself (``sorted_dt``)."""
+    """K4.  Numeric keys: search on the sorted radix keys.  String key columns are searched
+    on the sorted column itself (``sorted_dt``), alone or inside a tuple with other columns."""
     cols, desc = sort_key.get_columns(), sort_key.get_descending()
     if any(dev.is_string_key(dt.column(c)) for c in cols):
-        if len(cols) != 1:
-            raise NotImplementedError("range partitioning with a string key supports a single key column")
         assert sorted_dt is not None
+        if len(cols) != 1:
+            return dev.mixed_partition_cuts(rt, sorted_dt, norms, boundaries, cols, desc)
         return dev.string_partition_cuts(rt, sorted_dt.column(cols[0]), boundaries, desc[0])
     ktypes = [dev.key_type_of(dt.column(c).type) for c in cols]
     lower, upper, flags = keymod.normalize_boundaries(boundaries, ktypes, desc)

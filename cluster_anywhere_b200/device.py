@@ -993,9 +993,8 @@ def sort_permutation(rt: Runtime, table: DeviceTable, columns: Sequence[str],
         for name, desc in order[1:]:
             col = table.column(name)
             if is_string_key(col):
-                raise NotImplementedError(
-                    "range partitioning on several key columns is supported for numeric keys only; "
-                    f"{name!r} is {col.type}")
+                norms.append(None)  # searched on the sorted column itself (mixed_partition_cuts)
+                continue
             nk = rt.empty(n, torch.int64)
             rt.call("xchg_normalize_keys", _vp(col.data), key_type_of(col.type), int(bool(desc)),
                     _vp(col.validity), 0, _vp(perm), n, _vp(nk), rt.stream)
@@ -1026,6 +1025,69 @@ def partition_cuts(rt: Runtime, norms: List[torch.Tensor], n: int, lower: np.nda
     return [int(x) for x in cuts.tolist()]
 
 
+def _mixed_descriptors(rt: Runtime, table: DeviceTable, norms, boundaries: Sequence[tuple],
+                       columns: Sequence[str], descending: Sequence[bool]):
+    """Arguments of the *_mixed entry points for a key tuple with string columns:
+    -> (MixedCol array, lower, upper, flags device arrays, keep-alive list).  ``table`` holds
+    the string columns in the order the call wants (sorted for the boundary search, as
+    stored for the per-row form); ``norms[c]`` the radix keys of numeric column c."""
+    from . import keys as keymod
+
+    nb, ncols = len(boundaries), len(columns)
+    cols = [table.column(c) for c in columns]
+    ktypes = [None if is_string_key(col) else key_type_of(col.type) for col in cols]
+    lower, upper, flags = keymod.normalize_boundaries(boundaries, ktypes, descending)
+    keep = []
+
+    def up(arr: np.ndarray, dtype) -> torch.Tensor:
+        t = rt.empty(max(1, arr.size), dtype)
+        if arr.size:
+            _h2d(t.view(torch.uint8)[: arr.nbytes], np.ascontiguousarray(arr).view(np.uint8).reshape(-1))
+        keep.append(t)
+        return t
+
+    lo_d = up(lower.astype(np.uint64), torch.int64)
+    up_d = up(upper.astype(np.uint64), torch.int64)
+    fl_d = up(flags.astype(np.uint8), torch.uint8)
+    descs = (_cabi.MixedCol * ncols)()
+    for c, col in enumerate(cols):
+        d = descs[c]
+        d.descending = int(bool(descending[c]))
+        if ktypes[c] is None:
+            off, blob = keymod.pack_string_components(boundaries, c)
+            off_t = _string_offsets(rt, col)
+            keep.append(off_t)
+            d.kind = 1
+            d.offsets = off_t.data_ptr()
+            d.data = col.data.data_ptr() if col.data is not None else None
+            d.validity = col.validity.data_ptr() if col.validity is not None else None
+            d.bound_offsets = up(off, torch.int64).data_ptr()
+            d.bound_data = up(blob, torch.uint8).data_ptr()
+        else:
+            thr, has_last = keymod.last_class_threshold(ktypes[c], col.null_count)
+            d.kind = 0
+            d.norm = norms[c].data_ptr()
+            d.last_threshold = int(thr)
+            d.has_last = int(bool(has_last))
+    return descs, lo_d, up_d, fl_d, keep
+
+
+def mixed_partition_cuts(rt: Runtime, sorted_table: DeviceTable, norms, boundaries: Sequence[tuple],
+                         columns: Sequence[str], descending: Sequence[bool]) -> List[int]:
+    """K4 for key tuples with string columns: numeric columns through their sorted radix
+    keys (``norms``), string columns on the sorted column itself."""
+    nb = len(boundaries)
+    if nb == 0:
+        return []
+    descs, lo_d, up_d, fl_d, keep = _mixed_descriptors(rt, sorted_table, norms, boundaries, columns, descending)
+    cuts = rt.empty(nb, torch.int64)
+    rt.call("xchg_partition_bounds_mixed", descs, len(columns), sorted_table.num_rows, _vp(lo_d), _vp(up_d),
+            _vp(fl_d), nb, int(bool(descending[0])), _vp(cuts), rt.stream)
+    out = [int(x) for x in cuts.tolist()]
+    del keep
+    return out
+
+
 # ---------------------------------------------------------------------------
 # Per-row range partitioning (the exchange's map side on unsorted rows)
 # ---------------------------------------------------------------------------
@@ -1053,9 +1115,28 @@ def assign_partitions(rt: Runtime, table: DeviceTable, boundaries: Sequence[tupl
 
     cols, desc = sort_key.get_columns(), sort_key.get_descending()
     n, nb = table.num_rows, len(boundaries)
+    if any(is_string_key(table.column(c)) for c in cols) and len(cols) != 1:
+        norms = []
+        for name, d in zip(cols, desc):
+            col = table.column(name)
+            if is_string_key(col):
+                norms.append(None)
+                continue
+            if col.kind != "fixed":
+                raise NotImplementedError(f"sort key column {name!r} of type {col.type} is not supported")
+            nk = rt.empty(n, torch.int64)
+            rt.call("xchg_normalize_keys", _vp(col.data), key_type_of(col.type), int(bool(d)),
+                    _vp(col.validity), 0, None, n, _vp(nk), rt.stream)
+            norms.append(nk)
+        descs, lo_d, up_d, fl_d, keep = _mixed_descriptors(rt, table, norms, boundaries, cols, desc)
+        dest = rt.empty(n, torch.int32)
+        counts = rt.zeros(nb + 1, torch.int64)
+        rt.call("xchg_assign_partitions_mixed", descs, len(cols), n, _vp(lo_d), _vp(up_d), _vp(fl_d), nb,
+                int(bool(desc[0])), _vp(dest), _vp(counts), rt.stream)
+        rt.synchronize()  # the boundary buffers (`keep`) must outlive the kernel
+        del keep
+        return dest, counts
     if any(is_string_key(table.column(c)) for c in cols):
-        if len(cols) != 1:
-            raise NotImplementedError("range partitioning with a string key supports a single key column")
         col = table.column(cols[0])
         off_d, data_d, fl_d = _pack_string_boundaries(rt, boundaries)
         dest = rt.empty(n, torch.int32)

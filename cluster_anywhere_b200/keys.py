@@ -141,7 +141,9 @@ def normalize_boundary_value(value, key_type: int, desc: bool):
 
 def normalize_boundaries(boundaries: Sequence[tuple], key_types: Sequence[int],
                          descending: Sequence[bool]):
-    """Boundary tuples -> (lower[nb,ncols], upper[nb,ncols], flags[nb,ncols])."""
+    """Boundary tuples -> (lower[nb,ncols], upper[nb,ncols], flags[nb,ncols]).  A key type of
+    ``None`` marks a string / binary column: its components travel as bytes
+    (``pack_string_components``); here they only get the STOP / None flags."""
     nb, ncols = len(boundaries), len(key_types)
     lower = np.zeros((nb, ncols), dtype=np.uint64)
     upper = np.zeros((nb, ncols), dtype=np.uint64)
@@ -155,9 +157,35 @@ def normalize_boundaries(boundaries: Sequence[tuple], key_types: Sequence[int],
             if c >= len(b):
                 flags[i, c] = FLAG_STOP
                 continue
+            if key_types[c] is None:
+                flags[i, c] = FLAG_AFTER_ALL if b[c] is None else 0
+                continue
             lo, up, fl = normalize_boundary_value(b[c], key_types[c], bool(descending[c]))
             lower[i, c], upper[i, c], flags[i, c] = lo, up, fl
     return lower, upper, flags
+
+
+def pack_string_components(boundaries: Sequence[tuple], c: int):
+    """Component ``c`` of every boundary tuple as an Arrow-binary-like pair
+    (offsets int64[nb+1], bytes uint8[]); missing and None components are empty."""
+    vals = []
+    for b in boundaries:
+        if not isinstance(b, (tuple, list)):
+            b = (b,)
+        v = b[c] if c < len(b) else None
+        if v is None:
+            vals.append(b"")
+        elif isinstance(v, str):
+            vals.append(v.encode("utf-8"))
+        elif isinstance(v, (bytes, bytearray, memoryview)):
+            vals.append(bytes(v))
+        else:
+            raise TypeError(f"boundary component {v!r} does not compare with a string key column")
+    off = np.zeros(len(vals) + 1, dtype=np.int64)
+    if vals:
+        off[1:] = np.cumsum([len(v) for v in vals])
+    blob = np.frombuffer(b"".join(vals), dtype=np.uint8).copy() if off[-1] else np.zeros(0, np.uint8)
+    return off, blob
 
 
 def last_class_threshold(key_type: int, null_count: int):

@@ -349,6 +349,39 @@ int xchg_partition_bounds_bytes(const int64_t* sorted_offsets, const uint8_t* so
                                 const int64_t* bound_offsets, const uint8_t* bound_data,
                                 const uint8_t* bound_flags, int nb, int descending,
                                 uint64_t* cuts_out, void* stream);
+/*
+ * find_partition_index for key TUPLES that mix numeric and string / binary columns (the
+ * reference narrows [left, right) column by column whatever their types, util.py:757-802).
+ * cols_host: HOST array of ncols descriptors.  kind 0 = numeric: `norm` holds the column's n
+ * radix keys in sorted order, lower / upper / flags entries [b * ncols + c] as for
+ * xchg_partition_bounds; kind 1 = string: the SORTED column (offsets, data, validity) and
+ * the boundary strings of that column packed like an Arrow binary array (bound_offsets nb + 1
+ * entries, bound_data); of flags only bit1 (tuple ended) and bit2 (None component: equals the
+ * null rows, which hold NULL_SENTINEL) are read.  Descending columns replay numpy's probes
+ * over the reversed view.  cuts_out: nb uint64, device.
+ */
+typedef struct {
+  int32_t kind;             /* 0 numeric, 1 string / binary */
+  int32_t descending;
+  const uint64_t* norm;     /* kind 0 */
+  uint64_t last_threshold;  /* kind 0: radix keys >= this are the NaN / null class ... */
+  int32_t has_last;         /* ... when has_last != 0 */
+  int32_t reserved;
+  const int64_t* offsets;   /* kind 1: n + 1 byte offsets */
+  const uint8_t* data;
+  const uint8_t* validity;  /* may be NULL */
+  const int64_t* bound_offsets;
+  const uint8_t* bound_data;
+} xchg_mixed_col;
+int xchg_partition_bounds_mixed(const xchg_mixed_col* cols_host, int ncols, uint64_t n,
+                                const uint64_t* lower, const uint64_t* upper, const uint8_t* flags,
+                                int nb, int first_descending, uint64_t* cuts_out, void* stream);
+/* xchg_assign_partitions for such tuples: per ROW of the UNSORTED columns (kind 0: `norm` holds
+ * the radix keys in row order; kind 1: the column as stored).  counts_out may be NULL. */
+int xchg_assign_partitions_mixed(const xchg_mixed_col* cols_host, int ncols, uint64_t n,
+                                 const uint64_t* lower, const uint64_t* upper, const uint8_t* flags,
+                                 int nb, int first_descending, uint32_t* dest_out, uint64_t* counts_out,
+                                 void* stream);
 /* The same rule per row of an UNSORTED string column (see xchg_assign_partitions). */
 int xchg_assign_partitions_bytes(const int64_t* offsets, const uint8_t* data, const uint8_t* validity,
                                  uint64_t n, const int64_t* bound_offsets, const uint8_t* bound_data,

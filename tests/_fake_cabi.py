@@ -1057,6 +1057,156 @@ class FakeLib:
                 out[b] = n - mn
         return 0
 
+    # -- key tuples with string columns ------------------------------------------------
+    class _Last:
+        """NULL_SENTINEL of the reference (util.py:67-89): greater than every value, equal
+        to itself only."""
+
+        def __eq__(self, o):
+            return isinstance(o, type(self))
+
+        def __lt__(self, o):
+            return False
+
+        def __le__(self, o):
+            return isinstance(o, type(self))
+
+        def __gt__(self, o):
+            return not self.__le__(o)
+
+        def __ge__(self, o):
+            return True
+
+        __hash__ = object.__hash__
+
+    def _mixed_inputs(self, cols, ncols, n, nb):
+        out = []
+        for c in range(ncols):
+            d = cols[c]
+            if d.kind == 1:
+                rows = self._rows_bytes(d.offsets, d.data, n)
+                valid = (_bits(d.validity, 0, np.arange(n, dtype=np.int64)) if d.validity and n
+                         else np.ones(n, bool))
+                out.append(("s", bool(d.descending), rows, valid, self._rows_bytes(d.bound_offsets, d.bound_data, nb)))
+            else:
+                out.append(("n", bool(d.descending), _arr(d.norm, np.uint64, n), int(d.last_threshold),
+                            bool(d.has_last)))
+        return out
+
+    def xchg_partition_bounds_mixed(self, cols, ncols, n, lower, upper, flags, nb, first_desc, cuts, stream):
+        """Independent statement: string columns as the reference sees them -- object arrays
+        with NULL_SENTINEL, numpy.searchsorted with the reversing sorter for descending
+        columns (util.py:761-802); numeric columns through xchg_partition_bounds' own
+        narrowing, one column at a time."""
+        if nb == 0:
+            return 0
+        info = self._mixed_inputs(cols, ncols, n, nb)
+        fl_a = _arr(flags, np.uint8, nb * ncols) if _addr(flags) else np.zeros(nb * ncols, np.uint8)
+        out = _arr(cuts, np.uint64, nb)
+        last = self._Last()
+        for b in range(nb):
+            lo, hi, early = 0, n, False
+            for c in range(ncols):
+                if lo == hi:
+                    early = True
+                    break
+                f = int(fl_a[b * ncols + c])
+                if f & 2:
+                    break
+                if info[c][0] == "s":
+                    _, desc, rows, valid, bounds = info[c]
+                    vals = np.empty(hi - lo, dtype=object)
+                    for j in range(lo, hi):
+                        vals[j - lo] = rows[j] if valid[j] else last
+                    key = last if (f & 4) else bounds[b]
+                    m = hi - lo
+                    if desc:
+                        srt = np.arange(m - 1, -1, -1)
+                        nl = lo + (m - int(np.searchsorted(vals, key, side="right", sorter=srt)))
+                        nh = lo + (m - int(np.searchsorted(vals, key, side="left", sorter=srt)))
+                    else:
+                        nl = lo + int(np.searchsorted(vals, key, side="left"))
+                        nh = lo + int(np.searchsorted(vals, key, side="right"))
+                    lo, hi = nl, nh
+                    continue
+                # one numeric column: run the numeric entry point on the run [lo, hi)
+                _, desc, norm, thr, has_last = info[c]
+                seg = np.ascontiguousarray(norm[lo:hi])
+                one = (ctypes.c_void_p * 1)(seg.ctypes.data)
+                cd = (ctypes.c_uint8 * 1)(int(desc))
+                th = (ctypes.c_uint64 * 1)(thr)
+                hl = (ctypes.c_uint8 * 1)(int(has_last))
+                e = b * ncols + c
+                L = np.array([_arr(lower, np.uint64, nb * ncols)[e]], dtype=np.uint64)
+                U = np.array([_arr(upper, np.uint64, nb * ncols)[e]], dtype=np.uint64)
+                F = np.array([f], dtype=np.uint8)
+                res = np.zeros(2, dtype=np.uint64)
+                # first_desc=0 -> left edge, first_desc=1 -> right edge of the equal range
+                for side in (0, 1):
+                    self.xchg_partition_bounds(one, cd, th, hl, 1, hi - lo, L.ctypes.data, U.ctypes.data,
+                                               F.ctypes.data, 1, side, res[side:].ctypes.data, None)
+                lo, hi = lo + int(res[0]), lo + int(res[1])
+            out[b] = hi if (early or first_desc) else lo
+        return 0
+
+    def xchg_assign_partitions_mixed(self, cols, ncols, n, lower, upper, flags, nb, first_desc, dest, counts,
+                                     stream):
+        """Per row: count the boundaries the row is right of (tuple compare in sort order)."""
+        if _addr(counts):
+            _arr(counts, np.uint64, nb + 1)[:] = 0
+        if n == 0:
+            return 0
+        info = self._mixed_inputs(cols, ncols, n, nb)
+        lo_a = _arr(lower, np.uint64, nb * ncols)
+        up_a = _arr(upper, np.uint64, nb * ncols)
+        fl_a = _arr(flags, np.uint8, nb * ncols) if _addr(flags) else np.zeros(nb * ncols, np.uint8)
+
+        def cmp(i, b):
+            for c in range(ncols):
+                f = int(fl_a[b * ncols + c])
+                if f & 2:
+                    return 0
+                if info[c][0] == "s":
+                    _, desc, rows, valid, bounds = info[c]
+                    none = bool(f & 4)
+                    if not desc:
+                        if not valid[i]:
+                            if none:
+                                continue
+                            return 1
+                        if none:
+                            return -1
+                    elif none or not valid[i]:
+                        return 1
+                    r = (rows[i] > bounds[b]) - (rows[i] < bounds[b])
+                    if r:
+                        return -r if desc else r
+                    continue
+                _, desc, norm, _, _ = info[c]
+                if f & 4:
+                    return 1 if desc else -1
+                t = int(norm[i])
+                if t < int(lo_a[b * ncols + c]):
+                    return -1
+                if (f & 1) or t > int(up_a[b * ncols + c]):
+                    return 1
+            return 0
+
+        d = np.zeros(n, dtype=np.uint32)
+        for i in range(n):
+            cnt = 0
+            for b in range(nb):
+                c = cmp(i, b)
+                if (c > 0) if first_desc else (c >= 0):
+                    cnt += 1
+                else:
+                    break
+            d[i] = cnt
+        _arr(dest, np.uint32, n)[:] = d
+        if _addr(counts):
+            _arr(counts, np.uint64, nb + 1)[:] = np.bincount(d, minlength=nb + 1).astype(np.uint64)
+        return 0
+
     def xchg_assign_partitions_bytes(self, off, data, validity, n, boff, bdata, bflags, nb, desc, dest, counts,
                                      stream):
         if _addr(counts):
