@@ -113,6 +113,8 @@ _SIGNATURES = {
     "xchg_gather_rows": (c_int, [_P, c_uint32, _P, c_uint64, _P, _P]),
     "xchg_gather_rows_multi": (c_int, [_P, c_uint32, _P, c_int, ctypes.POINTER(c_uint64), ctypes.POINTER(c_uint64),
                                        ctypes.POINTER(c_void_p), _P]),
+    "xchg_host_register": (c_int, [_P, c_uint64, ctypes.POINTER(c_int)]),
+    "xchg_host_unregister": (c_int, [_P]),
     "xchg_offsets_widen": (c_int, [_P, c_uint64, c_int64, _P, _P]),
     "xchg_offsets_narrow": (c_int, [_P, c_uint64, _P, _P]),
     "xchg_offsets_uniform32": (c_int, [c_uint64, c_uint32, _P, _P]),

@@ -159,3 +159,32 @@ extern "C" int xchg_set_gather_ctas_per_sm(int ctas_per_sm) {
   g_gather_ctas_per_sm.store(ctas_per_sm);
   return XCHG_OK;
 }
+
+// ---- caller-owned host memory ---------------------------------------------------------
+extern "C" int xchg_host_register(const void* ptr, uint64_t bytes, int* already_out) {
+  XCHG_REQUIRE(ptr != nullptr && bytes > 0, "NULL / empty host range");
+  if (already_out) *already_out = 0;
+  cudaError_t e = cudaHostRegister(const_cast<void*>(ptr), (size_t)bytes, cudaHostRegisterDefault);
+  if (e == cudaErrorHostMemoryAlreadyRegistered) {
+    cudaGetLastError();  // not an error for the caller: clear it
+    if (already_out) *already_out = 1;
+    return XCHG_OK;
+  }
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    // read-only mappings (a sealed shared-memory object, an mmap'ed file) need the flag
+    e = cudaHostRegister(const_cast<void*>(ptr), (size_t)bytes, cudaHostRegisterReadOnly);
+  }
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    xchg_set_error("cudaHostRegister(%p, %llu): %s", ptr, (unsigned long long)bytes, cudaGetErrorString(e));
+    return XCHG_ERR_CUDA;
+  }
+  return XCHG_OK;
+}
+
+extern "C" int xchg_host_unregister(const void* ptr) {
+  XCHG_REQUIRE(ptr != nullptr, "NULL host pointer");
+  XCHG_CUDA_TRY(cudaHostUnregister(const_cast<void*>(ptr)));
+  return XCHG_OK;
+}

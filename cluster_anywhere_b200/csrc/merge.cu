@@ -9,11 +9,14 @@
 // ceil(log2 K) times.
 //
 // Rounds of pairwise merges (runs 0+1, 2+3, ...; an odd run out is carried over), each
-// round one launch over all pairs.  A CTA produces one 4096-element tile of one pair's
-// output: two merge-path searches in global memory bound the tile's slices of the left
-// and right run, both slices are staged in shared memory, every thread finds its own
-// diagonal there, merges 16 elements sequentially (left run wins ties: stable) into
-// registers, and the tile leaves through shared memory as coalesced stores.
+// round two launches over all pairs.  k_merge_splits: one thread per 4096-element output
+// tile does the merge-path search in global memory (~log2(n) dependent loads) that bounds
+// the tile's slices of the left and right run; doing this inside the merge CTAs put ~20 us
+// of load latency in front of every tile (measured: 1.5 TB/s of algorithmic bytes).
+// k_merge_pairs: a CTA stages both slices of its tile in shared memory, every thread finds
+// its own diagonal there, merges 16 elements sequentially (left run wins ties: stable; the
+// two head keys live in registers, one shared-memory load per step) and the tile leaves
+// through shared memory as coalesced stores.
 // Algorithmic bytes: 24 B per element and round (12 read + 12 written).
 #include <algorithm>
 
@@ -49,26 +52,51 @@ __device__ __forceinline__ uint32_t merge_path(const uint64_t* __restrict__ a, u
   return lo;
 }
 
+__device__ __forceinline__ int pair_of_tile(const MergePairs& mp, uint32_t tile) {
+  int j = 0;
+  while (j + 1 < mp.npairs && mp.tile0[j + 1] <= tile) ++j;  // <= 64 pairs: a short walk
+  return j;
+}
+
+// splits[t] = elements of the left run among the outputs before tile t of its pair
+__global__ void __launch_bounds__(128)
+k_merge_splits(const uint64_t* __restrict__ kin, MergePairs mp, uint32_t tiles, uint32_t* __restrict__ splits) {
+  const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
+  if (tile >= tiles) return;
+  const int j = pair_of_tile(mp, tile);
+  const uint64_t* A = kin + mp.a0[j];
+  const uint32_t na = mp.na[j], nb = mp.nb[j];
+  splits[tile] = merge_path(A, na, A + na, nb, (tile - mp.tile0[j]) * (uint32_t)MG_TILE);
+}
+
+template <bool PRESPLIT>
 __global__ void __launch_bounds__(MG_THREADS)
 k_merge_pairs(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin,
-              uint64_t* __restrict__ kout, uint32_t* __restrict__ vout, MergePairs mp) {
+              uint64_t* __restrict__ kout, uint32_t* __restrict__ vout, MergePairs mp,
+              const uint32_t* __restrict__ splits) {
   extern __shared__ __align__(16) uint8_t mg_smem[];
   uint64_t* sk = reinterpret_cast<uint64_t*>(mg_smem);
   uint32_t* sv = reinterpret_cast<uint32_t*>(mg_smem + (size_t)MG_TILE * 8);
   __shared__ uint32_t s_split[2];
   const int tid = threadIdx.x;
   const uint32_t tile = blockIdx.x;
-  int j = 0;
-  while (j + 1 < mp.npairs && mp.tile0[j + 1] <= tile) ++j;  // <= 64 pairs: a short walk
+  const int j = pair_of_tile(mp, tile);
   const uint64_t a0 = mp.a0[j];
   const uint32_t na = mp.na[j], nb = mp.nb[j];
   const uint64_t* A = kin + a0;
   const uint64_t* B = A + na;
   const uint32_t d0 = (tile - mp.tile0[j]) * (uint32_t)MG_TILE;
   const uint32_t d1 = min(d0 + (uint32_t)MG_TILE, na + nb);
-  if (tid < 2) s_split[tid] = merge_path(A, na, B, nb, tid == 0 ? d0 : d1);
-  __syncthreads();
-  const uint32_t as = s_split[0], ae = s_split[1];
+  uint32_t as, ae;
+  if (PRESPLIT) {
+    as = splits[tile];
+    ae = (tile + 1 < mp.tile0[j + 1]) ? splits[tile + 1] : na;  // the pair's last tile ends its left run
+  } else {
+    if (tid < 2) s_split[tid] = merge_path(A, na, B, nb, tid == 0 ? d0 : d1);
+    __syncthreads();
+    as = s_split[0];
+    ae = s_split[1];
+  }
   const uint32_t bs = d0 - as, be = d1 - ae;
   const uint32_t la = ae - as, lb = be - bs;  // la + lb = d1 - d0 <= MG_TILE
   // stage: A slice at [0, la), B slice at [la, la + lb)
@@ -88,17 +116,20 @@ k_merge_pairs(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin
   uint32_t ib = my0 - ia;
   uint64_t rk[MG_ITEMS];
   uint32_t rv[MG_ITEMS];
+  uint32_t rs[MG_ITEMS];
+  // head keys of both slices in registers; a read one past a slice's end stays inside the
+  // staging area (MG_TILE keys, then the values) and is never used
+  uint64_t ka = sk[ia], kb = sk[la + ib];
 #pragma unroll
   for (int i = 0; i < MG_ITEMS; ++i) {
-    if (my0 + i < my1) {
-      const bool take_a = ib >= lb || (ia < la && sk[ia] <= sk[la + ib]);
-      const uint32_t src = take_a ? ia : la + ib;
-      rk[i] = sk[src];
-      rv[i] = sv[src];
-      ia += take_a ? 1u : 0u;
-      ib += take_a ? 0u : 1u;
-    }
+    const bool take_a = ib >= lb || (ia < la && ka <= kb);
+    rk[i] = take_a ? ka : kb;
+    rs[i] = take_a ? ia : la + ib;
+    if (take_a) ka = sk[++ia];
+    else kb = sk[la + (++ib)];
   }
+#pragma unroll
+  for (int i = 0; i < MG_ITEMS; ++i) rv[i] = sv[min(rs[i], (uint32_t)MG_TILE - 1)];
   __syncthreads();
 #pragma unroll
   for (int i = 0; i < MG_ITEMS; ++i) {
@@ -135,6 +166,9 @@ k_check_runs(const uint64_t* __restrict__ keys, uint64_t n, const uint64_t* __re
   if (__syncthreads_or(bad) && threadIdx.x == 0) atomicOr(flag, 1u);
 }
 
+// tile splits of one round: at most n / MG_TILE + one partial tile per pair
+uint64_t merge_split_bytes(uint64_t n) { return xchg_align_up((n / MG_TILE + MG_MAX_PAIRS + 2) * 4, 256); }
+
 }  // namespace
 
 extern "C" int xchg_merge_workspace_bytes(uint64_t n, uint64_t* bytes_out) {
@@ -143,7 +177,8 @@ extern "C" int xchg_merge_workspace_bytes(uint64_t n, uint64_t* bytes_out) {
     xchg_set_error("n=%llu exceeds XCHG_MAX_ROWS", (unsigned long long)n);
     return XCHG_ERR_LIMIT;
   }
-  *bytes_out = xchg_align_up(n * 8, 256) + xchg_align_up(n * 4, 256) + 256 + (2 * MG_MAX_PAIRS + 2) * 8;
+  *bytes_out = xchg_align_up(n * 8, 256) + xchg_align_up(n * 4, 256) + 256 + (2 * MG_MAX_PAIRS + 2) * 8 +
+               merge_split_bytes(n);
   return XCHG_OK;
 }
 
@@ -167,8 +202,9 @@ extern "C" int xchg_merge_sorted_runs(const uint64_t* keys_in, const uint32_t* v
   for (int r = 0; r < nruns; ++r)
     XCHG_REQUIRE(run_start_host[r] <= run_start_host[r + 1], "run_start_host must not decrease");
 
-  XCHG_ONCE_PER_DEVICE(XCHG_CUDA_TRY(cudaFuncSetAttribute(k_merge_pairs, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                          (int)MG_SMEM)));
+  XCHG_ONCE_PER_DEVICE(
+      XCHG_CUDA_TRY(cudaFuncSetAttribute(k_merge_pairs<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MG_SMEM));
+      XCHG_CUDA_TRY(cudaFuncSetAttribute(k_merge_pairs<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MG_SMEM)));
   // runs of this round (empty runs dropped: they merge to nothing)
   uint64_t starts[2 * MG_MAX_PAIRS + 1];
   int k = 0;
@@ -181,6 +217,12 @@ extern "C" int xchg_merge_sorted_runs(const uint64_t* keys_in, const uint32_t* v
   uint32_t* ws_vals = (uint32_t*)(base + xchg_align_up(n * 8, 256));
   int rounds = 0;
   for (int kk = k; kk > 1; kk = (kk + 1) / 2) ++rounds;
+  // tile splits live behind the run starts; without a workspace that holds them (a caller
+  // merging two runs may pass none) the merge CTAs search for themselves
+  const uint64_t fixed = xchg_align_up(n * 8, 256) + xchg_align_up(n * 4, 256) + 256 + (2 * MG_MAX_PAIRS + 2) * 8;
+  uint32_t* d_splits = nullptr;
+  if (workspace && (uint64_t)(base - (uint8_t*)workspace) + fixed + merge_split_bytes(n) <= workspace_bytes)
+    d_splits = (uint32_t*)(base + fixed);
 
   if (unsorted_flag_out) {
     // run starts to the device: the tail of the workspace
@@ -207,7 +249,9 @@ extern "C" int xchg_merge_sorted_runs(const uint64_t* keys_in, const uint32_t* v
       mp.nb[0] = 0;
       mp.tile0[0] = 0;
       mp.tile0[1] = (uint32_t)((n + MG_TILE - 1) / MG_TILE);
-      XCHG_LAUNCH(XK_MERGE, s, k_merge_pairs<<<mp.tile0[1], MG_THREADS, MG_SMEM, s>>>(keys_in, nullptr, keys_out, vals_out, mp));
+      XCHG_LAUNCH(XK_MERGE, s,
+                  k_merge_pairs<false><<<mp.tile0[1], MG_THREADS, MG_SMEM, s>>>(keys_in, nullptr, keys_out, vals_out, mp,
+                                                                               nullptr));
       XCHG_LAUNCH_CHECK();
     }
     return XCHG_OK;
@@ -248,7 +292,13 @@ extern "C" int xchg_merge_sorted_runs(const uint64_t* keys_in, const uint32_t* v
     }
     mp.tile0[mp.npairs] = tiles;
     next[nk] = n;
-    XCHG_LAUNCH(XK_MERGE, s, k_merge_pairs<<<tiles, MG_THREADS, MG_SMEM, s>>>(kin, vin, ko, vo, mp));
+    if (d_splits) {
+      XCHG_LAUNCH(XK_MERGE, s, k_merge_splits<<<(tiles + 127) / 128, 128, 0, s>>>(kin, mp, tiles, d_splits));
+      XCHG_LAUNCH_CHECK();
+      XCHG_LAUNCH(XK_MERGE, s, k_merge_pairs<true><<<tiles, MG_THREADS, MG_SMEM, s>>>(kin, vin, ko, vo, mp, d_splits));
+    } else {
+      XCHG_LAUNCH(XK_MERGE, s, k_merge_pairs<false><<<tiles, MG_THREADS, MG_SMEM, s>>>(kin, vin, ko, vo, mp, nullptr));
+    }
     XCHG_LAUNCH_CHECK();
     for (int i = 0; i <= nk; ++i) starts[i] = next[i];
     k = nk;

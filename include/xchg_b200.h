@@ -696,6 +696,17 @@ int xchg_bitmap_pack(const uint8_t* in_bytes, uint64_t n, uint8_t* out, uint64_t
                      void* stream);
 int xchg_offsets_rebase(const int64_t* in, uint64_t count, int64_t base, int64_t* out, void* stream);
 
+/*
+ * Caller-owned host memory (the wire bytes of a block as they sit in the object store,
+ * python/ray/_private/arrow_serialization.py:785-809): page-lock [ptr, ptr + bytes) so that
+ * host->device copies out of it are asynchronous DMA instead of the driver's staged copy of
+ * pageable memory.  ptr / bytes must cover whole pages.  A range that is already registered is
+ * not an error (*already_out = 1; the caller must then NOT unregister it).  Read-only mappings
+ * are registered read-only.
+ */
+int xchg_host_register(const void* ptr, uint64_t bytes, int* already_out);
+int xchg_host_unregister(const void* ptr);
+
 #ifdef __cplusplus
 }
 #endif

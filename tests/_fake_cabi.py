@@ -1057,6 +1057,12 @@ class FakeLib:
                 out[b] = n - mn
         return 0
 
+    def xchg_host_register(self, ptr, nbytes, already_out):
+        return 0  # host memory is host memory here
+
+    def xchg_host_unregister(self, ptr):
+        return 0
+
     # -- key tuples with string columns ------------------------------------------------
     class _Last:
         """NULL_SENTINEL of the reference (util.py:67-89): greater than every value, equal
