@@ -28,7 +28,14 @@ constexpr int MG_THREADS = 256;
 constexpr int MG_ITEMS = 16;
 constexpr int MG_TILE = MG_THREADS * MG_ITEMS;
 constexpr int MG_MAX_PAIRS = 64;
-constexpr size_t MG_SMEM = (size_t)MG_TILE * 12;
+// Staging slot of tile element e.  A thread owns 16 consecutive elements; unpadded, the 32
+// lanes of a warp would hit one bank (stride 16 x 8 B = 128 B): ncu showed 71 % of the
+// shared-memory wavefronts as bank conflicts and the L1 pipe at 97 %.  One spare slot per 16
+// makes the stride 17: conflict-free for the register -> staging writes and for runs that
+// come mostly from one side.
+__host__ __device__ constexpr uint32_t mg_slot(uint32_t e) { return e + (e >> 4); }
+constexpr uint32_t MG_SLOTS = mg_slot(MG_TILE);
+constexpr size_t MG_SMEM = (size_t)MG_SLOTS * 12;
 
 struct MergePairs {
   // pair j merges A = [a0, a0 + na) and B = [a0 + na, a0 + na + nb) of the input into the
@@ -52,6 +59,17 @@ __device__ __forceinline__ uint32_t merge_path(const uint64_t* __restrict__ a, u
   return lo;
 }
 
+// the same search on the two slices staged in shared memory (A at elements [0, la), B behind it)
+__device__ __forceinline__ uint32_t merge_path_staged(const uint64_t* sk, uint32_t la, uint32_t lb, uint32_t diag) {
+  uint32_t lo = diag > lb ? diag - lb : 0, hi = min(diag, la);
+  while (lo < hi) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (sk[mg_slot(mid)] <= sk[mg_slot(la + diag - 1 - mid)]) lo = mid + 1;
+    else hi = mid;
+  }
+  return lo;
+}
+
 __device__ __forceinline__ int pair_of_tile(const MergePairs& mp, uint32_t tile) {
   int j = 0;
   while (j + 1 < mp.npairs && mp.tile0[j + 1] <= tile) ++j;  // <= 64 pairs: a short walk
@@ -69,14 +87,17 @@ k_merge_splits(const uint64_t* __restrict__ kin, MergePairs mp, uint32_t tiles, 
   splits[tile] = merge_path(A, na, A + na, nb, (tile - mp.tile0[j]) * (uint32_t)MG_TILE);
 }
 
-template <bool PRESPLIT>
-__global__ void __launch_bounds__(MG_THREADS)
+// CHECK (first round, on request): *flag |= 1 when a run is not ascending.  Every element of
+// both runs is staged by exactly one tile, so comparing neighbours in the staging area (and a
+// slice's first element with its predecessor in global memory) sees every adjacent pair.
+template <bool PRESPLIT, bool CHECK>
+__global__ void __launch_bounds__(MG_THREADS, 4)
 k_merge_pairs(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin,
               uint64_t* __restrict__ kout, uint32_t* __restrict__ vout, MergePairs mp,
-              const uint32_t* __restrict__ splits) {
+              const uint32_t* __restrict__ splits, uint32_t* __restrict__ flag) {
   extern __shared__ __align__(16) uint8_t mg_smem[];
   uint64_t* sk = reinterpret_cast<uint64_t*>(mg_smem);
-  uint32_t* sv = reinterpret_cast<uint32_t*>(mg_smem + (size_t)MG_TILE * 8);
+  uint32_t* sv = reinterpret_cast<uint32_t*>(mg_smem + (size_t)MG_SLOTS * 8);
   __shared__ uint32_t s_split[2];
   const int tid = threadIdx.x;
   const uint32_t tile = blockIdx.x;
@@ -97,55 +118,86 @@ k_merge_pairs(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin
     as = s_split[0];
     ae = s_split[1];
   }
+  // merge-path splits of sorted runs never decrease and never advance by more than a tile; runs
+  // that are NOT sorted can break both: keep the slices inside the staging area and say so
+  bool bad = false;
+  if (ae < as || ae - as > d1 - d0) {
+    bad = true;
+    ae = ae < as ? as : as + (d1 - d0);
+  }
   const uint32_t bs = d0 - as, be = d1 - ae;
   const uint32_t la = ae - as, lb = be - bs;  // la + lb = d1 - d0 <= MG_TILE
-  // stage: A slice at [0, la), B slice at [la, la + lb)
-  for (uint32_t i = tid; i < la; i += MG_THREADS) {
-    sk[i] = A[as + i];
-    sv[i] = vin ? vin[a0 + as + i] : (uint32_t)(a0 + as + i);
-  }
-  for (uint32_t i = tid; i < lb; i += MG_THREADS) {
-    sk[la + i] = B[bs + i];
-    sv[la + i] = vin ? vin[a0 + na + bs + i] : (uint32_t)(a0 + na + bs + i);
-  }
-  __syncthreads();
+  // stage: A slice at [0, la), B slice at [la, la + lb).  A fixed trip count and cp.async keep
+  // all 16 loads of a thread in flight at once (a loop over the two slices with a load and a
+  // shared-memory store per step went to memory 16 times in a row: ~29 us per tile)
   const uint32_t total = la + lb;
+  const uint32_t sk_s = (uint32_t)__cvta_generic_to_shared(sk);
+  const uint32_t sv_s = (uint32_t)__cvta_generic_to_shared(sv);
+#pragma unroll
+  for (int r = 0; r < MG_ITEMS; ++r) {
+    const uint32_t i = (uint32_t)tid + (uint32_t)r * MG_THREADS;
+    if (i < total) {
+      // position of staged element i in the round's input
+      const uint64_t g = i < la ? a0 + as + i : a0 + na + bs + (i - la);
+      const uint32_t p = mg_slot(i);
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sk_s + p * 8u), "l"(kin + g) : "memory");
+      if (vin) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sv_s + p * 4u), "l"(vin + g) : "memory");
+      else sv[p] = (uint32_t)g;
+    }
+  }
+  asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+  if (CHECK) {
+#pragma unroll
+    for (int r = 0; r < MG_ITEMS; ++r) {
+      const uint32_t i = (uint32_t)tid + (uint32_t)r * MG_THREADS;
+      if (i < total && i != 0 && i != la) bad |= sk[mg_slot(i - 1)] > sk[mg_slot(i)];
+    }
+    if (tid == 0 && la > 0 && as > 0) bad |= A[as - 1] > sk[0];
+    if (tid == 1 && lb > 0 && bs > 0) bad |= B[bs - 1] > sk[mg_slot(la)];
+    if (__syncthreads_or(bad) && tid == 0) atomicOr(flag, 1u);
+  }
   const uint32_t my0 = min((uint32_t)tid * MG_ITEMS, total);
   const uint32_t my1 = min(my0 + MG_ITEMS, total);
-  uint32_t ia = merge_path(sk, la, sk + la, lb, my0);
+  uint32_t ia = merge_path_staged(sk, la, lb, my0);
   uint32_t ib = my0 - ia;
   uint64_t rk[MG_ITEMS];
   uint32_t rv[MG_ITEMS];
   uint32_t rs[MG_ITEMS];
-  // head keys of both slices in registers; a read one past a slice's end stays inside the
-  // staging area (MG_TILE keys, then the values) and is never used
-  uint64_t ka = sk[ia], kb = sk[la + ib];
+  // head keys of both slices in registers; a read past a slice's end stays inside the
+  // staging area (key slots, then the values) and is never used
+  uint64_t ka = sk[mg_slot(ia)], kb = sk[mg_slot(la + ib)];
 #pragma unroll
   for (int i = 0; i < MG_ITEMS; ++i) {
     const bool take_a = ib >= lb || (ia < la && ka <= kb);
     rk[i] = take_a ? ka : kb;
     rs[i] = take_a ? ia : la + ib;
-    if (take_a) ka = sk[++ia];
-    else kb = sk[la + (++ib)];
+    if (take_a) ka = sk[mg_slot(++ia)];
+    else kb = sk[mg_slot(la + (++ib))];
   }
 #pragma unroll
-  for (int i = 0; i < MG_ITEMS; ++i) rv[i] = sv[min(rs[i], (uint32_t)MG_TILE - 1)];
+  for (int i = 0; i < MG_ITEMS; ++i) rv[i] = sv[mg_slot(min(rs[i], (uint32_t)MG_TILE - 1))];
   __syncthreads();
 #pragma unroll
   for (int i = 0; i < MG_ITEMS; ++i) {
     if (my0 + i < my1) {
-      sk[my0 + i] = rk[i];
-      sv[my0 + i] = rv[i];
+      sk[mg_slot(my0 + i)] = rk[i];
+      sv[mg_slot(my0 + i)] = rv[i];
     }
   }
   __syncthreads();
-  for (uint32_t i = tid; i < total; i += MG_THREADS) {
-    kout[a0 + d0 + i] = sk[i];
-    vout[a0 + d0 + i] = sv[i];
+#pragma unroll
+  for (int r = 0; r < MG_ITEMS; ++r) {
+    const uint32_t i = (uint32_t)tid + (uint32_t)r * MG_THREADS;
+    if (i < total) {
+      kout[a0 + d0 + i] = sk[mg_slot(i)];
+      vout[a0 + d0 + i] = sv[mg_slot(i)];
+    }
   }
 }
 
-// *flag |= 1 when some run is not sorted ascending (callers then fall back to a full sort)
+// *flag |= 1 when some run is not sorted ascending (callers then fall back to a full sort).
+// Only for a single run, which is copied; merges check while they stage (k_merge_pairs<., true>).
 __global__ void __launch_bounds__(256)
 k_check_runs(const uint64_t* __restrict__ keys, uint64_t n, const uint64_t* __restrict__ run_start, int nruns,
              uint32_t* __restrict__ flag) {
@@ -203,8 +255,10 @@ extern "C" int xchg_merge_sorted_runs(const uint64_t* keys_in, const uint32_t* v
     XCHG_REQUIRE(run_start_host[r] <= run_start_host[r + 1], "run_start_host must not decrease");
 
   XCHG_ONCE_PER_DEVICE(
-      XCHG_CUDA_TRY(cudaFuncSetAttribute(k_merge_pairs<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MG_SMEM));
-      XCHG_CUDA_TRY(cudaFuncSetAttribute(k_merge_pairs<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MG_SMEM)));
+      XCHG_CUDA_TRY(cudaFuncSetAttribute(k_merge_pairs<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MG_SMEM));
+      XCHG_CUDA_TRY(cudaFuncSetAttribute(k_merge_pairs<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MG_SMEM));
+      XCHG_CUDA_TRY(cudaFuncSetAttribute(k_merge_pairs<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MG_SMEM));
+      XCHG_CUDA_TRY(cudaFuncSetAttribute(k_merge_pairs<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MG_SMEM)));
   // runs of this round (empty runs dropped: they merge to nothing)
   uint64_t starts[2 * MG_MAX_PAIRS + 1];
   int k = 0;
@@ -224,7 +278,8 @@ extern "C" int xchg_merge_sorted_runs(const uint64_t* keys_in, const uint32_t* v
   if (workspace && (uint64_t)(base - (uint8_t*)workspace) + fixed + merge_split_bytes(n) <= workspace_bytes)
     d_splits = (uint32_t*)(base + fixed);
 
-  if (unsorted_flag_out) {
+  if (unsorted_flag_out && rounds == 0) {
+    // a single run is copied, not merged: its order is checked by a pass of its own.
     // run starts to the device: the tail of the workspace
     XCHG_REQUIRE(workspace != nullptr, "the sortedness check needs the workspace");
     uint64_t need = xchg_align_up(n * 8, 256) + xchg_align_up(n * 4, 256);
@@ -250,8 +305,8 @@ extern "C" int xchg_merge_sorted_runs(const uint64_t* keys_in, const uint32_t* v
       mp.tile0[0] = 0;
       mp.tile0[1] = (uint32_t)((n + MG_TILE - 1) / MG_TILE);
       XCHG_LAUNCH(XK_MERGE, s,
-                  k_merge_pairs<false><<<mp.tile0[1], MG_THREADS, MG_SMEM, s>>>(keys_in, nullptr, keys_out, vals_out, mp,
-                                                                               nullptr));
+                  (k_merge_pairs<false, false><<<mp.tile0[1], MG_THREADS, MG_SMEM, s>>>(keys_in, nullptr, keys_out,
+                                                                                        vals_out, mp, nullptr, nullptr)));
       XCHG_LAUNCH_CHECK();
     }
     return XCHG_OK;
@@ -292,12 +347,23 @@ extern "C" int xchg_merge_sorted_runs(const uint64_t* keys_in, const uint32_t* v
     }
     mp.tile0[mp.npairs] = tiles;
     next[nk] = n;
+    const bool check = round == 1 && unsorted_flag_out != nullptr;  // every run takes part in round 1
     if (d_splits) {
       XCHG_LAUNCH(XK_MERGE, s, k_merge_splits<<<(tiles + 127) / 128, 128, 0, s>>>(kin, mp, tiles, d_splits));
       XCHG_LAUNCH_CHECK();
-      XCHG_LAUNCH(XK_MERGE, s, k_merge_pairs<true><<<tiles, MG_THREADS, MG_SMEM, s>>>(kin, vin, ko, vo, mp, d_splits));
+      if (check) {
+        XCHG_LAUNCH(XK_MERGE, s, (k_merge_pairs<true, true><<<tiles, MG_THREADS, MG_SMEM, s>>>(kin, vin, ko, vo, mp, d_splits,
+                                                                                             unsorted_flag_out)));
+      } else {
+        XCHG_LAUNCH(XK_MERGE, s, (k_merge_pairs<true, false><<<tiles, MG_THREADS, MG_SMEM, s>>>(kin, vin, ko, vo, mp, d_splits,
+                                                                                              nullptr)));
+      }
+    } else if (check) {
+      XCHG_LAUNCH(XK_MERGE, s, (k_merge_pairs<false, true><<<tiles, MG_THREADS, MG_SMEM, s>>>(kin, vin, ko, vo, mp, nullptr,
+                                                                                            unsorted_flag_out)));
     } else {
-      XCHG_LAUNCH(XK_MERGE, s, k_merge_pairs<false><<<tiles, MG_THREADS, MG_SMEM, s>>>(kin, vin, ko, vo, mp, nullptr));
+      XCHG_LAUNCH(XK_MERGE, s, (k_merge_pairs<false, false><<<tiles, MG_THREADS, MG_SMEM, s>>>(kin, vin, ko, vo, mp, nullptr,
+                                                                                             nullptr)));
     }
     XCHG_LAUNCH_CHECK();
     for (int i = 0; i <= nk; ++i) starts[i] = next[i];
