@@ -26,11 +26,26 @@ from .sort_key import SortKey
 
 
 def _device_sort(rt: dev.Runtime, dt: dev.DeviceTable, sort_key: SortKey, want_norm: bool):
-    return dev.sort_permutation(rt, dt, sort_key.get_columns(), sort_key.get_descending(), want_norm)
+    """-> (perm, norms); a string-run hint of the sort (dev.sort_permutation) rides on norms."""
+    hints = {}
+    perm, norms = dev.sort_permutation(rt, dt, sort_key.get_columns(), sort_key.get_descending(), want_norm, hints)
+    if "string_runs" in hints:
+        norms = _Norms(norms)
+        norms.string_runs = hints["string_runs"]
+    return perm, norms
+
+
+class _Norms(list):
+    """The radix-key list of a sort plus what else the sort learned about its key columns."""
+    string_runs = None
 
 
 def _presorted(sort_key: SortKey, norms):
-    """Primary key column -> its radix keys in output order (see dev.take_table)."""
+    """Primary key column -> how dev.take_table can build it without a random gather: its
+    radix keys in output order (numeric keys) or one source row per run of equal strings."""
+    runs = getattr(norms, "string_runs", None)
+    if runs is not None:
+        return {runs[0]: ("rows", runs[1])}
     if not norms or norms[0] is None:
         return None
     return {sort_key.get_columns()[0]: (norms[0], sort_key.get_descending()[0])}

@@ -180,6 +180,57 @@ k_lengths_scan(const int64_t* __restrict__ in_off, const uint32_t* __restrict__ 
   }
 }
 
+// The same two passes for callers that also want the rows' SOURCE spans kept: the first pass
+// stores in_off[idx[i]] and the row's length (into out_off[i + 1], which the second pass scans
+// in place), so in_off -- a random 16-byte read per row that costs a 64-128-byte DRAM fill -- is
+// touched once per take instead of three times (lengths, scan, data gather).
+__global__ void __launch_bounds__(SC_THREADS)
+k_spans_reduce(const int64_t* __restrict__ in_off, const uint32_t* __restrict__ idx, uint64_t n,
+               int64_t* __restrict__ src_start, int64_t* __restrict__ out_off, int64_t* __restrict__ tile_sums) {
+  __shared__ int64_t swarp[SC_THREADS / 32];
+  const uint64_t base = (uint64_t)blockIdx.x * SC_TILE;
+  int64_t sum = 0;
+#pragma unroll
+  for (int k = 0; k < SC_ITEMS; ++k) {
+    const uint64_t i = base + k * SC_THREADS + threadIdx.x;
+    if (i < n) {
+      const uint32_t r = idx[i];
+      const int64_t b = in_off[r], len = in_off[r + 1] - b;
+      src_start[i] = b;
+      out_off[i + 1] = len;
+      sum += len;
+    }
+  }
+  int64_t tot;
+  block_exclusive_scan(sum, &tot, swarp);
+  if (threadIdx.x == 0) tile_sums[blockIdx.x] = tot;
+}
+
+// out_off[i + 1] holds row i's length on entry and the end of row i on exit (every element is
+// read and written by the same thread)
+__global__ void __launch_bounds__(SC_THREADS)
+k_spans_scan(uint64_t n, const int64_t* __restrict__ tile_excl, int64_t* out_off) {
+  __shared__ int64_t swarp[SC_THREADS / 32];
+  const uint64_t base = (uint64_t)blockIdx.x * SC_TILE + (uint64_t)threadIdx.x * SC_ITEMS;
+  int64_t len[SC_ITEMS];
+  int64_t sum = 0;
+#pragma unroll
+  for (int k = 0; k < SC_ITEMS; ++k) {
+    const uint64_t i = base + k;
+    len[k] = i < n ? out_off[i + 1] : 0;
+    sum += len[k];
+  }
+  int64_t tot;
+  int64_t run = tile_excl[blockIdx.x] + block_exclusive_scan(sum, &tot, swarp);
+  if (blockIdx.x == 0 && threadIdx.x == 0) out_off[0] = 0;
+#pragma unroll
+  for (int k = 0; k < SC_ITEMS; ++k) {
+    const uint64_t i = base + k;
+    run += len[k];
+    if (i < n) out_off[i + 1] = run;
+  }
+}
+
 // ------------------------------------------------------------- row gather ---
 
 constexpr int GR_THREADS = 256;
@@ -208,7 +259,8 @@ __device__ void copy_big_row(const uint8_t* __restrict__ src, uint8_t* __restric
   for (int64_t k = done + threadIdx.x; k < len; k += GR_THREADS) dst[k] = src[k];
 }
 
-template <bool UNIFORM>
+// SPANS: in_off holds the source START of every OUTPUT row (k_spans_reduce), idx is not read
+template <bool UNIFORM, bool SPANS = false>
 __global__ void __launch_bounds__(GR_THREADS)
 k_gather_rows(const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off, uint32_t width,
               const uint32_t* __restrict__ idx, uint64_t n_out, const int64_t* __restrict__ out_off,
@@ -238,14 +290,19 @@ k_gather_rows(const uint8_t* __restrict__ in, const int64_t* __restrict__ in_off
       uint32_t sz = 0;
       if (j < T) {
         const uint64_t r = r0 + j;
-        const uint32_t src_row = idx[r];
         int64_t s, d;
         uint32_t len;
-        if constexpr (UNIFORM) {
+        if constexpr (SPANS) {
+          s = in_off[r];
+          d = out_off[r];
+          len = (uint32_t)(out_off[r + 1] - d);
+        } else if constexpr (UNIFORM) {
+          const uint32_t src_row = idx[r];
           s = (int64_t)src_row * width;
           d = (int64_t)r * width;
           len = width;
         } else {
+          const uint32_t src_row = idx[r];
           s = in_off[src_row];
           len = (uint32_t)(in_off[src_row + 1] - s);
           d = out_off[r];
@@ -486,8 +543,10 @@ extern "C" int xchg_gather_offsets(const int64_t* in_off, const uint32_t* idx, u
 
 static int launch_gather_rows(bool uniform, const uint8_t* in, const int64_t* in_off, uint32_t width,
                               const uint32_t* idx, uint64_t n_out, const int64_t* out_off,
-                              uint8_t* out, uint32_t rows_per_tile, cudaStream_t s) {
+                              uint8_t* out, uint32_t rows_per_tile, cudaStream_t s, bool spans = false) {
   XCHG_ONCE_PER_DEVICE({
+    XCHG_CUDA_TRY((cudaFuncSetAttribute(k_gather_rows<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)GR_SMEM)));
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)GR_SMEM));
     XCHG_CUDA_TRY(cudaFuncSetAttribute(k_gather_rows<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -496,7 +555,10 @@ static int launch_gather_rows(bool uniform, const uint8_t* in, const int64_t* in
   const uint64_t ntiles = (n_out + rows_per_tile - 1) / rows_per_tile;
   const int cap = xchg_gather_ctas_per_sm();
   const int grid = (int)std::min<uint64_t>(ntiles, (uint64_t)xchg_sm_count() * (cap ? cap : 3 * 4));
-  if (uniform)
+  if (spans)
+    XCHG_LAUNCH(XK_GATHER_ROWS, s, (k_gather_rows<false, true><<<grid, GR_THREADS, GR_SMEM, s>>>(in, in_off, width, idx, n_out, out_off,
+                                                                                            out, rows_per_tile)));
+  else if (uniform)
     XCHG_LAUNCH(XK_GATHER_ROWS, s, k_gather_rows<true><<<grid, GR_THREADS, GR_SMEM, s>>>(in, in_off, width, idx, n_out, out_off, out,
                                                           rows_per_tile));
   else
@@ -531,6 +593,41 @@ extern "C" int xchg_gather_bytes(const uint8_t* in_data, const int64_t* in_off, 
   XCHG_REQUIRE(in_data && out_data, "NULL data pointers");
   return launch_gather_rows(false, in_data, in_off, 0, idx, n_out, out_off, out_data, GR_MAX_ROWS,
                             (cudaStream_t)stream);
+}
+
+extern "C" int xchg_gather_spans(const int64_t* in_off, const uint32_t* idx, uint64_t n_out,
+                                 int64_t* src_start_out, int64_t* out_off, void* workspace,
+                                 uint64_t workspace_bytes, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  XCHG_REQUIRE(out_off != nullptr, "out_off is NULL");
+  if (n_out == 0) {
+    XCHG_CUDA_TRY(cudaMemsetAsync(out_off, 0, 8, s));
+    return XCHG_OK;
+  }
+  XCHG_REQUIRE(in_off && idx && src_start_out && workspace, "NULL in_off / idx / src_start_out / workspace");
+  const uint64_t ntiles = (n_out + SC_TILE - 1) / SC_TILE;
+  int64_t* tiles = (int64_t*)xchg_align_up((uint64_t)(uintptr_t)workspace, 8);
+  if ((uint64_t)((uint8_t*)tiles - (uint8_t*)workspace) + ntiles * 8 > workspace_bytes) {
+    xchg_set_error("gather_spans workspace too small");
+    return XCHG_ERR_WORKSPACE;
+  }
+  XCHG_LAUNCH(XK_GATHER_OFFSETS, s,
+              k_spans_reduce<<<(unsigned)ntiles, SC_THREADS, 0, s>>>(in_off, idx, n_out, src_start_out, out_off, tiles));
+  XCHG_LAUNCH_CHECK();
+  XCHG_LAUNCH(XK_GATHER_OFFSETS, s, k_scan_tiles<<<1, SC_THREADS, 0, s>>>(tiles, ntiles));
+  XCHG_LAUNCH_CHECK();
+  XCHG_LAUNCH(XK_GATHER_OFFSETS, s, k_spans_scan<<<(unsigned)ntiles, SC_THREADS, 0, s>>>(n_out, tiles, out_off));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+extern "C" int xchg_gather_bytes_spans(const uint8_t* in_data, const int64_t* src_start, uint64_t n_out,
+                                       const int64_t* out_off, uint8_t* out_data, void* stream) {
+  if (n_out == 0) return XCHG_OK;
+  XCHG_REQUIRE(src_start && out_off, "NULL src_start / out_off");
+  XCHG_REQUIRE(in_data && out_data, "NULL data pointers");
+  return launch_gather_rows(false, in_data, src_start, 0, nullptr, n_out, out_off, out_data, GR_MAX_ROWS,
+                            (cudaStream_t)stream, true);
 }
 
 extern "C" int xchg_offsets_widen(const int32_t* in, uint64_t count, int64_t base, int64_t* out,

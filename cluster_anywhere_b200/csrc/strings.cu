@@ -225,6 +225,16 @@ k_flag_active(const uint8_t* __restrict__ unresolved, const uint32_t* __restrict
     active[j] = unresolved[gid[j]] ? 1u : 0u;
 }
 
+// head[j] = row j (in level-0 order) does NOT repeat the string of row j-1 in the final order:
+// it differs from it, or its group is still open (its rows move again, so nothing is known)
+__global__ void __launch_bounds__(ST_THREADS)
+k_string_run_heads(const uint8_t* __restrict__ fflag, const uint32_t* __restrict__ active, uint64_t m,
+                   uint8_t* __restrict__ head) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < m; j += stride)
+    head[j] = (fflag[j] || (active && active[j])) ? 1 : 0;
+}
+
 // list[excl[j]] = j for every flagged j (excl = exclusive scan of the flags)
 __global__ void __launch_bounds__(ST_THREADS)
 k_scatter_flagged(const uint32_t* __restrict__ active, const int64_t* __restrict__ excl, uint64_t m,
@@ -348,6 +358,16 @@ extern "C" int xchg_string_active_rows(const uint8_t* gflag, const uint8_t* ffla
                                                                                 unresolved_scratch));
   XCHG_LAUNCH(XK_PARTITION, s, k_flag_active<<<st_grid(m), ST_THREADS, 0, s>>>(unresolved_scratch, gid, m,
                                                                             active_out));
+  XCHG_LAUNCH_CHECK();
+  return XCHG_OK;
+}
+
+extern "C" int xchg_string_run_heads(const uint8_t* fflag, const uint32_t* active, uint64_t m, uint8_t* head_out,
+                                     void* stream) {
+  if (m == 0) return XCHG_OK;
+  XCHG_REQUIRE(fflag && head_out, "NULL argument");
+  XCHG_LAUNCH(XK_MISC, (cudaStream_t)stream,
+              k_string_run_heads<<<st_grid(m), ST_THREADS, 0, (cudaStream_t)stream>>>(fflag, active, m, head_out));
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
 }

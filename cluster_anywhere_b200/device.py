@@ -396,13 +396,15 @@ def take_column(rt: Runtime, col: DeviceColumn, idx: torch.Tensor, n_out: int) -
     ws_bytes = ctypes.c_uint64()
     _cabi.check(_cabi.load().xchg_gather_offsets_workspace_bytes(n_out, ctypes.byref(ws_bytes)))
     ws = rt.empty(ws_bytes.value)
-    rt.call("xchg_gather_offsets", _vp(col.offsets), _vp(idx), n_out, _vp(out_off), _vp(ws),
+    # the rows' source starts are kept between the offsets pass and the byte copy: the source
+    # offsets (a random read per row) are then touched once, not three times
+    starts = rt.empty(max(1, n_out), torch.int64)
+    rt.call("xchg_gather_spans", _vp(col.offsets), _vp(idx), n_out, _vp(starts), _vp(out_off), _vp(ws),
             ws_bytes.value, rt.stream, launches=3)
     total = int(out_off[n_out].item()) if n_out else 0  # sync: output byte count
     out = rt.empty(total)
     if total:
-        rt.call("xchg_gather_bytes", _vp(col.data), _vp(col.offsets), _vp(idx), n_out, _vp(out_off),
-                _vp(out), rt.stream)
+        rt.call("xchg_gather_bytes_spans", _vp(col.data), _vp(starts), n_out, _vp(out_off), _vp(out), rt.stream)
     return DeviceColumn(col.type, n_out, "var", col.width, out, out_off, validity, null_count)
 
 
@@ -461,6 +463,12 @@ def take_table(rt: Runtime, table: DeviceTable, idx: torch.Tensor, n_out: Option
     cols = []
     for name, c in zip(table.names, table.columns):
         pre = (presorted or {}).get(name)
+        if pre is not None and isinstance(pre[0], str):
+            # ("rows", index): a string key column whose sorted output repeats long runs of one
+            # value is copied from ONE source row per run -- byte-identical, and the reads of a
+            # heavy hitter stay in L2 instead of fetching every row's own copy from DRAM
+            cols.append(take_column(rt, c, pre[1], n_out) if n_out == c.n else take_column(rt, c, idx, n_out))
+            continue
         if (pre is not None and c.kind == "fixed" and n_out == c.n and n_out > 0
                 and _is_int_key(key_type_of(c.type))):
             norm, desc = pre
@@ -821,16 +829,44 @@ def _exclusive_scan_flags(rt: Runtime, flags: torch.Tensor, m: int) -> torch.Ten
     return out
 
 
-def _sort_string_column(rt: Runtime, col: DeviceColumn, desc: bool, perm, n: int, ws, ws_bytes):
+def _string_run_rows(rt: Runtime, order: torch.Tensor, fflag: torch.Tensor, active, m: int):
+    """rows[j] = source row of the FIRST row of the run of identical strings that sorted row j
+    belongs to (see xchg_string_run_heads), or None when every row is its own run."""
+    lib = _cabi.load()
+    head = rt.empty(m)
+    rt.call("xchg_string_run_heads", _vp(fflag), _vp(active), m, _vp(head), rt.stream)
+    wsb = ctypes.c_uint64()
+    _cabi.check(lib.xchg_groups_from_flags_bytes(m, ctypes.byref(wsb)))
+    gws = rt.empty(wsb.value)
+    gid = rt.empty(m, torch.int32)
+    first = rt.empty(m, torch.int32)
+    g_out = ctypes.c_uint64()
+    rt.call("xchg_groups_from_flags", _vp(head), None, m, _vp(gws), wsb.value, _vp(gid), _vp(first),
+            ctypes.byref(g_out), rt.stream, launches=3)  # sync: number of runs
+    runs = int(g_out.value)
+    if runs * 4 > m * 3:  # few repeats: a second index array would cost more than it saves
+        return None
+    src_first = rt.empty(runs, torch.int32)
+    rt.call("xchg_gather_fixed", _vp(order), 4, _vp(first), runs, _vp(src_first), rt.stream)
+    rows = rt.empty(m, torch.int32)
+    rt.call("xchg_gather_fixed", _vp(src_first), 4, _vp(gid), m, _vp(rows), rt.stream)
+    return rows
+
+
+def _sort_string_column(rt: Runtime, col: DeviceColumn, desc: bool, perm, n: int, ws, ws_bytes, runs_out=None):
     """Stable sort by one string column, most significant bytes first: ONE stable sort of
     all rows by their first 8 bytes, then only the rows that still tie AND whose tie group
     holds at least two different strings are looked at again, 8 bytes at a time (a heavy
     hitter's run of identical keys is final after one comparison with its neighbour), the
     length last (a proper prefix sorts first).  Same order as the LSD chain over every
     chunk -- pyarrow's bytewise order, nulls last -- at a cost that follows the number of
-    rows whose order is still open instead of rows x chunks."""
+    rows whose order is still open instead of rows x chunks.
+    ``runs_out`` (a list, optional) receives the row map of :func:`_string_run_rows` when the
+    level-0 pass found enough repeated keys for it to pay."""
     if os.environ.get("XCHG_STRING_ALGO", "msd") == "lsd":
         return _sort_string_column_lsd(rt, col, desc, perm, n, ws, ws_bytes)
+    want_runs = runs_out is not None and os.environ.get("XCHG_STRING_RUNS", "1") != "0"
+    level0 = {}
     off = _string_offsets(rt, col)
     lib = _cabi.load()
     # ---- level 0: every row, by (null-ness, chunk 0) ----
@@ -864,6 +900,8 @@ def _sort_string_column(rt: Runtime, col: DeviceColumn, desc: bool, perm, n: int
                 _vp(active), rt.stream, launches=2)
         excl = _exclusive_scan_flags(rt, active, m)
         a = int(excl[m].item())  # sync: rows still open
+        if from_byte == 8 and want_runs:
+            level0["fflag"], level0["active"] = fflag, (active if a else None)
         if a == 0:
             return None, None, 0
         lst = rt.empty(a, torch.int32)
@@ -874,8 +912,18 @@ def _sort_string_column(rt: Runtime, col: DeviceColumn, desc: bool, perm, n: int
 
     lst, gid_a, a = open_positions(order, sorted_keys, None, n, 8)
     del sorted_keys
-    if a == 0:
+
+    def finish():
+        # rows outside the open groups keep their level-0 position, so the level-0 repeats are
+        # repeats of the final order too
+        if level0:
+            rows = _string_run_rows(rt, order, level0["fflag"], level0["active"], n)
+            if rows is not None:
+                runs_out.append(rows)
         return order
+
+    if a == 0:
+        return finish()
     mx = rt.zeros(1, torch.int64)
     lens = rt.empty(n, torch.int32)
     rt.call("xchg_string_lengths", _vp(off), n, _vp(lens), _vp(mx), rt.stream)
@@ -915,7 +963,7 @@ def _sort_string_column(rt: Runtime, col: DeviceColumn, desc: bool, perm, n: int
         rt.call("xchg_gather_fixed", _vp(pos), 4, _vp(sub), a_next, _vp(pos_next), rt.stream)
         pos, gid_a, a = pos_next, gid_next, a_next
         level += 1
-    return order
+    return finish()
 
 
 def _pack_string_boundaries(rt: Runtime, boundaries: Sequence[tuple]):
@@ -957,12 +1005,15 @@ def string_partition_cuts(rt: Runtime, sorted_col: DeviceColumn, boundaries: Seq
 
 
 def sort_permutation(rt: Runtime, table: DeviceTable, columns: Sequence[str],
-                     descending: Sequence[bool], want_norm: bool = False):
+                     descending: Sequence[bool], want_norm: bool = False, hints: Optional[dict] = None):
     """Stable multi-key sort -> (perm uint32[n] as int32 tensor, [norm key arrays]).
 
     LSD over key columns (last key first); each column is one stable radix sort.
     ``norm`` (only when ``want_norm``) holds, per key column, the normalised keys
-    in FINAL sorted order -- the input of :func:`partition_cuts`.
+    in FINAL sorted order -- the input of :func:`partition_cuts`.  ``hints`` (a dict the
+    caller owns) receives ``"string_runs": (column, rows)`` when the PRIMARY key is a string
+    column with many repeated values: ``rows`` is a take index for that one column that reads
+    one source row per run of identical keys (see :func:`take_table`).
     """
     n = table.num_rows
     if n > (1 << 30) - 1:
@@ -976,7 +1027,10 @@ def sort_permutation(rt: Runtime, table: DeviceTable, columns: Sequence[str],
         name, desc = order[ci]
         col = table.column(name)
         if is_string_key(col):
-            perm = _sort_string_column(rt, col, bool(desc), perm, n, ws, ws_bytes)
+            runs = [] if (hints is not None and ci == 0) else None
+            perm = _sort_string_column(rt, col, bool(desc), perm, n, ws, ws_bytes, runs)
+            if runs:
+                hints["string_runs"] = (name, runs[0])
             continue
         if col.kind != "fixed":
             raise NotImplementedError(f"sort key column {name!r} of type {col.type} is not supported")

@@ -224,8 +224,14 @@ class DeviceExchange:
             boundaries = self.sample_boundaries(ds, sort_key, r, seed) if r > 1 else []
         n = ds.num_rows
         self._stamp("tl.sort_prologue")
+        hints = {}
         perm, norms = dev.sort_permutation(rt, ds.table, sort_key.get_columns(),
-                                           sort_key.get_descending(), want_norm=len(boundaries) > 0)
+                                           sort_key.get_descending(), want_norm=len(boundaries) > 0, hints=hints)
+        if "string_runs" in hints:
+            from ..block_accessor import _Norms
+
+            norms = _Norms(norms)
+            norms.string_runs = hints["string_runs"]
         self._stamp("tl.sort_permutation")
         self._gpu_mark("g.keys_sorted")
         string_key = any(dev.is_string_key(ds.table.column(c)) for c in sort_key.get_columns())

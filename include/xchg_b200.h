@@ -388,6 +388,12 @@ int xchg_assign_partitions_bytes(const int64_t* offsets, const uint8_t* data, co
                                  const uint8_t* bound_flags, int nb, int descending,
                                  uint32_t* dest_out, uint64_t* counts_out, void* stream);
 
+/* head_out[j] = 1 unless row j of the level-0 order is known to repeat the string of row j-1 in
+ * the FINAL order (fflag[j] == 0 and its tie group is closed; active may be NULL = no open
+ * group).  Runs of repeats let a caller copy a sorted key column from one source row per run
+ * (heavy hitters: the reads stay in L2) instead of fetching every row's own copy. */
+int xchg_string_run_heads(const uint8_t* fflag, const uint32_t* active, uint64_t m, uint8_t* head_out,
+                          void* stream);
 /*
  * MSD refinement of a string sort.  After a stable sort by chunk 0 only the rows that tie
  * there can be out of order, and of those only the ones whose tie group holds at least two
@@ -475,6 +481,19 @@ int xchg_gather_offsets_static(const int64_t* in_off, const uint32_t* idx, uint6
 int xchg_gather_bytes(const uint8_t* in_data, const int64_t* in_off, const uint32_t* idx,
                       uint64_t n_out, const int64_t* out_off, uint8_t* out_data,
                       void* stream);
+/*
+ * The same take with the rows' source spans kept between the two steps: xchg_gather_spans is
+ * xchg_gather_offsets that also stores src_start_out[i] = in_off[idx[i]] (int64, n_out entries);
+ * xchg_gather_bytes_spans copies the bytes from those starts.  in_off -- one random 16-byte read
+ * per row, a 64-128-byte DRAM fill -- is then read once per take instead of three times.  Same
+ * output; workspace as xchg_gather_offsets_workspace_bytes.
+ */
+int xchg_gather_spans(const int64_t* in_off, const uint32_t* idx, uint64_t n_out,
+                      int64_t* src_start_out, int64_t* out_off, void* workspace,
+                      uint64_t workspace_bytes, void* stream);
+int xchg_gather_bytes_spans(const uint8_t* in_data, const int64_t* src_start, uint64_t n_out,
+                            const int64_t* out_off, uint8_t* out_data, void* stream);
+
 /* Uniform-width rows (every row `width` bytes; GraySort payload, tensor rows):
  * out row i = in row idx[i]; no offsets are read. */
 /* xchg_gather_rows_multi: the same for up to 16 output segments in ONE launch: segment d

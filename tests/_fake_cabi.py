@@ -274,6 +274,29 @@ class FakeLib:
             dst[oo[j]:oo[j + 1]] = src[io[ix[j]]:io[ix[j] + 1]]
         return 0
 
+    def xchg_gather_spans(self, in_off, idx, n, src_start, out_off, ws, wsb, stream):
+        o = _arr(out_off, np.int64, n + 1)
+        o[0] = 0
+        if n == 0:
+            return 0
+        ix = _arr(idx, np.uint32, n).astype(np.int64)
+        io = _arr(in_off, np.int64, int(ix.max()) + 2)
+        _arr(src_start, np.int64, n)[:] = io[ix]
+        o[1:] = np.cumsum(io[ix + 1] - io[ix])
+        return 0
+
+    def xchg_gather_bytes_spans(self, in_data, src_start, n, out_off, out_data, stream):
+        if n == 0:
+            return 0
+        st = _arr(src_start, np.int64, n)
+        oo = _arr(out_off, np.int64, n + 1)
+        ln = np.diff(oo)
+        src = _arr(in_data, np.uint8, int((st + ln).max()))
+        dst = _arr(out_data, np.uint8, int(oo[n]))
+        for j in range(n):
+            dst[oo[j]:oo[j + 1]] = src[st[j]:st[j] + ln[j]]
+        return 0
+
     def xchg_offsets_widen(self, inp, count, base, out, stream):
         i = _arr(inp, np.int32, count).astype(np.int64)
         _arr(out, np.int64, count)[:] = i - i[0] + base
@@ -1003,6 +1026,15 @@ class FakeLib:
         unresolved = np.zeros(ngroups, bool)
         unresolved[gi[(f != 0) & (g == 0)]] = True
         _arr(active, np.uint32, m)[:] = unresolved[gi].astype(np.uint32)
+        return 0
+
+    def xchg_string_run_heads(self, fflag, active, m, head, stream):
+        if m == 0:
+            return 0
+        f = _arr(fflag, np.uint8, m) != 0
+        if _addr(active):
+            f = f | (_arr(active, np.uint32, m) != 0)
+        _arr(head, np.uint8, m)[:] = f.astype(np.uint8)
         return 0
 
     def xchg_scatter_flagged(self, flags, excl, m, out, stream):

@@ -177,3 +177,60 @@ def test_gather_rows_tma_variant_equals_the_default(w, n_in, n_out):
     libc.setenv(b"XCHG_GATHER_BULK", b"0", 1)
     exp = src.cpu().numpy().reshape(n_in, w)[idx.cpu().numpy()].reshape(-1)
     assert np.array_equal(outs[0], exp) and np.array_equal(outs[1], exp)
+
+
+@pytest.mark.parametrize("kind", ["short", "mixed", "huge_row", "empties"])
+def test_ragged_take_with_cached_spans_equals_the_plain_take(engine, kind):
+    """xchg_gather_spans + xchg_gather_bytes_spans (source starts kept between the offsets
+    pass and the byte copy) against xchg_gather_offsets + xchg_gather_bytes, and both against
+    numpy: identical offsets and bytes (Table.take on a var-width column,
+    transform_pyarrow.py:45-71)."""
+    import ctypes
+
+    from cluster_anywhere_b200 import _cabi
+
+    rt = dev.Runtime()
+    rng = np.random.default_rng({"short": 1, "mixed": 2, "huge_row": 3, "empties": 4}[kind])
+    n_in = 3000 if engine == "b200" else 300
+    if kind == "short":
+        lens = rng.integers(0, 24, n_in)
+    elif kind == "mixed":
+        lens = rng.integers(0, 700, n_in)
+    elif kind == "huge_row":
+        lens = rng.integers(0, 90, n_in)
+        lens[rng.integers(0, n_in, 3)] = 70_000  # wider than the staging tile: the whole-CTA copy
+    else:
+        lens = np.where(rng.random(n_in) < 0.8, 0, rng.integers(1, 40, n_in))
+    off = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    data = rng.integers(0, 256, int(off[-1]) + 16, dtype=np.uint8)
+    n_out = 2 * n_in + 37
+    idx = rng.integers(0, n_in, n_out).astype(np.uint32)
+
+    def up(a, dt):
+        t = rt.empty(max(1, a.size), dt)
+        if a.size:
+            dev._h2d(t.view(torch.uint8)[: a.nbytes], np.ascontiguousarray(a).view(np.uint8).reshape(-1))
+        return t
+
+    d_off, d_data, d_idx = up(off, torch.int64), up(data, torch.uint8), up(idx.view(np.int32), torch.int32)
+    wsb = ctypes.c_uint64()
+    _cabi.check(_cabi.load().xchg_gather_offsets_workspace_bytes(n_out, ctypes.byref(wsb)))
+    ws = rt.empty(wsb.value)
+    vp = dev._vp
+    oo1, oo2 = rt.empty(n_out + 1, torch.int64), rt.empty(n_out + 1, torch.int64)
+    starts = rt.empty(n_out, torch.int64)
+    rt.call("xchg_gather_offsets", vp(d_off), vp(d_idx), n_out, vp(oo1), vp(ws), wsb.value, rt.stream)
+    rt.call("xchg_gather_spans", vp(d_off), vp(d_idx), n_out, vp(starts), vp(oo2), vp(ws), wsb.value, rt.stream)
+    rt.synchronize()
+    exp_off = np.concatenate([[0], np.cumsum(lens[idx])]).astype(np.int64)
+    assert np.array_equal(oo1.cpu().numpy(), exp_off) and np.array_equal(oo2.cpu().numpy(), exp_off)
+    assert np.array_equal(starts.cpu().numpy(), off[idx])
+    total = int(exp_off[-1])
+    out1, out2 = rt.zeros(total + 16), rt.zeros(total + 16)
+    rt.call("xchg_gather_bytes", vp(d_data), vp(d_off), vp(d_idx), n_out, vp(oo1), vp(out1), rt.stream)
+    rt.call("xchg_gather_bytes_spans", vp(d_data), vp(starts), n_out, vp(oo2), vp(out2), rt.stream)
+    rt.synchronize()
+    exp = np.concatenate([data[off[r]:off[r + 1]] for r in idx]) if total else np.zeros(0, np.uint8)
+    assert np.array_equal(out1.cpu().numpy()[:total], exp)
+    assert np.array_equal(out2.cpu().numpy()[:total], exp)
+    assert not out2.cpu().numpy()[total:].any()  # nothing written past the end

@@ -50,3 +50,40 @@ def test_string_key_inside_a_multi_key_sort(engine):
     for cols, desc in ((["a", "s"], [False, True]), (["s", "b"], [False, False]), (["a", "s", "b"], [True, False, True])):
         got = B200ArrowBlockAccessor.for_block(t).sort(SortKey(cols, desc))
         assert tables_equal(got, O.sort_table(t, cols, desc)), (cols, desc)
+
+
+@pytest.mark.parametrize("desc", [False, True])
+def test_primary_string_key_is_copied_from_one_row_per_run(engine, desc):
+    """A sort whose primary key is a string column with repeated values hands out a second
+    take index for that column -- one source row per run of identical keys -- and the column
+    built from it is byte-identical to the plain take by the sort permutation."""
+    import torch
+
+    from cluster_anywhere_b200 import device as dev
+
+    rng = np.random.default_rng(77)
+    n = 5000
+    words = _words(rng, n, "zipf")
+    # two strings that share their first 8 bytes: their tie group stays open past level 0
+    words[::50] = ["w0000001-tail-a" if i % 2 else "w0000001-tail-b" for i in range(len(words[::50]))]
+    mask = rng.random(n) < 0.05
+    t = pa.table({"s": pa.array([None if m else w for w, m in zip(words, mask)], pa.string()),
+                  "i": pa.array(np.arange(n), pa.int64())})
+    rt = dev.default_runtime()
+    dt = dev.stage_table(rt, t)
+    hints = {}
+    perm, _ = dev.sort_permutation(rt, dt, ["s"], [desc], False, hints)
+    assert "string_runs" in hints and hints["string_runs"][0] == "s"
+    rows = hints["string_runs"][1]
+    rt.synchronize()
+    p, r = perm.cpu().numpy().view(np.uint32), rows.cpu().numpy().view(np.uint32)
+    assert (p != r).any(), "repeated keys must share a source row"
+    same = dev.export_table(rt, dev.take_table(rt, dt, perm, n, {"s": ("rows", rows)}))
+    plain = dev.export_table(rt, dev.take_table(rt, dt, perm, n))
+    assert tables_equal(same, plain) and tables_equal(same, O.sort_table(t, ["s"], [desc]))
+    # the accessor path uses it by itself
+    assert tables_equal(B200ArrowBlockAccessor.for_block(t).sort(SortKey("s", desc)), plain)
+    # a secondary string key gets no hint (its runs are not runs of the final order)
+    hints2 = {}
+    dev.sort_permutation(rt, dt, ["i", "s"], [False, desc], False, hints2)
+    assert "string_runs" not in hints2
