@@ -99,7 +99,7 @@ _SIGNATURES = {
     "xchg_string_chunk_keys": (c_int, [_P, _P, c_uint64, c_uint32, _P, _P]),
     "xchg_string_tie_flags": (c_int, [_P, _P, _P, _P, _P, _P, c_uint64, c_uint64, _P, _P, _P]),
     "xchg_string_active_rows": (c_int, [_P, _P, _P, c_uint64, c_uint64, _P, _P, _P]),
-    "xchg_string_run_heads": (c_int, [_P, _P, c_uint64, _P, _P]),
+    "xchg_string_run_heads": (c_int, [_P, _P, c_uint64, c_uint32, _P, _P]),
     "xchg_scatter_flagged": (c_int, [_P, _P, c_uint64, _P, _P]),
     "xchg_string_chunk_keys_rows": (c_int, [_P, _P, _P, c_uint64, c_uint32, _P, _P]),
     "xchg_scatter_u32": (c_int, [_P, _P, c_uint64, _P, _P]),

@@ -227,12 +227,15 @@ k_flag_active(const uint8_t* __restrict__ unresolved, const uint32_t* __restrict
 
 // head[j] = row j (in level-0 order) does NOT repeat the string of row j-1 in the final order:
 // it differs from it, or its group is still open (its rows move again, so nothing is known)
+// A run is also cut every `period` rows: each stretch of the output then reads its own copy
+// of the value, instead of every SM reading ONE source row of a heavy hitter (a single hot
+// line serialises in its L2 slice).
 __global__ void __launch_bounds__(ST_THREADS)
 k_string_run_heads(const uint8_t* __restrict__ fflag, const uint32_t* __restrict__ active, uint64_t m,
-                   uint8_t* __restrict__ head) {
+                   uint32_t period, uint8_t* __restrict__ head) {
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < m; j += stride)
-    head[j] = (fflag[j] || (active && active[j])) ? 1 : 0;
+    head[j] = (fflag[j] || (active && active[j]) || (period && j % period == 0)) ? 1 : 0;
 }
 
 // list[excl[j]] = j for every flagged j (excl = exclusive scan of the flags)
@@ -362,12 +365,13 @@ extern "C" int xchg_string_active_rows(const uint8_t* gflag, const uint8_t* ffla
   return XCHG_OK;
 }
 
-extern "C" int xchg_string_run_heads(const uint8_t* fflag, const uint32_t* active, uint64_t m, uint8_t* head_out,
-                                     void* stream) {
+extern "C" int xchg_string_run_heads(const uint8_t* fflag, const uint32_t* active, uint64_t m, uint32_t period,
+                                     uint8_t* head_out, void* stream) {
   if (m == 0) return XCHG_OK;
   XCHG_REQUIRE(fflag && head_out, "NULL argument");
   XCHG_LAUNCH(XK_MISC, (cudaStream_t)stream,
-              k_string_run_heads<<<st_grid(m), ST_THREADS, 0, (cudaStream_t)stream>>>(fflag, active, m, head_out));
+              k_string_run_heads<<<st_grid(m), ST_THREADS, 0, (cudaStream_t)stream>>>(fflag, active, m, period,
+                                                                                    head_out));
   XCHG_LAUNCH_CHECK();
   return XCHG_OK;
 }

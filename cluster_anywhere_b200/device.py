@@ -834,7 +834,8 @@ def _string_run_rows(rt: Runtime, order: torch.Tensor, fflag: torch.Tensor, acti
     belongs to (see xchg_string_run_heads), or None when every row is its own run."""
     lib = _cabi.load()
     head = rt.empty(m)
-    rt.call("xchg_string_run_heads", _vp(fflag), _vp(active), m, _vp(head), rt.stream)
+    period = int(os.environ.get("XCHG_STRING_RUN_PERIOD", "512"))  # one copy per take tile
+    rt.call("xchg_string_run_heads", _vp(fflag), _vp(active), m, period, _vp(head), rt.stream)
     wsb = ctypes.c_uint64()
     _cabi.check(lib.xchg_groups_from_flags_bytes(m, ctypes.byref(wsb)))
     gws = rt.empty(wsb.value)

@@ -34,7 +34,6 @@ import torch
 from . import _cabi
 from . import device as dev
 
-_PAGE = 4096
 
 
 def table_to_ipc(table: pa.Table) -> pa.Buffer:
@@ -66,8 +65,11 @@ class HostRegistration:
         self.failed = 0
 
     def add(self, *bufs) -> int:
-        """Page-lock the pages spanned by the buffers (anything ``pa.py_buffer`` accepts);
-        ranges that touch or share a page are registered as one.  -> number of ranges from
+        """Page-lock the buffers (anything ``pa.py_buffer`` accepts); overlapping ranges are
+        registered as one.  The ranges are registered byte-exact, NOT rounded out to pages: a
+        heap neighbour that shares a buffer's first or last page must stay "pageable" in the
+        driver's eyes, or a later copy into it -- half inside a registered range -- is refused
+        (seen as `invalid argument` on a plain ``tensor.cpu()``).  -> number of ranges from
         which copies are now asynchronous."""
         if not self._rt.is_cuda:
             return 0
@@ -75,11 +77,11 @@ class HostRegistration:
         for buf in bufs:
             b = buf if isinstance(buf, pa.Buffer) else pa.py_buffer(buf)
             if b.size:
-                spans.append((b.address // _PAGE * _PAGE, (b.address + b.size + _PAGE - 1) // _PAGE * _PAGE))
+                spans.append((b.address, b.address + b.size))
         spans.sort()
         merged: List[List[int]] = []
         for lo, hi in spans:
-            if merged and lo <= merged[-1][1]:
+            if merged and lo < merged[-1][1]:
                 merged[-1][1] = max(merged[-1][1], hi)
             else:
                 merged.append([lo, hi])

@@ -390,10 +390,11 @@ int xchg_assign_partitions_bytes(const int64_t* offsets, const uint8_t* data, co
 
 /* head_out[j] = 1 unless row j of the level-0 order is known to repeat the string of row j-1 in
  * the FINAL order (fflag[j] == 0 and its tie group is closed; active may be NULL = no open
- * group).  Runs of repeats let a caller copy a sorted key column from one source row per run
- * (heavy hitters: the reads stay in L2) instead of fetching every row's own copy. */
-int xchg_string_run_heads(const uint8_t* fflag, const uint32_t* active, uint64_t m, uint8_t* head_out,
-                          void* stream);
+ * group), or j is a multiple of `period` (0 = never).  Runs of repeats let a caller copy a sorted
+ * key column from one source row per run instead of fetching every row's own copy; the period
+ * keeps a heavy hitter from becoming ONE hot line that every SM reads. */
+int xchg_string_run_heads(const uint8_t* fflag, const uint32_t* active, uint64_t m, uint32_t period,
+                          uint8_t* head_out, void* stream);
 /*
  * MSD refinement of a string sort.  After a stable sort by chunk 0 only the rows that tie
  * there can be out of order, and of those only the ones whose tie group holds at least two
@@ -719,7 +720,9 @@ int xchg_offsets_rebase(const int64_t* in, uint64_t count, int64_t base, int64_t
  * Caller-owned host memory (the wire bytes of a block as they sit in the object store,
  * python/ray/_private/arrow_serialization.py:785-809): page-lock [ptr, ptr + bytes) so that
  * host->device copies out of it are asynchronous DMA instead of the driver's staged copy of
- * pageable memory.  ptr / bytes must cover whole pages.  A range that is already registered is
+ * pageable memory.  Pass the buffer's exact range (do not round it out to pages: a neighbour
+ * sharing its first or last page must not end up half inside a registered range, copies into
+ * it would be refused).  A range that is already registered is
  * not an error (*already_out = 1; the caller must then NOT unregister it).  Read-only mappings
  * are registered read-only.
  */

@@ -1028,12 +1028,14 @@ class FakeLib:
         _arr(active, np.uint32, m)[:] = unresolved[gi].astype(np.uint32)
         return 0
 
-    def xchg_string_run_heads(self, fflag, active, m, head, stream):
+    def xchg_string_run_heads(self, fflag, active, m, period, head, stream):
         if m == 0:
             return 0
         f = _arr(fflag, np.uint8, m) != 0
         if _addr(active):
             f = f | (_arr(active, np.uint32, m) != 0)
+        if period:
+            f = f | (np.arange(m) % period == 0)
         _arr(head, np.uint8, m)[:] = f.astype(np.uint8)
         return 0
 
