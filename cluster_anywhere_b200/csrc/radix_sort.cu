@@ -152,11 +152,23 @@ k_key_scan(const T* __restrict__ keys, uint32_t n, int desc, KeyShifts ks, int w
   // one shared-memory atomic per key and place; a warp whose 32 keys share the digit (sorted
   // or narrow inputs) adds once instead -- that test is only made while it keeps succeeding
   bool try_uniform = true;
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_up; i += stride) {
+  // four keys per thread and trip, all loads issued before the first is used: with one load
+  // in flight per thread the pass ran at 2.4 TB/s (30 % of DRAM bandwidth, latency-bound)
+  constexpr int KS_UNROLL = 4;
+  for (uint32_t i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n_up; i0 += stride * KS_UNROLL) {
+    uint64_t kq[KS_UNROLL];
+#pragma unroll
+    for (int u = 0; u < KS_UNROLL; ++u) {
+      const uint64_t iu = (uint64_t)i0 + (uint64_t)u * stride;
+      kq[u] = iu < n ? norm_value<T>(keys[iu], desc != 0) : 0;
+    }
+#pragma unroll
+    for (int u = 0; u < KS_UNROLL; ++u) {
+    const uint64_t i = (uint64_t)i0 + (uint64_t)u * stride;
+    if (i >= n_up) break;  // warp-uniform: a warp's 32 indices share their 32-aligned block
     const bool active = i < n;
-    uint64_t key = 0;
+    const uint64_t key = kq[u];
     if (active) {
-      key = norm_value<T>(keys[i], desc != 0);
       acc_or |= key;
       acc_and &= key;
     }
@@ -178,6 +190,7 @@ k_key_scan(const T* __restrict__ keys, uint32_t n, int desc, KeyShifts ks, int w
       try_uniform = all_uni;  // warp-uniform by construction
     } else if (active) {
       for (int p = 0; p < ks.n; ++p) atomicAdd(&sh[p * BINS + ((uint32_t)(key >> ks.shift[p]) & 255u)], 1u);
+    }
     }
   }
   if (want_orand) {
