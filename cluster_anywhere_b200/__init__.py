@@ -8,7 +8,7 @@ from ._cabi import XchgError  # noqa: F401
 from .block import BlockExecStats, BlockMetadata  # noqa: F401
 from .block_accessor import B200ArrowBlockAccessor  # noqa: F401
 from .sort_key import SortKey  # noqa: F401
-from .aggregate import AggregateFn, Count, Max, Mean, Min, Std, Sum  # noqa: F401
+from .aggregate import AbsMax, AggregateFn, Count, Max, Mean, Min, Std, Sum  # noqa: F401
 
 __all__ = ["B200ArrowBlockAccessor", "SortKey", "BlockMetadata", "BlockExecStats", "XchgError",
-           "AggregateFn", "Count", "Sum", "Min", "Max", "Mean", "Std"]
+           "AggregateFn", "Count", "Sum", "Min", "Max", "Mean", "Std", "AbsMax"]

@@ -1,9 +1,9 @@
 """Aggregations of ``groupby().aggregate()`` and their device implementation.
 
-Host surface: ``Count / Sum / Min / Max / Mean / Std`` with the reference's
+Host surface: ``Count / Sum / Min / Max / Mean / Std / AbsMax`` with the reference's
 constructor arguments, result names and null policy (python/ray/data/aggregate.py:
-97-326, _internal/null_aggregate.py:11-25).  ``AbsMax / Quantile / Unique`` are row /
-list based in the reference (:330-489) and stay on the reference path: asking this
+97-354, _internal/null_aggregate.py:11-25).  ``Quantile / Unique`` are row /
+list based in the reference (:367-489) and stay on the reference path: asking this
 engine for them raises ``NotImplementedError``.
 
 Device side (``aggregate_table``): the hash group-by of csrc/aggregate.cu (K8), its
@@ -31,7 +31,7 @@ from . import _cabi
 from . import device as dev
 from .device import DeviceColumn, DeviceTable, _vp
 
-KIND_COUNT, KIND_SUM, KIND_MIN, KIND_MAX, KIND_MEAN, KIND_STD = range(6)
+KIND_COUNT, KIND_SUM, KIND_MIN, KIND_MAX, KIND_MEAN, KIND_STD, KIND_ABSMAX = range(7)
 ROWS_COL = "__xchg_rows"
 STATE_PREFIX = "__xchg_state:"
 STATE_WORDS = 6
@@ -114,18 +114,28 @@ class Std(AggregateFn):
         super().__init__(_named("std", on, alias_name), on, ignore_nulls, ddof)
 
 
+class AbsMax(AggregateFn):
+    """aggregate.py:330-354: ``max(0, |x|)`` over the group's non-null values (a NaN never wins
+    Python's ``max(a, abs(r))``).  Computed from the group's min and max at finalisation."""
+
+    kind = KIND_ABSMAX
+
+    def __init__(self, on: Optional[str] = None, ignore_nulls: bool = True, alias_name: Optional[str] = None):
+        super().__init__(_named("abs_max", on, alias_name), on, ignore_nulls)
+
+
 def _unsupported(name):
     class _Unsupported(AggregateFn):
         def __init__(self, *a, **k):
             raise NotImplementedError(
-                f"{name} is row / list based in the reference (python/ray/data/aggregate.py:330-489) "
+                f"{name} is row / list based in the reference (python/ray/data/aggregate.py:367-489) "
                 "and is not offloaded to the B200 engine; use the reference path for it")
 
     _Unsupported.__name__ = name
     return _Unsupported
 
 
-AbsMax, Quantile, Unique = _unsupported("AbsMax"), _unsupported("Quantile"), _unsupported("Unique")
+Quantile, Unique = _unsupported("Quantile"), _unsupported("Unique")
 
 
 def check_aggs(aggs: Sequence[AggregateFn]):
@@ -409,7 +419,8 @@ def aggregate_table(rt: dev.Runtime, table: DeviceTable, key: Optional[str],
             vt = dev.key_type_of(vc.type)
             # min / max / NaN counts only where something reads them: Min, Max, or a partial
             # row (whose consumer is unknown here)
-            want_minmax = int((not finalize) or any(a.kind in (KIND_MIN, KIND_MAX) and a.on == name for a in aggs))
+            want_minmax = int((not finalize)
+                              or any(a.kind in (KIND_MIN, KIND_MAX, KIND_ABSMAX) and a.on == name for a in aggs))
             rt.call("xchg_agg_accumulate", _vp(rgid), _vp(vc.data), vt, _vp(vc.validity), 0, n, g, _vp(st),
                     want_minmax, _vp(rows), rt.stream, launches=2)
             if need_m2:
@@ -445,7 +456,7 @@ def aggregate_table(rt: dev.Runtime, table: DeviceTable, key: Optional[str],
             st, m2, vt = stats[a.on]
             rt.call("xchg_agg_finalize", a.kind, a.ddof, int(a.ignore_nulls), vt, g, _vp(rows), _vp(st),
                     _vp(m2), _vp(out), _vp(vb), rt.stream)
-            int_out = a.kind in (KIND_SUM, KIND_MIN, KIND_MAX) and _is_int_type(vt)
+            int_out = a.kind in (KIND_SUM, KIND_MIN, KIND_MAX, KIND_ABSMAX) and _is_int_type(vt)
             typ = pa.int64() if int_out else pa.float64()
         validity, nulls = (None, 0) if a.kind == KIND_COUNT else _bytes_to_validity(rt, vb, g)
         cols.append(DeviceColumn(typ, g, "fixed", 8, out.view(torch.uint8), None, validity, nulls))

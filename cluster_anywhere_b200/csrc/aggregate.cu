@@ -424,7 +424,10 @@ k_finalize(int kind, int ddof, int ignore_nulls, int sum_is_int, int val_is_sign
       valid_out[i] = 1;
       continue;
     }
-    const uint64_t c = a.cnt[i];
+    uint64_t c = a.cnt[i];
+    // AbsMax accumulates row by row in the reference, and its null test (pandas.isnull,
+    // null_aggregate.py:269-276) takes NaN for a null: only the other values count
+    if (kind == 6 && !sum_is_int) c -= a.nan[i] < c ? a.nan[i] : c;
     const bool ok = c > 0 && (ignore_nulls || c == rows[i]);
     valid_out[i] = ok ? 1 : 0;
     uint64_t r = 0;
@@ -443,6 +446,22 @@ k_finalize(int kind, int ddof, int ignore_nulls, int sum_is_int, int val_is_sign
         }
       } else if (kind == 4) {
         r = (uint64_t)__double_as_longlong(s / (double)c);
+      } else if (kind == 6) {
+        // AbsMax (python/ray/data/aggregate.py:330-354): max(0, |x|) over the group's values =
+        // the larger magnitude of its min and max (both skip NaN, which counts as a null here)
+        if (sum_is_int) {
+          if (val_is_signed) {
+            const long long mn = (long long)(a.minv[i] ^ 0x8000000000000000ull);
+            const long long mx = (long long)(a.maxv[i] ^ 0x8000000000000000ull);
+            const uint64_t an = mn < 0 ? (uint64_t)(-(mn + 1)) + 1ull : (uint64_t)mn;
+            const uint64_t ax = mx < 0 ? (uint64_t)(-(mx + 1)) + 1ull : (uint64_t)mx;
+            r = an > ax ? an : ax;
+          } else {
+            r = a.maxv[i];
+          }
+        } else {
+          r = (uint64_t)__double_as_longlong(fmax(fabs(dec_double(a.minv[i])), fabs(dec_double(a.maxv[i]))));
+        }
       } else {
         double v = 0.0;
         if (c >= 2) v = sqrt(m2[i] / ((double)c - (double)ddof));
@@ -1234,7 +1253,7 @@ extern "C" int xchg_agg_finalize(int kind, int ddof, int ignore_nulls, int value
                                  uint64_t num_groups, const uint64_t* rows, const uint64_t* stats,
                                  const double* m2, void* out, uint8_t* valid_out, void* stream) {
   if (num_groups == 0) return XCHG_OK;
-  XCHG_REQUIRE(kind >= 0 && kind <= 5, "kind must be 0..5");
+  XCHG_REQUIRE(kind >= 0 && kind <= 6, "kind must be 0..6");
   XCHG_REQUIRE(rows && out && valid_out, "NULL rows / out / valid_out");
   XCHG_REQUIRE(kind == 0 || stats, "NULL stats");
   XCHG_REQUIRE(kind != 5 || m2, "std needs m2");

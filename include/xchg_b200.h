@@ -682,10 +682,12 @@ int xchg_agg_merge_states(const uint32_t* row_gid, const uint64_t* partial_state
                           void* stream);
 int xchg_agg_pack_states(uint64_t num_groups, const uint64_t* stats, const double* m2,
                          uint64_t* partial_states_out, void* stream);
-/* kind: 0 count, 1 sum, 2 min, 3 max, 4 mean, 5 std(ddof).  out: num_groups 8-byte
- * values (int64 for count and for sum/min/max of integer columns, double otherwise);
- * valid_out: one byte per group (0 = null result: no non-null value, or a null with
- * ignore_nulls = 0). */
+/* kind: 0 count, 1 sum, 2 min, 3 max, 4 mean, 5 std(ddof), 6 abs_max (AbsMax,
+ * python/ray/data/aggregate.py:330-354: the larger magnitude of the group's min and max;
+ * NaN counts as a null there, as the reference's row-wise null test does).  out: num_groups
+ * 8-byte values (int64 for count and for sum/min/max/abs_max of integer columns, double
+ * otherwise); valid_out: one byte per group (0 = null result: no non-null value, or a null
+ * with ignore_nulls = 0). */
 int xchg_agg_finalize(int kind, int ddof, int ignore_nulls, int value_type, uint64_t num_groups,
                       const uint64_t* rows, const uint64_t* stats, const double* m2, void* out,
                       uint8_t* valid_out, void* stream);

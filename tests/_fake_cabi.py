@@ -877,6 +877,9 @@ class FakeLib:
     def xchg_agg_finalize(self, kind, ddof, ignore_nulls, vt, g, rows, stats, m2, out, valid_out, stream):
         if g == 0:
             return 0
+        if not 0 <= kind <= 6:
+            self.err = b"kind must be 0..6"
+            return -1
         r = _arr(rows, np.uint64, g)
         o = _arr(out, np.uint64, g)
         v = _arr(valid_out, np.uint8, g)
@@ -888,6 +891,8 @@ class FakeLib:
         is_int = dt.kind in "iu"
         st = _arr(stats, np.uint64, 5 * g).reshape(5, g)
         cnt = st[0]
+        if kind == 6 and not is_int:
+            cnt = cnt - np.minimum(st[4], cnt)  # AbsMax: NaN counts as null (pandas.isnull)
         ok = (cnt > 0) & (bool(ignore_nulls) | (cnt == r))
         v[:] = ok.astype(np.uint8)
         s = st[1].view(np.int64).astype(np.float64) if is_int else st[1].view(np.float64)
@@ -906,6 +911,21 @@ class FakeLib:
                     res = f.view(np.uint64)
             elif kind == 4:
                 res = (s / cnt.astype(np.float64)).view(np.uint64)
+            elif kind == 6:
+                def dec(e):
+                    b = np.where(e >> np.uint64(63), e & np.uint64((1 << 63) - 1), ~e)
+                    return b.view(np.float64)
+
+                if is_int and dt.kind == "i":
+                    mn = (st[2] ^ np.uint64(1 << 63)).view(np.int64).astype(object)
+                    mx = (st[3] ^ np.uint64(1 << 63)).view(np.int64).astype(object)
+                    res = np.array([max(abs(int(x)), abs(int(y))) & ((1 << 64) - 1) for x, y in zip(mn, mx)],
+                                   dtype=np.uint64)
+                elif is_int:
+                    res = st[3].copy()
+                else:
+                    f = np.maximum(np.abs(dec(st[2])), np.abs(dec(st[3])))
+                    res = np.ascontiguousarray(f).view(np.uint64)
             else:
                 m = _arr(m2, np.float64, g)
                 c = cnt.astype(np.float64)
