@@ -57,7 +57,10 @@ def main():
     cases = [(["k"], [False], None), (["k", "f"], [True, False], None), (["f"], [True], None),
              (["f", "k"], [True, True], None), (["s"], [False], None), (["s"], [True], None),
              (["s"], [False], [("s1",), ("s5",), (None,)]),
-             (["k"], [False], [(-20,), (0,), (0,), (31,)]), (["k"], [True], [(10,), (-10,)])]
+             (["k"], [False], [(-20,), (0,), (0,), (31,)]), (["k"], [True], [(10,), (-10,)]),
+             # key tuples that mix numeric and string columns (xchg_*_mixed)
+             (["k", "s"], [False, False], None), (["s", "k"], [False, True], None),
+             (["k", "s"], [False, False], [(-20, "s1"), (0, None), (10, "s5"), (10, "s5s5")])]
     for cols, desc, bounds in cases:
         sk = SortKey(cols, desc)
         out = ex.sort_blocks_distributed(mine, sk, boundaries=bounds, seed=3)
