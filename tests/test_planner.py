@@ -276,3 +276,26 @@ def test_block_builders():
     d.add_block(pd.DataFrame({"x": [5, 6]}))
     d.add({"x": 7})
     assert d.build()["x"].to_pylist() == [5, 6, 7]
+
+
+@pytest.mark.parametrize("strategy", STRATEGIES, ids=lambda s: s.value)
+@pytest.mark.parametrize("cols,desc", [(["k", "s"], [False, False]), (["s", "k"], [False, True])])
+def test_sort_by_numeric_and_string_keys(engine, strategy, cols, desc):
+    """Dataset.sort on a key tuple that mixes numeric and string columns, through the planner
+    with sampled boundaries (planner/sort.py:43-62 -> SortTaskSpec.sample_boundaries): every
+    strategy returns the stable sort of all rows, cut into as many blocks as came in.  Planner
+    and scheduler logic only: the kernels underneath run on the GPU in tests/test_mixed_keys.py."""
+    if engine == "b200":
+        pytest.skip("host logic; GPU coverage of the same kernels is in tests/test_mixed_keys.py")
+    rng = np.random.default_rng(8)
+    words = ["", "a", "ab", "b", "zz", "m" * 20]
+    tables = [pa.table({"k": pa.array(rng.integers(-3, 4, n), pa.int32()),
+                        "s": pa.array([None if rng.random() < 0.1 else words[int(rng.integers(0, len(words)))]
+                                       for _ in range(n)], pa.string()),
+                        "row": pa.array(np.arange(n), pa.int64())}) for n in (400, 0, 250, 90)]
+    ctx = P.DataContext(shuffle_strategy=strategy)
+    out, _ = P.execute_all_to_all(P.Sort(P.InputData(), SortKey(cols, desc)), _bundles(tables), ctx)
+    blocks = _blocks_of(out)
+    assert len(blocks) == len(tables)
+    got = pa.concat_tables([b for b in blocks if b.num_rows])
+    assert G.tables_equal(got, O.sort_table(pa.concat_tables(tables), cols, desc))
